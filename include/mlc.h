@@ -1,0 +1,165 @@
+/* mlc.h - C ABI of libmlcomp_b200.so
+ *
+ * B200 (sm_100a) implementation of MLComp's post-inference scoring and
+ * post-processing hot path.  The reference (deepalcoholic/mlcomp 20.3.1.1) is
+ * pure Python: this path has no FFI there.  Each entry point therefore names
+ * the Python function(s) of the reference whose arithmetic it replaces
+ * (paths relative to the reference root); INTEGRATION.md shows the ctypes
+ * stub a maintainer would add on the reference side.
+ *
+ * Conventions
+ *  - every function returns MLC_OK (0) or a negative MLC_ERR_* code; the text
+ *    of the last error on the calling thread is mlc_last_error();
+ *  - "dev" pointers are device memory owned by the caller, "host" pointers
+ *    are ordinary host memory read before the call returns;
+ *  - nothing here allocates or frees device memory; scratch is passed in;
+ *  - `stream` is a cudaStream_t (NULL = legacy default stream); all work is
+ *    enqueued asynchronously on it; no call synchronises unless it says so;
+ *  - planes are (image, class) pairs, plane index p = image * n_cls + class;
+ *    logits are row-major [n_img][n_cls][H][W] per source.
+ */
+#ifndef MLC_H_
+#define MLC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MLC_OK               0
+#define MLC_ERR_ARG        (-1)  /* bad argument (null, range, alignment)   */
+#define MLC_ERR_CUDA       (-2)  /* a CUDA runtime call or launch failed     */
+#define MLC_ERR_UNSUPPORTED (-3) /* valid request this build cannot serve    */
+#define MLC_ERR_CAPACITY   (-4)  /* caller-provided buffer too small         */
+
+/* element type of logits */
+#define MLC_F16 0
+#define MLC_F32 1
+
+/* activation: utils/torch.py:11-18 apply_activation */
+#define MLC_ACT_NONE    0
+#define MLC_ACT_SIGMOID 1
+
+/* Composed inverse test-time transform of one source, i.e. what
+ * TtaWrap.inverse (contrib/transform/tta.py:20-31) does to it:
+ *   out[y][x] = src[ys][xs],  (u, v) = TRANSPOSE ? (x, y) : (y, x),
+ *   ys = VFLIP ? Hs-1-u : u,  xs = HFLIP ? Ws-1-v : v,
+ * (Hs, Ws) = the source's own plane shape = TRANSPOSE ? (W, H) : (H, W). */
+#define MLC_XF_HFLIP     1
+#define MLC_XF_VFLIP     2
+#define MLC_XF_TRANSPOSE 4
+
+#define MLC_MAX_SOURCES  32   /* TTA variants x ensemble members            */
+#define MLC_MAX_THR      255  /* thresholds in one search grid              */
+#define MLC_MAX_AREAS    8    /* min-area candidates per class              */
+#define MLC_MAX_CLASSES_SEG 64
+#define MLC_LUT_BYTES    65536
+
+int mlc_version(void);
+const char *mlc_last_error(void);
+
+/* ---- classification ---------------------------------------------------
+ * Replaces  preds.argmax(axis=1)  +  sklearn confusion_matrix(targets,
+ * argmax, labels=arange(C))  (worker/reports/classification.py:133-138) and
+ * the per-sample hit (examples/digit-recognizer/executors/valid.py:47).
+ *   preds_dev   [n][n_cls] f16/f32 row-major (logits or probabilities)
+ *   labels_dev  [n] int64; rows whose label is outside [0,n_cls) are dropped
+ *               from cm (sklearn's rule) and counted in stats[1]
+ *   cm_dev      [n_cls][n_cls] int64, rows = truth, cols = prediction;
+ *               ADDED to (zero it for a fresh matrix) so chunks accumulate
+ *   stats_dev   [2] int64, ADDED to: {#argmax==label, #dropped}
+ *   argmax_dev  [n] int32 or NULL: first index of the row maximum (NaN
+ *               counts as maximal, like numpy)
+ */
+int mlc_confusion(const void *preds_dev, int dtype, int64_t n, int n_cls,
+                  const int64_t *labels_dev, int64_t *cm_dev,
+                  int64_t *stats_dev, int32_t *argmax_dev, void *stream);
+
+/* ---- segmentation: fused TTA / ensemble mean + threshold histogram -----
+ * Replaces, for every pixel, apply_activation (utils/torch.py:11-18) ->
+ * TtaWrap.inverse / flip (contrib/transform/tta.py:20-31,
+ * contrib/torch/tensors.py:4-8) -> mean over sources -> the `>=`, `.sum()`
+ * and `targets*outputs` passes of dice_numpy (contrib/metrics/dice.py:6-11,
+ * 20) for ALL thresholds at once.
+ *
+ * cnt(p) = #{k : p >= thr[k]} (fp32 compare, thr ascending); NaN -> 0.
+ *   hist_dev [n_img*n_cls][2][n_thr+1] uint32: hist[p][g][j] = pixels of
+ *   plane p with ground truth g (gt byte != 0) and cnt == j.  Overwritten.
+ *
+ *   src_dev_ptrs host array of n_src device pointers, each [n_img][n_cls]
+ *               [Hs][Ws] of `dtype`; xform host array of MLC_XF_* masks
+ *   gt_dev      [n_img][n_cls][H][W] uint8 one-hot planes
+ *               (contrib/dataset/segment.py:36-56 builds them as fp32)
+ *   thr_host    [n_thr] fp32 ascending, n_thr <= MLC_MAX_THR
+ *   lut_dev     NULL, or MLC_LUT_BYTES made by mlc_seg_lut_build with the
+ *               same thr/act: enables the table path for a single
+ *               untransformed fp16 source (results are identical)
+ */
+int mlc_seg_lut_build(const float *thr_host, int n_thr, int act,
+                      uint8_t *lut_dev, void *stream);
+
+int mlc_seg_hist(const void *const *src_dev_ptrs, const int32_t *xform,
+                 int n_src, int dtype, const uint8_t *gt_dev, int64_t n_img,
+                 int n_cls, int H, int W, const float *thr_host, int n_thr,
+                 int act, const uint8_t *lut_dev, uint32_t *hist_dev,
+                 void *stream);
+
+/* Same fusion, writing the fp32 probabilities [n_img][n_cls][H][W] instead
+ * (what utils/torch.py:24-29 `_infer` returns after the mean). */
+int mlc_seg_prob(const void *const *src_dev_ptrs, const int32_t *xform,
+                 int n_src, int dtype, int64_t n_img, int n_cls, int H, int W,
+                 int act, float *prob_dev, void *stream);
+
+/* ---- segmentation: histograms -> dice for the whole search grid --------
+ * Replaces the loop of dice_numpy calls (contrib/metrics/dice.py:4-23) over
+ * thresholds x min-areas x planes.  From hist: T = sum_j hist[1][j],
+ * P[k] = sum_{j>k} (hist[0][j]+hist[1][j]), I[k] = sum_{j>k} hist[1][j];
+ * min-area rule dice.py:13-15, empty rule :17-18, 2I/(T+P+eps) in fp64 :20-23.
+ *   min_area_host [n_cls][n_area] int32 (0 disables), n_area <= MLC_MAX_AREAS
+ *   dice_sum_dev  [n_cls][n_thr][n_area] fp64: sum over images (overwritten;
+ *                 summed in a fixed order: bit-reproducible)
+ *   micro_dev     [n_cls][1+2*n_thr] int64 or NULL: {T, P[0..], I[0..]}
+ *                 summed over images (overwritten)
+ *   work_dev      scratch of at least mlc_dice_search_workspace(...) bytes
+ */
+size_t mlc_dice_search_workspace(int64_t n_img, int n_cls, int n_thr,
+                                 int n_area);
+int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img, int n_cls,
+                    int n_thr, const int32_t *min_area_host, int n_area,
+                    int empty_one, double eps, double *dice_sum_dev,
+                    int64_t *micro_dev, void *work_dev, size_t work_bytes,
+                    void *stream);
+
+/* Per-plane dice at one chosen (threshold index, min_area) per class:
+ * dice_dev [n_img*n_cls] fp64 (the per-image `scores` the report builders
+ * take, worker/reports/segmenation.py:148-150). */
+int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img, int n_cls,
+                   int n_thr, const int32_t *k_host, const int32_t *min_area_host,
+                   int empty_one, double eps, double *dice_dev, void *stream);
+
+/* ---- run-length encoding ------------------------------------------------
+ * Replaces (prob >= t) + min-area reject + mask2rle
+ * (contrib/transform/rle.py:4-13): column-major, 1-based (start, length).
+ *   thr_host, min_area_host  [n_cls]
+ *   runs_dev   int32[capacity]: (start, length) pairs, plane by plane in
+ *              arbitrary order; plane p owns runs_dev[off[p] .. off[p]+2*cnt[p])
+ *   off_dev    [planes] int64, cnt_dev [planes] int32 (#runs),
+ *   area_dev   [planes] int32 mask area BEFORE the min-area rule (or NULL)
+ *   total_dev  [1] int64: int32 elements needed; if > capacity the planes
+ *              that did not fit have off = -1 and the caller retries bigger.
+ *   src may be uint8 masks already: dtype MLC_U8 with act NONE and thr 0.5
+ */
+#define MLC_U8 2
+int mlc_rle_encode(const void *const *src_dev_ptrs, const int32_t *xform,
+                   int n_src, int dtype, int64_t n_img, int n_cls, int H, int W,
+                   const float *thr_host, const int32_t *min_area_host, int act,
+                   int32_t *runs_dev, int64_t capacity, int64_t *off_dev,
+                   int32_t *cnt_dev, int32_t *area_dev, int64_t *total_dev,
+                   void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MLC_H_ */

@@ -1,0 +1,267 @@
+// K1b: per-plane histograms -> suffix scan -> P(t), I(t), T -> dice for the
+// whole (threshold x min-area) grid, summed over images in a fixed order.
+// Contract: include/mlc.h (mlc_dice_search, mlc_plane_dice).
+#include "mlc_common.cuh"
+
+namespace mlc {
+
+struct AreaTable {
+  int v[MLC_MAX_CLASSES_SEG * MLC_MAX_AREAS];
+};
+
+// dice.py:13-23 from exact integers.  t, p, i < 2^31.
+__device__ __forceinline__ double dice_point(unsigned t, unsigned p, unsigned i,
+                                             int min_area, int empty_one,
+                                             double eps) {
+  if (min_area > 0 && p < (unsigned)min_area) {  // dice.py:13-15
+    p = 0;
+    i = 0;
+  }
+  if (empty_one && t == 0 && p == 0) return 1.0;  // dice.py:17-18
+  // dice.py:20-23: 2*I (exact) / (T + P + eps) in fp64
+  return (double)(2ull * i) / ((double)((unsigned long long)t + p) + eps);
+}
+
+// Inclusive suffix sum over j (bins) of packed (total << 32 | positives)
+// across the CTA; returns S[j] = sum_{i >= j} v[i].
+__device__ __forceinline__ unsigned long long block_suffix_sum(
+    unsigned long long v, unsigned long long *warp_tot) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int n_warps = blockDim.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned long long t = __shfl_down_sync(0xffffffffu, v, o);
+    if (lane + o < 32) v += t;
+  }
+  if (lane == 0) warp_tot[w] = v;
+  __syncthreads();
+  unsigned long long add = 0;
+  for (int k = w + 1; k < n_warps; ++k) add += warp_tot[k];
+  __syncthreads();
+  return v + add;
+}
+
+struct SearchArgs {
+  const uint32_t *hist;
+  double *partial;               // [n_chunks][C][B][A]
+  unsigned long long *micro;     // [C][1+2B] or null
+  AreaTable areas;               // [C][A]
+  long long n_img;
+  int C, B, A;
+  int imgs_per_chunk;
+  int empty_one;
+  double eps;
+};
+
+// grid = (C, n_chunks); thread j owns bin j (j <= B) and threshold k = j.
+__global__ void __launch_bounds__(256)
+dice_search_kernel(const __grid_constant__ SearchArgs a) {
+  __shared__ unsigned long long warp_tot[8];
+  __shared__ unsigned long long S[MLC_MAX_THR + 2];
+  const int c = blockIdx.x, chunk = blockIdx.y;
+  const int j = threadIdx.x;
+  const int nb = a.B + 1;
+  const long long n0 = (long long)chunk * a.imgs_per_chunk;
+  const long long n1 = min(a.n_img, n0 + a.imgs_per_chunk);
+  double acc[MLC_MAX_AREAS];
+#pragma unroll
+  for (int m = 0; m < MLC_MAX_AREAS; ++m) acc[m] = 0.0;
+  unsigned long long sumP = 0, sumI = 0, sumT = 0;
+  int area[MLC_MAX_AREAS];
+#pragma unroll
+  for (int m = 0; m < MLC_MAX_AREAS; ++m)
+    area[m] = m < a.A ? a.areas.v[c * a.A + m] : 0;
+
+  for (long long n = n0; n < n1; ++n) {
+    const uint32_t *h = a.hist + ((size_t)n * a.C + c) * 2 * nb;
+    unsigned long long v = 0;
+    if (j < nb) {
+      const unsigned h0 = h[j], h1 = h[nb + j];
+      v = ((unsigned long long)(h0 + h1) << 32) | h1;
+    }
+    const unsigned long long s = block_suffix_sum(v, warp_tot);
+    if (j < nb) S[j] = s;
+    if (j == 0) S[nb] = 0ull;
+    __syncthreads();
+    if (j < a.B) {
+      const unsigned long long up = S[j + 1];  // bins above threshold j
+      const unsigned p = (unsigned)(up >> 32), i = (unsigned)up;
+      const unsigned t = (unsigned)S[0];
+#pragma unroll
+      for (int m = 0; m < MLC_MAX_AREAS; ++m)
+        if (m < a.A)
+          acc[m] += dice_point(t, p, i, area[m], a.empty_one, a.eps);
+      sumP += p;
+      sumI += i;
+      if (j == 0) sumT += t;
+    }
+    __syncthreads();
+  }
+  if (j < a.B) {
+    double *out = a.partial +
+                  (((size_t)chunk * a.C + c) * a.B + j) * a.A;
+#pragma unroll
+    for (int m = 0; m < MLC_MAX_AREAS; ++m)
+      if (m < a.A) out[m] = acc[m];
+    if (a.micro) {
+      unsigned long long *mo = a.micro + (size_t)c * (1 + 2 * a.B);
+      if (j == 0 && sumT) atomicAdd(mo, sumT);
+      if (sumP) atomicAdd(mo + 1 + j, sumP);
+      if (sumI) atomicAdd(mo + 1 + a.B + j, sumI);
+    }
+  }
+}
+
+// Sum the per-chunk partials in chunk order (fixed order => reproducible).
+__global__ void dice_reduce_kernel(const double *partial, double *out,
+                                   int n_chunks, long long cells) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cells) return;
+  double s = 0.0;
+  for (int k = 0; k < n_chunks; ++k) s += partial[(size_t)k * cells + i];
+  out[i] = s;
+}
+
+static int chunks_for(int64_t n_img, int n_cls) {
+  long long per_cls = (4ll * 148 + n_cls - 1) / n_cls;  // shape-only, no device query
+  if (per_cls < 1) per_cls = 1;
+  return (int)(n_img < per_cls ? (n_img < 1 ? 1 : n_img) : per_cls);
+}
+
+struct PlaneArgs {
+  const uint32_t *hist;
+  double *dice;
+  long long n_planes;
+  int C, B;
+  int empty_one;
+  double eps;
+  int k[MLC_MAX_CLASSES_SEG];
+  int area[MLC_MAX_CLASSES_SEG];
+};
+
+// one warp per plane
+__global__ void __launch_bounds__(256)
+plane_dice_kernel(const __grid_constant__ PlaneArgs a) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (warp >= a.n_planes) return;
+  const int c = (int)(warp % a.C);
+  const int nb = a.B + 1;
+  const uint32_t *h = a.hist + (size_t)warp * 2 * nb;
+  const int k = a.k[c];
+  unsigned t = 0, p = 0, i = 0;
+  for (int j = lane; j < nb; j += 32) {
+    const unsigned h0 = h[j], h1 = h[nb + j];
+    t += h1;
+    if (j > k) {
+      p += h0 + h1;
+      i += h1;
+    }
+  }
+  for (int o = 16; o; o >>= 1) {
+    t += __shfl_xor_sync(0xffffffffu, t, o);
+    p += __shfl_xor_sync(0xffffffffu, p, o);
+    i += __shfl_xor_sync(0xffffffffu, i, o);
+  }
+  if (lane == 0)
+    a.dice[warp] = dice_point(t, p, i, a.area[c], a.empty_one, a.eps);
+}
+
+}  // namespace mlc
+
+using namespace mlc;
+
+extern "C" size_t mlc_dice_search_workspace(int64_t n_img, int n_cls, int n_thr,
+                                            int n_area) {
+  if (n_img < 0 || n_cls < 1 || n_thr < 1 || n_area < 1) return 0;
+  return (size_t)chunks_for(n_img, n_cls) * n_cls * n_thr * n_area *
+         sizeof(double);
+}
+
+extern "C" int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img,
+                               int n_cls, int n_thr,
+                               const int32_t *min_area_host, int n_area,
+                               int empty_one, double eps, double *dice_sum_dev,
+                               int64_t *micro_dev, void *work_dev,
+                               size_t work_bytes, void *stream) {
+  MLC_REQUIRE(hist_dev && dice_sum_dev && min_area_host,
+              "hist/dice_sum/min_area pointer is null");
+  MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && n_cls <= MLC_MAX_CLASSES_SEG,
+              "bad n_img=%lld / n_cls=%d (max %d classes)", (long long)n_img,
+              n_cls, MLC_MAX_CLASSES_SEG);
+  MLC_REQUIRE(n_thr >= 1 && n_thr <= MLC_MAX_THR, "n_thr=%d outside [1, %d]",
+              n_thr, MLC_MAX_THR);
+  MLC_REQUIRE(n_area >= 1 && n_area <= MLC_MAX_AREAS,
+              "n_area=%d outside [1, %d]", n_area, MLC_MAX_AREAS);
+  const size_t need = mlc_dice_search_workspace(n_img, n_cls, n_thr, n_area);
+  if (!work_dev || work_bytes < need) {
+    set_error("workspace of %zu bytes needed, %zu given", need, work_bytes);
+    return MLC_ERR_CAPACITY;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long cells = (long long)n_cls * n_thr * n_area;
+  if (micro_dev)
+    MLC_CUDA(cudaMemsetAsync(micro_dev, 0,
+                             (size_t)n_cls * (1 + 2 * n_thr) * 8, st));
+  if (n_img == 0) {
+    MLC_CUDA(cudaMemsetAsync(dice_sum_dev, 0, (size_t)cells * 8, st));
+    return MLC_OK;
+  }
+  SearchArgs a;
+  a.hist = hist_dev;
+  a.partial = static_cast<double *>(work_dev);
+  a.micro = reinterpret_cast<unsigned long long *>(micro_dev);
+  for (int i = 0; i < n_cls * n_area; ++i) {
+    MLC_REQUIRE(min_area_host[i] >= 0, "min_area[%d] is negative", i);
+    a.areas.v[i] = min_area_host[i];
+  }
+  a.n_img = n_img;
+  a.C = n_cls;
+  a.B = n_thr;
+  a.A = n_area;
+  const int n_chunks = chunks_for(n_img, n_cls);
+  a.imgs_per_chunk = (int)((n_img + n_chunks - 1) / n_chunks);
+  a.empty_one = empty_one;
+  a.eps = eps;
+  const int threads = ((n_thr + 1) + 31) / 32 * 32;  // one per bin
+  dice_search_kernel<<<dim3(n_cls, n_chunks), threads, 0, st>>>(a);
+  MLC_LAUNCH_CHECK("dice_search_kernel");
+  dice_reduce_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, st>>>(
+      a.partial, dice_sum_dev, n_chunks, cells);
+  MLC_LAUNCH_CHECK("dice_reduce_kernel");
+  return MLC_OK;
+}
+
+extern "C" int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img,
+                              int n_cls, int n_thr, const int32_t *k_host,
+                              const int32_t *min_area_host, int empty_one,
+                              double eps, double *dice_dev, void *stream) {
+  MLC_REQUIRE(hist_dev && dice_dev && k_host && min_area_host,
+              "hist/dice/k/min_area pointer is null");
+  MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && n_cls <= MLC_MAX_CLASSES_SEG,
+              "bad n_img=%lld / n_cls=%d (max %d classes)", (long long)n_img,
+              n_cls, MLC_MAX_CLASSES_SEG);
+  MLC_REQUIRE(n_thr >= 1 && n_thr <= MLC_MAX_THR, "n_thr=%d outside [1, %d]",
+              n_thr, MLC_MAX_THR);
+  if (n_img == 0) return MLC_OK;
+  PlaneArgs a;
+  a.hist = hist_dev;
+  a.dice = dice_dev;
+  a.n_planes = (long long)n_img * n_cls;
+  a.C = n_cls;
+  a.B = n_thr;
+  a.empty_one = empty_one;
+  a.eps = eps;
+  for (int c = 0; c < n_cls; ++c) {
+    MLC_REQUIRE(k_host[c] >= 0 && k_host[c] < n_thr,
+                "threshold index %d of class %d outside [0, %d)", k_host[c], c,
+                n_thr);
+    MLC_REQUIRE(min_area_host[c] >= 0, "min_area of class %d is negative", c);
+    a.k[c] = k_host[c];
+    a.area[c] = min_area_host[c];
+  }
+  const long long blocks = (a.n_planes + 7) / 8;
+  plane_dice_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  MLC_LAUNCH_CHECK("plane_dice_kernel");
+  return MLC_OK;
+}

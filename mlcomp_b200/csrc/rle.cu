@@ -1,0 +1,231 @@
+// K3: threshold (+ min-area reject) -> Kaggle run-length pairs, one CTA per
+// plane, one read of the logits.  Contract: include/mlc.h (mlc_rle_encode).
+//
+// mask2rle (contrib/transform/rle.py:4-13) scans the mask column-major
+// (img.T.flatten()).  Phase 1 reads the row-major plane with coalesced row
+// segments and transposes in registers: a lane keeps 8 columns and shifts one
+// bit per row into 8 words, so after 32 rows it owns 8 finished words of the
+// COLUMN-major bit plane, which lives in shared memory as bits[x][Hw]
+// (Hw = ceil(H/32) words per column, padding bits zero).  Phase 2 finds run
+// starts / ends per word with shifts and popc/ffs, a block-wide scan gives
+// every thread its output slot, the CTA reserves its slice of the output with
+// one atomic and writes (start, end) then turns end into length in place.
+#include "mlc_common.cuh"
+
+namespace mlc {
+
+constexpr int kRleThreads = 512;
+constexpr size_t kRleMaxSmem = 200 * 1024;
+
+struct RleArgs {
+  SrcSet src;
+  float thr[MLC_MAX_CLASSES_SEG];
+  int min_area[MLC_MAX_CLASSES_SEG];
+  int32_t *runs;
+  long long capacity;
+  long long *off;
+  int32_t *cnt;
+  int32_t *area;
+  unsigned long long *total;
+  long long n_planes;
+  int C, H, W, Hw;
+  int act;
+};
+
+__device__ __forceinline__ int block_excl_scan(int v, int *warp_tot,
+                                               int *total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_tot[w] = inc;
+  __syncthreads();
+  int add = 0, all = 0;
+  const int n_warps = blockDim.x >> 5;
+  for (int k = 0; k < n_warps; ++k) {
+    const int t = warp_tot[k];
+    if (k < w) add += t;
+    all += t;
+  }
+  __syncthreads();
+  *total = all;
+  return add + inc - v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kRleThreads)
+rle_kernel(const __grid_constant__ RleArgs a) {
+  extern __shared__ uint32_t bits[];  // [W][Hw]
+  __shared__ int warp_tot[kRleThreads / 32];
+  __shared__ long long s_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n_warps = kRleThreads / 32;
+  const int H = a.H, W = a.W, Hw = a.Hw;
+  const int nW = W * Hw;
+  const int hl = (H - 1) & 31;  // top valid bit of a column's last word
+  const int xchunks = (W + 255) / 256;
+  const int n_tiles = Hw * xchunks;
+
+  for (long long plane = blockIdx.x; plane < a.n_planes; plane += gridDim.x) {
+    const int c = (int)(plane % a.C);
+    const float thr = a.thr[c];
+    const size_t plane_off = (size_t)plane * H * W;
+
+    // ---- phase 1: column-major bit plane ---------------------------------
+    for (int tile = warp; tile < n_tiles; tile += n_warps) {
+      const int yb = tile / xchunks;
+      const int x0 = (tile - yb * xchunks) * 256 + lane * 8;
+      const int nv = min(8, W - x0);
+      uint32_t word[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (nv > 0) {
+        const int rows = min(32, H - yb * 32);
+        for (int r = 0; r < rows; ++r) {
+          float p[8];
+          fused_prob8<T>(a.src, plane_off, H, W, yb * 32 + r, x0, nv, a.act,
+                         p);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            word[i] |= (uint32_t)(i < nv && p[i] >= thr) << r;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (i < nv) bits[(x0 + i) * Hw + yb] = word[i];
+      }
+    }
+    __syncthreads();
+
+    // ---- phase 2: runs -----------------------------------------------------
+    const int per = (nW + kRleThreads - 1) / kRleThreads;
+    const int q0 = min(nW, (int)threadIdx.x * per);
+    const int q1 = min(nW, q0 + per);
+    int n_starts = 0, n_px = 0;
+    for (int q = q0; q < q1; ++q) {
+      const uint32_t w = bits[q];
+      const int yb = q % Hw;
+      uint32_t prev = 0;
+      if (q > 0) prev = yb > 0 ? bits[q - 1] >> 31 : (bits[q - 1] >> hl) & 1u;
+      n_starts += __popc(w & ~((w << 1) | prev));
+      n_px += __popc(w);
+    }
+    int tot_runs, tot_px;
+    const int my_first = block_excl_scan(n_starts, warp_tot, &tot_runs);
+    (void)block_excl_scan(n_px, warp_tot, &tot_px);
+    const int min_area = a.min_area[c];
+    if (min_area > 0 && tot_px < min_area) tot_runs = 0;  // dice.py:13-15 rule
+    if (threadIdx.x == 0) {
+      long long base = (long long)atomicAdd(a.total, 2ull * tot_runs);
+      if (base + 2ll * tot_runs > a.capacity) base = -1;
+      s_base = base;
+      a.off[plane] = base;
+      a.cnt[plane] = tot_runs;
+      if (a.area) a.area[plane] = tot_px;
+    }
+    __syncthreads();
+    const long long base = s_base;
+    if (tot_runs > 0 && base >= 0) {
+      int32_t *out = a.runs + base;
+      int si = my_first;
+      for (int q = q0; q < q1; ++q) {
+        const uint32_t w = bits[q];
+        const int x = q / Hw, yb = q - x * Hw;
+        uint32_t prev = 0, next = 0;
+        if (q > 0) prev = yb > 0 ? bits[q - 1] >> 31 : (bits[q - 1] >> hl) & 1u;
+        if (q + 1 < nW) next = bits[q + 1] & 1u;
+        const int top = yb == Hw - 1 ? hl : 31;
+        uint32_t starts = w & ~((w << 1) | prev);
+        uint32_t ends = w & ~((w >> 1) | (next << top));
+        const int pos0 = x * H + yb * 32 + 1;  // 1-based, column-major
+        int ei = si - (int)prev;
+        while (starts) {
+          const int b = __ffs(starts) - 1;
+          starts &= starts - 1;
+          out[2 * (si++)] = pos0 + b;
+        }
+        while (ends) {
+          const int b = __ffs(ends) - 1;
+          ends &= ends - 1;
+          out[2 * (ei++) + 1] = pos0 + b + 1;  // exclusive end
+        }
+      }
+      __syncthreads();
+      for (int j = threadIdx.x; j < tot_runs; j += kRleThreads)
+        out[2 * j + 1] -= out[2 * j];  // rle.py:12 runs[1::2] -= runs[::2]
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace mlc
+
+using namespace mlc;
+
+extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
+                              const int32_t *xform, int n_src, int dtype,
+                              int64_t n_img, int n_cls, int H, int W,
+                              const float *thr_host,
+                              const int32_t *min_area_host, int act,
+                              int32_t *runs_dev, int64_t capacity,
+                              int64_t *off_dev, int32_t *cnt_dev,
+                              int32_t *area_dev, int64_t *total_dev,
+                              void *stream) {
+  MLC_REQUIRE(dtype == MLC_F16 || dtype == MLC_F32 || dtype == MLC_U8,
+              "dtype %d is not MLC_F16/MLC_F32/MLC_U8", dtype);
+  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID,
+              "unknown activation code %d", act);
+  MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && n_cls <= MLC_MAX_CLASSES_SEG &&
+                  H >= 1 && W >= 1,
+              "bad shape n_img=%lld n_cls=%d H=%d W=%d", (long long)n_img,
+              n_cls, H, W);
+  MLC_REQUIRE((long long)H * W < (1ll << 31) - 2, "plane of %d x %d too large",
+              H, W);
+  MLC_REQUIRE(thr_host && min_area_host, "thr_host / min_area_host is null");
+  MLC_REQUIRE(off_dev && cnt_dev && total_dev, "off/cnt/total is null");
+  MLC_REQUIRE(capacity >= 0 && (runs_dev || capacity == 0),
+              "runs_dev is null with capacity %lld", (long long)capacity);
+  RleArgs a;
+  const int eb = dtype == MLC_F16 ? 2 : dtype == MLC_F32 ? 4 : 1;
+  if (int rc = fill_srcset(a.src, src_dev_ptrs, xform, n_src, eb, H, W))
+    return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  MLC_CUDA(cudaMemsetAsync(total_dev, 0, 8, st));
+  if (n_img == 0) return MLC_OK;
+  for (int c = 0; c < n_cls; ++c) {
+    MLC_REQUIRE(thr_host[c] == thr_host[c], "thr[%d] is NaN", c);
+    MLC_REQUIRE(min_area_host[c] >= 0, "min_area[%d] is negative", c);
+    a.thr[c] = thr_host[c];
+    a.min_area[c] = min_area_host[c];
+  }
+  a.runs = runs_dev;
+  a.capacity = capacity;
+  a.off = reinterpret_cast<long long *>(off_dev);
+  a.cnt = cnt_dev;
+  a.area = area_dev;
+  a.total = reinterpret_cast<unsigned long long *>(total_dev);
+  a.n_planes = (long long)n_img * n_cls;
+  a.C = n_cls;
+  a.H = H;
+  a.W = W;
+  a.Hw = (H + 31) / 32;
+  a.act = act;
+  const size_t smem = (size_t)W * a.Hw * 4;
+  if (smem > kRleMaxSmem) {
+    set_error("plane %d x %d needs %zu bytes of shared memory for its bit "
+              "plane; this build supports up to %zu",
+              H, W, smem, kRleMaxSmem);
+    return MLC_ERR_UNSUPPORTED;
+  }
+  void (*kern)(RleArgs) = dtype == MLC_F16   ? rle_kernel<__half>
+                          : dtype == MLC_F32 ? rle_kernel<float>
+                                             : rle_kernel<uint8_t>;
+  MLC_CUDA(cudaFuncSetAttribute(kern,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)kRleMaxSmem));
+  const int per_sm = (int)max((size_t)1, min((size_t)4, (220 * 1024) / (smem + 1024)));
+  const int grid = (int)min(a.n_planes, (long long)per_sm * sm_count());
+  kern<<<grid, kRleThreads, smem, st>>>(a);
+  MLC_LAUNCH_CHECK("rle_kernel");
+  return MLC_OK;
+}

@@ -1,0 +1,335 @@
+"""Torch-tensor front end of the C ABI (include/mlc.h).
+
+Thin by design: validate device / dtype / contiguity, allocate outputs with
+torch, pass raw pointers and the current CUDA stream through ctypes.  All
+arithmetic happens in the CUDA kernels of ``csrc/``; nothing here computes on
+the CPU and nothing falls back to PyTorch ops.
+"""
+import ctypes
+from ctypes import c_float, c_int32, c_void_p
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import (MLC_ACT_NONE, MLC_ACT_SIGMOID, MLC_F16, MLC_F32, MLC_U8,
+                   MLC_XF_HFLIP, MLC_XF_TRANSPOSE, MLC_XF_VFLIP, check)
+
+__all__ = ['activation_code', 'compose_tta', 'confusion', 'seg_lut',
+           'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
+           'threshold_grid', 'counts_from_hist', 'rle_strings']
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(t, name, dtypes=None):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError(f'{name} must be a CUDA tensor (mlcomp_b200 has no '
+                        'CPU path)')
+    if not t.is_contiguous():
+        raise ValueError(f'{name} must be contiguous')
+    if dtypes is not None and t.dtype not in dtypes:
+        raise TypeError(f'{name} has dtype {t.dtype}, expected one of {dtypes}')
+    return t
+
+
+def _ptr(t):
+    return c_void_p(t.data_ptr()) if t is not None else c_void_p(0)
+
+
+def _dtype_code(t):
+    if t.dtype == torch.float16:
+        return MLC_F16
+    if t.dtype == torch.float32:
+        return MLC_F32
+    if t.dtype == torch.uint8:
+        return MLC_U8
+    raise TypeError(f'unsupported element type {t.dtype}')
+
+
+def activation_code(activation):
+    """utils/torch.py:11-18: falsy -> none, 'sigmoid'; anything else raises
+    with the reference's message ('softmax' over classes is not served by
+    the segmentation kernels)."""
+    if not activation:
+        return MLC_ACT_NONE
+    if activation == 'sigmoid':
+        return MLC_ACT_SIGMOID
+    raise Exception(f'unknown activation = {activation}')
+
+
+def compose_tta(tags):
+    """Collapse the transform list of one TTA variant to an MLC_XF_* mask
+    describing what TtaWrap.inverse (contrib/transform/tta.py:20-31) does:
+    'hflip' flips the last dim, 'vflip' the one before, 'transpose' swaps
+    them, applied in list order.  Tags are the short names of
+    utils/config.py:93-104."""
+    tr = vf = hf = False
+    for t in tags:
+        if t == 'hflip':      # out'[y][x] = out[y][W-1-x]
+            if tr:
+                vf = not vf
+            else:
+                hf = not hf
+        elif t == 'vflip':
+            if tr:
+                hf = not hf
+            else:
+                vf = not vf
+        elif t == 'transpose':
+            tr = not tr
+        else:
+            raise Exception(f'Unknwon augmentation {t}')
+    return (MLC_XF_HFLIP if hf else 0) | (MLC_XF_VFLIP if vf else 0) | \
+        (MLC_XF_TRANSPOSE if tr else 0)
+
+
+def threshold_grid(bins=100):
+    """The search grid: thr[k] = float32(k / bins)."""
+    return (np.arange(bins) / bins).astype(np.float32)
+
+
+# ---------------------------------------------------------------- classify
+def confusion(preds, labels, cm=None, stats=None, want_argmax=False):
+    """argmax + confusion matrix + hit count (mlc_confusion).
+
+    Returns (cm [C,C] int64, stats [2] int64 = {correct, dropped},
+    argmax [n] int32 or None).  Pass cm/stats back in to accumulate chunks.
+    """
+    lib = _lib.load()
+    preds = _need_cuda(preds, 'preds', (torch.float16, torch.float32))
+    labels = _need_cuda(labels, 'labels', (torch.int64,))
+    if preds.dim() != 2 or labels.dim() != 1 or labels.shape[0] != preds.shape[0]:
+        raise ValueError('preds must be [n, C] and labels [n]')
+    n, c = preds.shape
+    dev = preds.device
+    if cm is None:
+        cm = torch.zeros((c, c), dtype=torch.int64, device=dev)
+    if stats is None:
+        stats = torch.zeros(2, dtype=torch.int64, device=dev)
+    _need_cuda(cm, 'cm', (torch.int64,))
+    _need_cuda(stats, 'stats', (torch.int64,))
+    if tuple(cm.shape) != (c, c) or stats.numel() != 2:
+        raise ValueError('cm must be [C, C] and stats [2]')
+    am = torch.empty(n, dtype=torch.int32, device=dev) if want_argmax else None
+    with torch.cuda.device(dev):
+        check(lib.mlc_confusion(_ptr(preds), _dtype_code(preds), n, c,
+                                _ptr(labels), _ptr(cm), _ptr(stats), _ptr(am),
+                                _stream()))
+    return cm, stats, am
+
+
+# ---------------------------------------------------------------- segment
+def _sources(sources, xforms, allow_u8=False):
+    if isinstance(sources, torch.Tensor):
+        sources = [sources]
+    sources = list(sources)
+    if not sources:
+        raise ValueError('at least one source is required')
+    if xforms is None:
+        xforms = [0] * len(sources)
+    xforms = [compose_tta(x) if not isinstance(x, int) else x for x in xforms]
+    if len(xforms) != len(sources):
+        raise ValueError('one transform per source is required')
+    ok = (torch.float16, torch.float32) + ((torch.uint8,) if allow_u8 else ())
+    first = _need_cuda(sources[0], 'sources[0]', ok)
+    if first.dim() != 4:
+        raise ValueError('sources must be [n_img, n_cls, H, W]')
+    tr0 = bool(xforms[0] & MLC_XF_TRANSPOSE)
+    n, c = first.shape[:2]
+    h, w = (first.shape[3], first.shape[2]) if tr0 else first.shape[2:]
+    for i, (s, x) in enumerate(zip(sources, xforms)):
+        _need_cuda(s, f'sources[{i}]', (first.dtype,))
+        want = (n, c, w, h) if x & MLC_XF_TRANSPOSE else (n, c, h, w)
+        if tuple(s.shape) != want or s.device != first.device:
+            raise ValueError(f'sources[{i}] has shape {tuple(s.shape)}, '
+                             f'expected {want} on {first.device}')
+    ptrs = (c_void_p * len(sources))(*[s.data_ptr() for s in sources])
+    xf = (c_int32 * len(sources))(*xforms)
+    return sources, ptrs, xf, int(n), int(c), int(h), int(w)
+
+
+def _thr(thr):
+    thr = np.ascontiguousarray(np.asarray(thr, dtype=np.float32).ravel())
+    return thr, thr.ctypes.data_as(ctypes.POINTER(c_float))
+
+
+def seg_lut(thr, activation='sigmoid', device=None):
+    """64 KiB table cnt(activation(x)) for every fp16 code (mlc_seg_lut_build)."""
+    lib = _lib.load()
+    thr, thr_p = _thr(thr)
+    device = torch.device('cuda' if device is None else device)
+    lut = torch.empty(_lib.MLC_LUT_BYTES, dtype=torch.uint8, device=device)
+    with torch.cuda.device(lut.device):
+        check(lib.mlc_seg_lut_build(thr_p, len(thr), activation_code(activation),
+                                    _ptr(lut), _stream()))
+    return lut
+
+
+def seg_hist(sources, gt, thr, xforms=None, activation='sigmoid', lut=None,
+             out=None):
+    """Fused TTA/ensemble mean + activation + label-conditioned histogram of
+    cnt(p) = #{k: p >= thr[k]} (mlc_seg_hist).  Returns int32
+    [n_img, n_cls, 2, B+1] (counts are < 2**31)."""
+    lib = _lib.load()
+    sources, ptrs, xf, n, c, h, w = _sources(sources, xforms)
+    gt = _need_cuda(gt, 'gt', (torch.uint8,))
+    if tuple(gt.shape) != (n, c, h, w):
+        raise ValueError(f'gt has shape {tuple(gt.shape)}, expected '
+                         f'{(n, c, h, w)} uint8 one-hot planes')
+    thr, thr_p = _thr(thr)
+    dev = sources[0].device
+    if out is None:
+        out = torch.empty((n, c, 2, len(thr) + 1), dtype=torch.int32, device=dev)
+    _need_cuda(out, 'out', (torch.int32,))
+    if out.numel() != n * c * 2 * (len(thr) + 1):
+        raise ValueError('out has the wrong size')
+    if lut is not None:
+        _need_cuda(lut, 'lut', (torch.uint8,))
+        if lut.numel() != _lib.MLC_LUT_BYTES:
+            raise ValueError('lut must come from seg_lut()')
+    with torch.cuda.device(dev):
+        check(lib.mlc_seg_hist(ptrs, xf, len(sources), _dtype_code(sources[0]),
+                               _ptr(gt), n, c, h, w, thr_p, len(thr),
+                               activation_code(activation), _ptr(lut),
+                               _ptr(out), _stream()))
+    return out
+
+
+def seg_prob(sources, xforms=None, activation='sigmoid'):
+    """Fused mean of activated, un-transformed sources -> fp32 [n,c,H,W]."""
+    lib = _lib.load()
+    sources, ptrs, xf, n, c, h, w = _sources(sources, xforms)
+    dev = sources[0].device
+    out = torch.empty((n, c, h, w), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.mlc_seg_prob(ptrs, xf, len(sources), _dtype_code(sources[0]),
+                               n, c, h, w, activation_code(activation),
+                               _ptr(out), _stream()))
+    return out
+
+
+def _areas(min_areas, n_cls):
+    a = np.asarray(min_areas, dtype=np.int64)
+    if a.ndim == 1:
+        a = np.broadcast_to(a, (n_cls, a.shape[0]))
+    if a.ndim != 2 or a.shape[0] != n_cls:
+        raise ValueError('min_areas must be [A] or [n_cls, A]')
+    a = np.ascontiguousarray(a.astype(np.int32))
+    return a, a.ctypes.data_as(ctypes.POINTER(c_int32))
+
+
+def dice_search(hist, min_areas=(0,), empty_one=True, eps=1e-6,
+                want_micro=True):
+    """Histograms -> sum over images of dice for every (class, threshold,
+    min-area) (mlc_dice_search).  Returns (dice_sum fp64 [C,B,A],
+    micro int64 [C, 1+2B] = {T, P[k], I[k]} or None)."""
+    lib = _lib.load()
+    hist = _need_cuda(hist, 'hist', (torch.int32,))
+    if hist.dim() != 4 or hist.shape[2] != 2:
+        raise ValueError('hist must be [n_img, n_cls, 2, B+1]')
+    n, c, _, nb = hist.shape
+    b = nb - 1
+    areas, areas_p = _areas(min_areas, c)
+    a = areas.shape[1]
+    dev = hist.device
+    out = torch.empty((c, b, a), dtype=torch.float64, device=dev)
+    micro = torch.empty((c, 1 + 2 * b), dtype=torch.int64, device=dev) \
+        if want_micro else None
+    need = lib.mlc_dice_search_workspace(n, c, b, a)
+    work = torch.empty(max(need, 8), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.mlc_dice_search(_ptr(hist), n, c, b, areas_p, a,
+                                  int(bool(empty_one)), float(eps), _ptr(out),
+                                  _ptr(micro), _ptr(work), work.numel(),
+                                  _stream()))
+    return out, micro
+
+
+def plane_dice(hist, k_per_class, min_area_per_class, empty_one=True,
+               eps=1e-6):
+    """Per-plane dice at one (threshold index, min_area) per class
+    (mlc_plane_dice): fp64 [n_img, n_cls]."""
+    lib = _lib.load()
+    hist = _need_cuda(hist, 'hist', (torch.int32,))
+    n, c, _, nb = hist.shape
+    k = np.ascontiguousarray(np.broadcast_to(
+        np.asarray(k_per_class, dtype=np.int32), (c,)))
+    ar = np.ascontiguousarray(np.broadcast_to(
+        np.asarray(min_area_per_class, dtype=np.int32), (c,)))
+    out = torch.empty((n, c), dtype=torch.float64, device=hist.device)
+    with torch.cuda.device(hist.device):
+        check(lib.mlc_plane_dice(_ptr(hist), n, c, nb - 1,
+                                 k.ctypes.data_as(ctypes.POINTER(c_int32)),
+                                 ar.ctypes.data_as(ctypes.POINTER(c_int32)),
+                                 int(bool(empty_one)), float(eps), _ptr(out),
+                                 _stream()))
+    return out
+
+
+def counts_from_hist(hist):
+    """Host-side view helper for tests/reports: (T [n,c], P [n,c,B],
+    I [n,c,B]) int64 from a histogram tensor, via torch integer ops on the
+    device (not on the timed path)."""
+    h = hist.to(torch.int64)
+    tot = h[:, :, 0] + h[:, :, 1]
+    p = tot.flip(-1).cumsum(-1).flip(-1)[..., 1:]
+    i = h[:, :, 1].flip(-1).cumsum(-1).flip(-1)[..., 1:]
+    return h[:, :, 1].sum(-1), p, i
+
+
+# -------------------------------------------------------------------- rle
+def rle_encode(sources, thr_per_class, min_area_per_class=0, xforms=None,
+               activation='sigmoid', capacity=None):
+    """(prob >= thr_c) + min-area reject + column-major run-length pairs
+    (mlc_rle_encode).  Returns device tensors
+    (runs int32 [total], off int64 [n,c], cnt int32 [n,c], area int32 [n,c]);
+    plane p owns runs[off[p] : off[p] + 2*cnt[p]] as (start, length) pairs.
+    Synchronises once to learn the total size (and retries if the first
+    guess of the capacity was too small)."""
+    lib = _lib.load()
+    sources, ptrs, xf, n, c, h, w = _sources(sources, xforms, allow_u8=True)
+    dev = sources[0].device
+    thr = np.ascontiguousarray(np.broadcast_to(
+        np.asarray(thr_per_class, dtype=np.float32), (c,)))
+    ar = np.ascontiguousarray(np.broadcast_to(
+        np.asarray(min_area_per_class, dtype=np.int32), (c,)))
+    off = torch.empty((n, c), dtype=torch.int64, device=dev)
+    cnt = torch.empty((n, c), dtype=torch.int32, device=dev)
+    area = torch.empty((n, c), dtype=torch.int32, device=dev)
+    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    if capacity is None:
+        # 1 run pair per 64 px is generous for real masks; retried if not
+        capacity = max(1024, n * c * h * w // 32)
+    while True:
+        runs = torch.empty(capacity, dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.mlc_rle_encode(
+                ptrs, xf, len(sources), _dtype_code(sources[0]), n, c, h, w,
+                thr.ctypes.data_as(ctypes.POINTER(c_float)),
+                ar.ctypes.data_as(ctypes.POINTER(c_int32)),
+                activation_code(activation), _ptr(runs), capacity, _ptr(off),
+                _ptr(cnt), _ptr(area), _ptr(total), _stream()))
+        need = int(total.item())
+        if need <= capacity:
+            return runs[:need], off, cnt, area
+        capacity = need
+
+
+def rle_strings(runs, off, cnt):
+    """Format device run pairs as the reference's strings
+    (contrib/transform/rle.py:13: ' '.join(str(x) for x in runs)); one string
+    per plane, '' for an empty mask.  Host-side formatting of integers the
+    GPU produced."""
+    runs_h = runs.cpu().numpy()
+    off_h = off.cpu().numpy().ravel()
+    cnt_h = cnt.cpu().numpy().ravel()
+    out = []
+    for o, k in zip(off_h, cnt_h):
+        if k == 0:
+            out.append('')
+        else:
+            out.append(' '.join(map(str, runs_h[o:o + 2 * k].tolist())))
+    return out

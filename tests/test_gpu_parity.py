@@ -1,0 +1,410 @@
+"""GPU parity: CUDA kernels (through the C ABI) against the CPU oracle on the
+same seeded inputs.  Integer outputs bit-exact; dice within 1e-5 relative (in
+practice bit-equal); probabilities: bit-equal to torch's CUDA sigmoid (the
+reference's own device path, utils/torch.py:15,24-25) and within 1 ulp of the
+CPU oracle, with threshold-straddling pixels counted and bounded."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+DEV = 'cuda:0'
+
+
+@pytest.fixture(scope='module')
+def ops():
+    from mlcomp_b200 import ops as o
+    return o
+
+
+def synth_seg(n, c, h, w, seed, dtype=torch.float16, n_src=1, empty=0.5):
+    """SURVEY.md 8(d)-style synthetic planes, generated on the CPU."""
+    rng = np.random.default_rng(seed)
+    gt = np.zeros((n, c, h, w), np.uint8)
+    yy, xx = np.mgrid[0:h, 0:w]
+    for i in range(n):
+        for j in range(c):
+            if rng.random() < empty:
+                continue
+            for _ in range(rng.integers(1, 4)):
+                cy, cx = rng.integers(0, h), rng.integers(0, w)
+                ry = rng.integers(1, max(2, h // 3))
+                rx = rng.integers(1, max(2, w // 3))
+                gt[i, j] |= (((yy - cy) / ry) ** 2 + ((xx - cx) / rx) ** 2
+                             <= 1).astype(np.uint8)
+    base = 8 * (gt.astype(np.float32) - 0.5) + rng.normal(0, 1.5, gt.shape)
+    srcs = [torch.from_numpy((base + rng.normal(0, 0.5, gt.shape))
+                             .astype(np.float32)).to(dtype)
+            for _ in range(n_src)]
+    return srcs, torch.from_numpy(gt)
+
+
+def forward_tta(x, tags):
+    """What the model saw: apply the transforms so that tta_inverse undoes
+    them (flips are involutions; inverse order for the general case)."""
+    return oracle.tta_inverse(x, list(reversed(tags))).contiguous()
+
+
+def ulp_diff(a, b):
+    ai = a.view(np.int32).astype(np.int64)
+    bi = b.view(np.int32).astype(np.int64)
+    return np.abs(ai - bi)
+
+
+# ------------------------------------------------------------ classification
+@pytest.mark.parametrize('n,c,dtype', [(42000, 10, torch.float32),
+                                       (5000, 10, torch.float16),
+                                       (777, 3, torch.float32),
+                                       (3000, 64, torch.float32),
+                                       (2000, 100, torch.float32),
+                                       (500, 1000, torch.float16),
+                                       (1, 1, torch.float32)])
+def test_confusion_bit_exact(ops, n, c, dtype):
+    rng = np.random.default_rng(n + c)
+    y = rng.integers(0, c, n)
+    logits = rng.normal(0, 1, (n, c)).astype(np.float32)
+    logits[np.arange(n), y] += 3.0
+    if c >= 3:
+        logits[: n // 10, 0] = logits[: n // 10, 2] = 7.0   # ties -> lowest
+    p = torch.from_numpy(logits).to(dtype)
+    ref_in = p.float().numpy()
+    cm, stats, am = ops.confusion(p.to(DEV), torch.from_numpy(y).to(DEV),
+                                  want_argmax=True)
+    assert np.array_equal(am.cpu().numpy(), ref_in.argmax(axis=1))
+    want = oracle.confusion(y, ref_in) if len(np.unique(y)) > 0 else None
+    assert cm.dtype == torch.int64
+    assert np.array_equal(cm.cpu().numpy(), want)
+    assert np.array_equal(cm.cpu().numpy(), oracle.confusion_numpy(y, ref_in))
+    scores = oracle.classify_scores(ref_in, y)
+    assert int(stats[0]) == int(scores.sum()) and int(stats[1]) == 0
+    # accumulate a second chunk into the same matrix
+    cm2, stats2, _ = ops.confusion(p.to(DEV), torch.from_numpy(y).to(DEV),
+                                   cm=cm, stats=stats)
+    assert np.array_equal(cm2.cpu().numpy(), 2 * want)
+    assert int(stats2[0]) == 2 * int(scores.sum())
+
+
+def test_confusion_nan_and_foreign_labels(ops):
+    rng = np.random.default_rng(5)
+    n, c = 4096, 7
+    logits = rng.normal(0, 1, (n, c)).astype(np.float32)
+    logits[5, 3] = np.nan
+    logits[6, 2] = np.nan
+    logits[6, 5] = np.nan
+    logits[7, :] = np.inf
+    logits[8, :] = -np.inf
+    y = rng.integers(0, c, n)
+    y[10] = -1
+    y[11] = c
+    y[12] = 10 ** 12
+    cm, stats, am = ops.confusion(torch.from_numpy(logits).to(DEV),
+                                  torch.from_numpy(y).to(DEV), want_argmax=True)
+    assert np.array_equal(am.cpu().numpy(), logits.argmax(axis=1))
+    assert np.array_equal(cm.cpu().numpy(), oracle.confusion_numpy(y, logits))
+    assert int(stats[1]) == 3
+
+
+# ------------------------------------------------------------- probabilities
+def test_sigmoid_bit_equal_to_torch_cuda_all_fp16_codes(ops):
+    codes = torch.arange(65536, dtype=torch.int32).to(torch.int16)
+    x = codes.view(torch.float16).reshape(1, 1, 256, 256).to(DEV)
+    got = ops.seg_prob([x]).cpu().numpy()
+    dev = torch.sigmoid(x.float()).cpu().numpy()
+    same = (got.view(np.int32) == dev.view(np.int32)) | \
+        (np.isnan(got) & np.isnan(dev))
+    assert same.all(), f'{(~same).sum()} fp16 codes differ from torch CUDA'
+    cpu = torch.sigmoid(x.cpu().float()).numpy()
+    fin = np.isfinite(cpu)
+    d = ulp_diff(got[fin], cpu[fin])
+    print(f'\nGPU vs CPU torch.sigmoid over fp16 codes: max {d.max()} ulp, '
+          f'{(d > 0).sum()} of {fin.sum()} differ')
+    assert d.max() <= 2
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.float32])
+@pytest.mark.parametrize('tags', [
+    [[]], [['hflip']], [['vflip']], [['hflip', 'vflip']],
+    [[], ['hflip'], ['vflip'], ['hflip', 'vflip']],
+    [['transpose']], [['transpose', 'hflip']], [['vflip', 'transpose']],
+    [[], ['transpose'], ['hflip', 'transpose', 'vflip']],
+    [[], [], [], [], []],
+])
+@pytest.mark.parametrize('shape', [(2, 3, 16, 24), (1, 2, 35, 53), (2, 1, 8, 7)])
+def test_fused_prob_matches_oracle(ops, dtype, tags, shape):
+    n, c, h, w = shape
+    srcs, _ = synth_seg(n, c, h, w, seed=h * w + len(tags), dtype=dtype,
+                        n_src=len(tags))
+    seen = [forward_tta(s, t) for s, t in zip(srcs, tags)]
+    want = oracle.fuse_probs(seen, tags, 'sigmoid')
+    got = ops.seg_prob([s.to(DEV) for s in seen], xforms=tags).cpu().numpy()
+    assert got.shape == want.shape
+    d = ulp_diff(got, want)
+    # each sigmoid within 1 ulp of the CPU's; a mean of S of them within S
+    assert d.max() <= max(2, len(tags)), d.max()
+    # exact against the same arithmetic done by torch on the device
+    acc = None
+    for s, t in zip(seen, tags):
+        p = oracle.tta_inverse(torch.sigmoid(s.to(DEV).float()), t)
+        acc = p.clone() if acc is None else acc + p
+    dev = (acc / np.float32(len(tags))).cpu().numpy()
+    assert np.array_equal(got.view(np.int32), dev.view(np.int32))
+    # no activation: the mean alone is exact against numpy
+    raw = ops.seg_prob([s.to(DEV) for s in seen], xforms=tags,
+                       activation=None).cpu().numpy()
+    assert np.array_equal(raw, oracle.fuse_probs(seen, tags, None))
+
+
+def test_compose_tta_matches_inverse(ops):
+    import itertools
+    base = torch.arange(3 * 5, dtype=torch.float32).reshape(1, 1, 3, 5)
+    for k in range(0, 4):
+        for tags in itertools.product(oracle.TTA_TAGS, repeat=k):
+            tags = list(tags)
+            seen = forward_tta(base, tags)
+            got = ops.seg_prob([seen.to(DEV)], xforms=[tags], activation=None)
+            assert torch.equal(got.cpu(), base), tags
+
+
+# ----------------------------------------------------------------- histogram
+def check_hist(ops, srcs_seen, tags, gt, thr, use_lut=False):
+    dev_src = [s.to(DEV) for s in srcs_seen]
+    lut = ops.seg_lut(thr) if use_lut else None
+    hist = ops.seg_hist(dev_src, gt.to(DEV), thr, xforms=tags, lut=lut)
+    prob_gpu = ops.seg_prob(dev_src, xforms=tags).cpu().numpy()
+    h = hist.cpu().numpy().astype(np.int64)
+    n, c = gt.shape[:2]
+    # (a) exact w.r.t. the device's own probabilities
+    for i in range(n):
+        for j in range(c):
+            want = oracle.bin_counts(gt[i, j].numpy(), prob_gpu[i, j], thr)
+            assert np.array_equal(h[i, j], want), (i, j)
+    # (b) against the CPU oracle: only threshold-straddling pixels may move
+    prob_cpu = oracle.fuse_probs(srcs_seen, tags, 'sigmoid')
+    moved = 0
+    for i in range(n):
+        for j in range(c):
+            want = oracle.bin_counts(gt[i, j].numpy(), prob_cpu[i, j], thr)
+            if np.array_equal(h[i, j], want):
+                continue
+            cg = np.searchsorted(thr, prob_gpu[i, j].ravel(), side='right')
+            cc = np.searchsorted(thr, prob_cpu[i, j].ravel(), side='right')
+            bad = cg != cc
+            assert (np.abs(cg - cc)[bad] == 1).all()
+            d = ulp_diff(prob_gpu[i, j].ravel()[bad], prob_cpu[i, j].ravel()[bad])
+            assert d.max() <= max(2, len(tags))
+            moved += int(bad.sum())
+            assert np.abs(h[i, j] - want).sum() <= 2 * bad.sum()
+    total = gt.numel()
+    print(f'\nstraddling pixels: {moved} of {total}')
+    assert moved <= max(2, total // 100000)
+    return hist
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.float32])
+@pytest.mark.parametrize('shape,tags', [
+    ((3, 4, 64, 80), [[]]),
+    ((2, 2, 35, 53), [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]),
+    ((2, 1, 33, 41), [[], [], [], [], []]),
+    ((1, 2, 24, 24), [[], ['transpose'], ['hflip', 'transpose']]),
+    ((1, 1, 1, 9), [[]]),
+    ((2, 3, 7, 1), [['vflip']]),
+])
+def test_seg_hist_matches_oracle(ops, dtype, shape, tags):
+    n, c, h, w = shape
+    srcs, gt = synth_seg(n, c, h, w, seed=7 + h + len(tags), dtype=dtype,
+                         n_src=len(tags))
+    seen = [forward_tta(s, t) for s, t in zip(srcs, tags)]
+    check_hist(ops, seen, tags, gt, oracle.threshold_grid(100))
+
+
+def test_seg_hist_edge_values(ops):
+    """Probabilities exactly on thresholds, +-1 ulp, +-inf, NaN, all-empty
+    and all-full ground truth; arbitrary (non-uniform) threshold table."""
+    thr = oracle.threshold_grid(100)
+    vals = []
+    for t in thr:
+        t = np.float32(t)
+        vals += [t, np.nextafter(t, np.float32(2)), np.nextafter(t, np.float32(-1))]
+    vals += [np.float32(np.inf), np.float32(-np.inf), np.float32(np.nan),
+             np.float32(1.0), np.float32(0.0)]
+    p = np.array(vals, np.float32)
+    pad = (-len(p)) % 16
+    p = np.concatenate([p, np.zeros(pad, np.float32)]).reshape(1, 1, -1, 16)
+    p = np.repeat(p, 3, axis=0)
+    gt = np.zeros(p.shape, np.uint8)
+    gt[1] = 1
+    gt[2, :, ::2] = 1
+    for table in (thr, np.array([0.1, 0.1, 0.5, 0.77, 3.0], np.float32),
+                  np.array([0.5], np.float32)):
+        hist = ops.seg_hist([torch.from_numpy(p).to(DEV)],
+                            torch.from_numpy(gt).to(DEV), table,
+                            activation=None).cpu().numpy()
+        for i in range(3):
+            want = oracle.bin_counts(gt[i, 0], p[i, 0], table)
+            assert np.array_equal(hist[i, 0], want)
+
+
+def test_lut_path_equals_generic_on_every_fp16_code(ops):
+    codes = torch.arange(65536, dtype=torch.int32).to(torch.int16)
+    x = codes.view(torch.float16).reshape(2, 2, 128, 128).contiguous().to(DEV)
+    rng = np.random.default_rng(0)
+    gt = torch.from_numpy((rng.random((2, 2, 128, 128)) < 0.3)
+                          .astype(np.uint8)).to(DEV)
+    for thr in (oracle.threshold_grid(100), oracle.threshold_grid(255),
+                np.array([0.5], np.float32)):
+        lut = ops.seg_lut(thr)
+        a = ops.seg_hist([x], gt, thr)
+        b = ops.seg_hist([x], gt, thr, lut=lut)
+        assert torch.equal(a, b)
+        # and the table itself is the binning of the device's sigmoid
+        p = ops.seg_prob([x]).cpu().numpy().ravel()
+        want = np.searchsorted(thr, p, side='right')
+        want[np.isnan(p)] = 0
+        assert np.array_equal(lut.cpu().numpy(), want)
+
+
+def test_lut_path_matches_oracle_and_splits_big_planes(ops):
+    srcs, gt = synth_seg(3, 2, 64, 96, seed=11)
+    thr = oracle.threshold_grid(100)
+    check_hist(ops, srcs, [[]], gt, thr, use_lut=True)
+    # one big plane: exercised the multi-unit (atomic flush) path
+    srcs, gt = synth_seg(1, 1, 1024, 1536, seed=12, empty=0.0)
+    x, g = srcs[0].to(DEV), gt.to(DEV)
+    a = ops.seg_hist([x], g, thr, lut=ops.seg_lut(thr))
+    b = ops.seg_hist([x], g, thr)
+    assert torch.equal(a, b)
+    p = ops.seg_prob([x]).cpu().numpy()
+    assert np.array_equal(a.cpu().numpy()[0, 0],
+                          oracle.bin_counts(gt[0, 0].numpy(), p[0, 0], thr))
+
+
+# ---------------------------------------------------------------- dice grid
+def test_dice_search_matches_dice_numpy_loop(ops):
+    n, c, h, w = 5, 3, 24, 40
+    srcs, gt = synth_seg(n, c, h, w, seed=21, empty=0.5)
+    thr = oracle.threshold_grid(100)
+    areas = np.array([[0, 5, 50, 400, 2000]] * c)
+    areas[1] = [0, 1, 2, 3, 10 ** 6]
+    hist = ops.seg_hist([srcs[0].to(DEV)], gt.to(DEV), thr)
+    prob = ops.seg_prob([srcs[0].to(DEV)]).cpu().numpy()
+    dsum, micro = ops.dice_search(hist, areas)
+    table = np.stack([oracle.dice_grid_slow(gt.numpy()[:, j:j + 1].astype(np.float32),
+                                            prob[:, j:j + 1], thr, areas[j])
+                      for j in range(c)], axis=1)[:, :, 0]
+    want = table.sum(axis=0)                      # [c, B, A]
+    got = dsum.cpu().numpy()
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=0)   # north_star tolerance
+    np.testing.assert_allclose(got, want, rtol=1e-13, atol=0)  # what we see
+    tt, pp, ii = oracle.micro_stats(gt.numpy(), prob, thr)
+    m = micro.cpu().numpy()
+    assert np.array_equal(m[:, 0], tt)
+    assert np.array_equal(m[:, 1:1 + len(thr)], pp)
+    assert np.array_equal(m[:, 1 + len(thr):], ii)
+    # per-plane dice at a chosen point per class is bit-equal to dice_numpy
+    ks = [50, 17, 80]
+    ars = [0, 3, 400]
+    per = ops.plane_dice(hist, ks, ars).cpu().numpy()
+    for i in range(n):
+        for j in range(c):
+            ref = oracle.plane_dice(gt.numpy()[i, j].astype(np.float32),
+                                    prob[i, j], np.float32(thr[ks[j]]), ars[j])
+            assert per[i, j] == float(ref)
+    # empty_one=False, other eps
+    d2, _ = ops.dice_search(hist, [0, 7], empty_one=False, eps=1e-3)
+    t2 = oracle.dice_grid_fast(gt.numpy(), prob, thr, [0, 7], False, 1e-3)
+    np.testing.assert_allclose(d2.cpu().numpy(), t2.sum(axis=0), rtol=1e-13)
+
+
+def test_dice_search_many_images_is_reproducible(ops):
+    n, c = 700, 4
+    rng = np.random.default_rng(1)
+    hist = rng.integers(0, 50, (n, c, 2, 101)).astype(np.int32)
+    hist[::3, :, 1, :] = 0          # empty targets
+    hist[::6, :, :, 1:] = 0         # nothing predicted above thr[0]
+    h = torch.from_numpy(hist).to(DEV)
+    a, m1 = ops.dice_search(h, [0, 100, 2000])
+    b, m2 = ops.dice_search(h, [0, 100, 2000])
+    assert torch.equal(a, b) and torch.equal(m1, m2)
+    tot = hist.astype(np.int64).sum(axis=2)
+    pos = hist[:, :, 1].astype(np.int64)
+    P = tot[..., ::-1].cumsum(-1)[..., ::-1][..., 1:]
+    I = pos[..., ::-1].cumsum(-1)[..., ::-1][..., 1:]
+    T = pos.sum(-1)
+    want = np.zeros((c, 100, 3))
+    for i in range(n):
+        for j in range(c):
+            for k, ar in enumerate([0, 100, 2000]):
+                want[j, :, k] += oracle.dice_from_counts(T[i, j], P[i, j],
+                                                         I[i, j], ar)
+    np.testing.assert_allclose(a.cpu().numpy(), want, rtol=1e-12)
+
+
+# ---------------------------------------------------------------------- rle
+@pytest.mark.parametrize('dtype', [torch.float16, torch.float32])
+@pytest.mark.parametrize('shape,tags', [
+    ((3, 2, 64, 96), [[]]),
+    ((2, 2, 35, 53), [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]),
+    ((1, 1, 256, 320), [[]]),
+    ((2, 1, 33, 300), [[]]),
+    ((2, 3, 1, 40), [[]]),
+    ((2, 3, 40, 1), [[]]),
+])
+def test_rle_matches_mask2rle(ops, dtype, shape, tags):
+    n, c, h, w = shape
+    srcs, _ = synth_seg(n, c, h, w, seed=31 + h, dtype=dtype, n_src=len(tags),
+                        empty=0.3)
+    seen = [forward_tta(s, t) for s, t in zip(srcs, tags)]
+    dev_src = [s.to(DEV) for s in seen]
+    thr = np.linspace(0.3, 0.7, c).astype(np.float32)
+    areas = np.array([0, 30, 10 ** 6][:c] + [0] * max(0, c - 3), np.int32)[:c]
+    runs, off, cnt, area = ops.rle_encode(dev_src, thr, areas, xforms=tags)
+    got = ops.rle_strings(runs, off, cnt)
+    prob = ops.seg_prob(dev_src, xforms=tags).cpu().numpy()
+    k = 0
+    for i in range(n):
+        for j in range(c):
+            want = oracle.rle_submission(prob[i, j], thr[j], int(areas[j]))
+            assert got[k] == want, (i, j)
+            assert int(area[i, j]) == int((prob[i, j] >= thr[j]).sum())
+            k += 1
+
+
+def test_rle_edge_masks_and_retry(ops):
+    rng = np.random.default_rng(9)
+    h, w = 70, 45
+    masks = [np.zeros((h, w), np.uint8), np.ones((h, w), np.uint8),
+             (rng.random((h, w)) < 0.5).astype(np.uint8)]
+    m = np.zeros((h, w), np.uint8)
+    m[h // 2:, :] = 1
+    m[0, 1:] = 1                                  # runs spanning column ends
+    masks.append(m)
+    m = np.zeros((h, w), np.uint8)
+    m[-1, :] = 1
+    m[0, :] = 1                                   # end of col joins next col
+    masks.append(m)
+    x = torch.from_numpy(np.stack(masks)[:, None]).to(DEV)
+    # capacity=2 forces the overflow + retry path
+    runs, off, cnt, area = ops.rle_encode([x], 0.5, 0, activation=None,
+                                          capacity=2)
+    got = ops.rle_strings(runs, off, cnt)
+    for s, mk in zip(got, masks):
+        assert s == oracle.rle_encode(mk)
+        assert np.array_equal(oracle.rle_decode(s, (w, h)), mk)
+    assert got[0] == '' and got[1] == f'1 {h * w}'
+
+
+def test_errors_are_loud(ops):
+    from mlcomp_b200._lib import MlcError
+    x = torch.zeros(1, 1, 8, 8, dtype=torch.float16, device=DEV)
+    g = torch.zeros(1, 1, 8, 8, dtype=torch.uint8, device=DEV)
+    with pytest.raises(MlcError, match='ascending'):
+        ops.seg_hist([x], g, [0.5, 0.4])
+    with pytest.raises(Exception, match='unknown activation'):
+        ops.seg_hist([x], g, [0.5], activation='relu')
+    with pytest.raises(Exception, match='Unknwon augmentation'):
+        ops.seg_prob([x], xforms=[['rot90']])
+    with pytest.raises(TypeError, match='CUDA tensor'):
+        ops.seg_prob([x.cpu()])
