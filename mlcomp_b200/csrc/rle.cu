@@ -138,7 +138,9 @@ rle_kernel(const __grid_constant__ RleArgs a) {
         uint32_t starts = w & ~((w << 1) | prev);
         uint32_t ends = w & ~((w >> 1) | (next << top));
         const int pos0 = x * H + yb * 32 + 1;  // 1-based, column-major
-        int ei = si - (int)prev;
+        // ends before this word = starts before it, minus the run (if any)
+        // that is still open across the word boundary
+        int ei = si - (int)(prev & w & 1u);
         while (starts) {
           const int b = __ffs(starts) - 1;
           starts &= starts - 1;

@@ -1,0 +1,184 @@
+"""Dataset-level scoring on top of the kernels: the loops the reference's
+(missing) ``Valid`` / ``Infer`` executors ran around ``dice_numpy`` and
+``mask2rle``, kept on the device.
+
+``SegSearch``   threshold x min-area dice search over a validation set that is
+                fed chunk by chunk (device tensors, or pinned host buffers
+                with copies overlapped against compute), optionally sharded
+                over ranks and combined with one small all-reduce.
+``ClassifyScore`` arg-max, confusion matrix, accuracy (config 1).
+"""
+import numpy as np
+import torch
+
+from . import ops
+
+__all__ = ['SegSearch', 'ClassifyScore', 'shard_range']
+
+
+def shard_range(n, rank, world):
+    """Contiguous image range of ``rank``: [lo, hi)."""
+    return (n * rank) // world, (n * (rank + 1)) // world
+
+
+class SegSearch:
+    """Accumulates sum_i dice(i, c, t, a) and the global integer counts.
+
+    score[c, t, a] = mean over images of dice_numpy(gt, prob, thr[t], area[a])
+    (contrib/metrics/dice.py:4-23, empty_one rule per plane); best point per
+    class = first arg-max over (t, a).
+    """
+
+    def __init__(self, n_cls, thr=None, min_areas=(0,), activation='sigmoid',
+                 empty_one=True, eps=1e-6, device='cuda', use_lut=True):
+        self.n_cls = int(n_cls)
+        self.thr = ops.threshold_grid(100) if thr is None else \
+            np.asarray(thr, dtype=np.float32)
+        areas = np.asarray(min_areas, dtype=np.int64)
+        if areas.ndim == 1:
+            areas = np.broadcast_to(areas, (self.n_cls, areas.shape[0]))
+        self.min_areas = np.ascontiguousarray(areas)
+        self.activation = activation
+        self.empty_one = empty_one
+        self.eps = eps
+        self.device = torch.device(device)
+        self.lut = ops.seg_lut(self.thr, activation, self.device) \
+            if use_lut else None
+        b, a = len(self.thr), self.min_areas.shape[1]
+        self.dice_sum = torch.zeros((self.n_cls, b, a), dtype=torch.float64,
+                                    device=self.device)
+        self.micro = torch.zeros((self.n_cls, 1 + 2 * b), dtype=torch.int64,
+                                 device=self.device)
+        self.n_img = 0
+        self._copy_stream = None
+        self._stage = None
+
+    # -- device-resident chunk ------------------------------------------------
+    def add(self, sources, gt, xforms=None):
+        """Score one chunk already in HBM; returns its histograms
+        [n, C, 2, B+1] (int32) for per-image reporting."""
+        hist = ops.seg_hist(sources, gt, self.thr, xforms=xforms,
+                            activation=self.activation, lut=self.lut)
+        dsum, micro = ops.dice_search(hist, self.min_areas, self.empty_one,
+                                      self.eps)
+        self.dice_sum += dsum
+        self.micro += micro
+        self.n_img += hist.shape[0]
+        return hist
+
+    # -- host-resident chunks: copies overlapped with compute -----------------
+    def add_host(self, sources, gt, xforms=None, chunk=64):
+        """Score host tensors (pinned for full speed).  The set is cut into
+        chunks of ``chunk`` images; chunk i+1 is copied on a side stream
+        while chunk i is scored, through two staging buffers per input."""
+        if isinstance(sources, torch.Tensor):
+            sources = [sources]
+        n = gt.shape[0]
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        key = (len(sources), tuple(sources[0].shape[1:]), sources[0].dtype,
+               tuple(gt.shape[1:]), chunk)
+        if self._stage is None or self._stage[0] != key:
+            bufs = []
+            for _ in range(2):
+                s = [torch.empty((chunk,) + tuple(x.shape[1:]), dtype=x.dtype,
+                                 device=self.device) for x in sources]
+                g = torch.empty((chunk,) + tuple(gt.shape[1:]),
+                                dtype=torch.uint8, device=self.device)
+                bufs.append((s, g, torch.cuda.Event(), torch.cuda.Event()))
+            self._stage = (key, bufs)
+        bufs = self._stage[1]
+        main = torch.cuda.current_stream(self.device)
+        for idx, lo in enumerate(range(0, n, chunk)):
+            hi = min(n, lo + chunk)
+            s_buf, g_buf, copied, consumed = bufs[idx & 1]
+            with torch.cuda.stream(self._copy_stream):
+                if idx >= 2:
+                    self._copy_stream.wait_event(consumed)
+                for d, x in zip(s_buf, sources):
+                    d[:hi - lo].copy_(x[lo:hi], non_blocking=True)
+                g_buf[:hi - lo].copy_(gt[lo:hi], non_blocking=True)
+                copied.record(self._copy_stream)
+            main.wait_event(copied)
+            self.add([d[:hi - lo] for d in s_buf], g_buf[:hi - lo], xforms)
+            consumed.record(main)
+
+    # -- combine + search -------------------------------------------------------
+    def result(self, group=None):
+        """Combine ranks (if torch.distributed is initialised / ``group``
+        given) and search the grid.  Integer counts: one all_reduce(SUM),
+        exact.  fp64 dice sums: all_gather then summed in rank order on every
+        rank, so all ranks (and reruns) get bit-identical scores."""
+        import torch.distributed as dist
+        dice_sum, micro, n_img = self.dice_sum, self.micro, self.n_img
+        if dist.is_available() and dist.is_initialized() and \
+                dist.get_world_size(group) > 1:
+            world = dist.get_world_size(group)
+            ints = torch.cat([micro.reshape(-1),
+                              torch.tensor([n_img], dtype=torch.int64,
+                                           device=micro.device)])
+            dist.all_reduce(ints, op=dist.ReduceOp.SUM, group=group)
+            micro = ints[:-1].reshape(micro.shape)
+            n_img = int(ints[-1].item())
+            parts = [torch.empty_like(dice_sum) for _ in range(world)]
+            dist.all_gather(parts, dice_sum, group=group)
+            dice_sum = parts[0].clone()
+            for p in parts[1:]:
+                dice_sum += p
+        score = (dice_sum / max(n_img, 1)).cpu().numpy()      # [C, B, A]
+        m = micro.cpu().numpy()
+        b = len(self.thr)
+        t_sum, p_sum, i_sum = m[:, 0], m[:, 1:1 + b], m[:, 1 + b:]
+        best = []
+        for c in range(self.n_cls):
+            k, a = divmod(int(np.argmax(score[c])), score.shape[2])
+            best.append({'class': c, 'threshold_index': k,
+                         'threshold': float(self.thr[k]),
+                         'min_area': int(self.min_areas[c, a]),
+                         'dice': float(score[c, k, a])})
+        union = t_sum[:, None] + p_sum
+        return {
+            'n_img': int(n_img),
+            'score': score,
+            'best': best,
+            'dice': float(np.mean([r['dice'] for r in best])),
+            'micro_T': t_sum, 'micro_P': p_sum, 'micro_I': i_sum,
+            'micro_dice': 2.0 * i_sum / (union + self.eps),
+            # IoU is not in the reference: self-consistent only
+            'micro_iou': i_sum / (union - i_sum + self.eps),
+        }
+
+
+class ClassifyScore:
+    """argmax + confusion matrix + accuracy over chunks (config 1):
+    worker/reports/classification.py:133-138 and
+    examples/digit-recognizer/executors/valid.py:45-52."""
+
+    def __init__(self, n_cls, device='cuda'):
+        self.n_cls = int(n_cls)
+        self.device = torch.device(device)
+        self.cm = torch.zeros((n_cls, n_cls), dtype=torch.int64,
+                              device=self.device)
+        self.stats = torch.zeros(2, dtype=torch.int64, device=self.device)
+        self.n = 0
+
+    def add(self, preds, labels, want_argmax=False):
+        _, _, am = ops.confusion(preds, labels, cm=self.cm, stats=self.stats,
+                                 want_argmax=want_argmax)
+        self.n += preds.shape[0]
+        return am
+
+    def result(self, group=None):
+        import torch.distributed as dist
+        ints = torch.cat([self.cm.reshape(-1), self.stats,
+                          torch.tensor([self.n], dtype=torch.int64,
+                                       device=self.device)])
+        if dist.is_available() and dist.is_initialized() and \
+                dist.get_world_size(group) > 1:
+            dist.all_reduce(ints, op=dist.ReduceOp.SUM, group=group)
+        h = ints.cpu().numpy()
+        c = self.n_cls
+        cm = h[:c * c].reshape(c, c)
+        correct, dropped, n = int(h[c * c]), int(h[c * c + 1]), int(h[-1])
+        return {'confusion': cm, 'correct': correct, 'dropped': dropped,
+                'n': n, 'accuracy': correct / n if n else float('nan')}
