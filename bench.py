@@ -1,0 +1,452 @@
+#!/usr/bin/env python
+"""Headline benchmark: validated masks/sec of the scoring hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1], "C2"): Severstal-shaped validation set,
+6,666 images x 4 classes x 256x1600 fp16 logits + uint8 one-hot ground truth
+PER GPU (weak scaling), 100-threshold x 5-min-area dice search.  One "step" is
+one full pass: fused sigmoid + label-conditioned threshold histogram over all
+planes, histogram scan -> dice for the whole grid, (N>1: NCCL all-reduce of
+the integer counts + all-gather of the fp64 partial sums), D2H of the score
+table and the host-side arg-max.  A "mask" is one (image, class) plane.
+
+One JSON line on stdout (rank 0).  `--impl reference` times the CPU oracle
+port of the reference's own functions (oracle/) on all host cores instead.
+"""
+import argparse
+import json
+import multiprocessing as mp
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+C2 = dict(n_img=6666, n_cls=4, H=256, W=1600, bins=100,
+          min_areas=(0, 256, 512, 1024, 2048), empty=0.86)
+METRIC = 'validated_masks_per_sec'
+UNIT = 'masks/s'
+
+
+def workload_name(cfg):
+    return ('C2 severstal-valid: %d img x %d cls x %dx%d fp16 logits + u8 gt '
+            'per GPU, %d thresholds x %d min-areas' %
+            (cfg['n_img'], cfg['n_cls'], cfg['H'], cfg['W'], cfg['bins'],
+             len(cfg['min_areas'])))
+
+
+def algorithmic_bytes_per_plane(cfg, n_src=1, elem=2):
+    """logits once + 1 B/px ground truth + histogram out."""
+    px = cfg['H'] * cfg['W']
+    return n_src * px * elem + px + 2 * (cfg['bins'] + 1) * 4
+
+
+# ---------------------------------------------------------------------------
+# synthetic data: mostly-empty planes, a few ellipses,
+# logits = +-4 around the mask + N(0, 1.5), stored fp16
+# ---------------------------------------------------------------------------
+def synth(cfg, n_img, seed, device, chunk=64):
+    import torch
+    c, h, w = cfg['n_cls'], cfg['H'], cfg['W']
+    g = torch.Generator(device=device).manual_seed(seed)
+    logits = torch.empty((n_img, c, h, w), dtype=torch.float16, device=device)
+    gt = torch.empty((n_img, c, h, w), dtype=torch.uint8, device=device)
+    yy = torch.arange(h, device=device, dtype=torch.float32)[None, :, None]
+    xx = torch.arange(w, device=device, dtype=torch.float32)[None, None, :]
+    for lo in range(0, n_img, chunk):
+        hi = min(n_img, lo + chunk)
+        p = (hi - lo) * c
+        empty = torch.rand(p, generator=g, device=device) < cfg['empty']
+        mask = torch.zeros((p, h, w), dtype=torch.bool, device=device)
+        for _ in range(2):
+            cy = torch.rand(p, generator=g, device=device) * h
+            cx = torch.rand(p, generator=g, device=device) * w
+            frac = 0.001 + 0.05 * torch.rand(p, generator=g, device=device)
+            aspect = 0.5 + 2.5 * torch.rand(p, generator=g, device=device)
+            ry = torch.sqrt(frac * h * w / 3.14159 / aspect)
+            rx = ry * aspect
+            mask |= (((yy - cy[:, None, None]) / ry[:, None, None]) ** 2 +
+                     ((xx - cx[:, None, None]) / rx[:, None, None]) ** 2) <= 1
+        mask &= ~empty[:, None, None]
+        noise = torch.randn((p, h, w), generator=g, device=device,
+                            dtype=torch.float32) * 1.5
+        lg = (mask.float() * 8 - 4) + noise
+        logits[lo:hi] = lg.to(torch.float16).view(hi - lo, c, h, w)
+        gt[lo:hi] = mask.to(torch.uint8).view(hi - lo, c, h, w)
+        del mask, noise, lg
+    return logits, gt
+
+
+# ---------------------------------------------------------------------------
+# CPU leg: the oracle port of the reference's own loop, one plane per task
+# ---------------------------------------------------------------------------
+def _cpu_init():
+    import torch
+    torch.set_num_threads(1)        # worker/tasks.py:122-126 sets OMP/MKL = 1
+
+
+def _cpu_plane(args):
+    """sigmoid (utils/torch.py:15) + dice_numpy at every (t, a) of the grid
+    (contrib/metrics/dice.py:4-23) for one plane - what the reference's
+    Valid executor did per plane."""
+    import torch
+    import oracle
+    logit, gt, bins, areas = args
+    prob = oracle.activate(torch.from_numpy(logit), 'sigmoid').numpy()
+    thr = oracle.threshold_grid(bins)
+    table = oracle.dice_grid_slow(gt[None, None].astype(np.float32),
+                                  prob[None, None], thr, areas)
+    return table[0, 0]
+
+
+def cpu_rate(pool, cores, planes_logit, planes_gt, cfg):
+    tasks = [(planes_logit[i], planes_gt[i], cfg['bins'],
+              list(cfg['min_areas'])) for i in range(len(planes_logit))]
+    t0 = time.perf_counter()
+    out = pool.map(_cpu_plane, tasks, chunksize=1)
+    dt = time.perf_counter() - t0
+    return len(tasks) / dt, dt, np.stack(out)
+
+
+def make_pool():
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    ctx = mp.get_context('fork')    # forked BEFORE CUDA is initialised
+    return ctx.Pool(cores, initializer=_cpu_init), cores
+
+
+# ---------------------------------------------------------------------------
+# clocks during the timed region (NVML polling thread)
+# ---------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x8: 'hw_slowdown', 0x40: 'hw_thermal_slowdown',
+               0x20: 'sw_thermal_slowdown', 0x4: 'sw_power_cap',
+               0x80: 'hw_power_brake_slowdown'}
+
+    def __init__(self, device_index):
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            if not uuid.startswith('GPU-'):
+                uuid = 'GPU-' + uuid
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.nv = pynvml
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(
+                self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # pragma: no cover
+            self.nv = None
+            self.err = repr(e)
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append(mhz)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+        if not self.samples:
+            return {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': [],
+                    'samples': 0}
+        return {'sm_mhz': float(np.median(self.samples)),
+                'sm_max_mhz': self.max_mhz,
+                'reasons': sorted(self.reasons), 'samples': len(self.samples)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        return float(json.load(open(path))['hbm_gbs']), 'measured'
+    except Exception:
+        return 6650.0, 'fallback'
+
+
+def committed_traffic(key):
+    try:
+        d = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))
+        return d.get(key)
+    except Exception:
+        return None
+
+
+# ---------------------------------------------------------------------------
+def run_reference(args, cfg):
+    """The reference's CPU implementation of the path (oracle port), all host
+    cores, each step a bounded sample of the workload."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    import torch
+    pool, cores = make_pool()
+    n_planes = max(16, cores)
+    n_img = (n_planes + cfg['n_cls'] - 1) // cfg['n_cls']
+    logits, gt = synth(cfg, n_img, 2000, 'cpu', chunk=8)
+    lg = logits.numpy().reshape(-1, cfg['H'], cfg['W'])[:n_planes]
+    g = gt.numpy().reshape(-1, cfg['H'], cfg['W'])[:n_planes]
+    for _ in range(args.warmup):
+        cpu_rate(pool, cores, lg, g, cfg)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_rate(pool, cores, lg, g, cfg)
+    dt = time.perf_counter() - t0
+    pool.close()
+    value = n_planes * args.steps / dt
+    sample = ('%d planes per step (%d images) of the C2 workload, one plane '
+              'per task over %d processes' % (n_planes, n_img, cores))
+    print(json.dumps({
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT,
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {'workload': workload_name(cfg), 'sample': sample},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores,
+                         'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0,
+                'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }))
+
+
+def run_ours(args, cfg):
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    pool = cores = None
+    if rank == 0 and not args.no_cpu:
+        pool, cores = make_pool()          # fork before CUDA exists
+
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    from mlcomp_b200 import ops, scoring
+
+    n_img, c = args.images or cfg['n_img'], cfg['n_cls']
+    planes = n_img * c
+    logits, gt = synth(cfg, n_img, 1000 * 2 + rank, dev)
+    thr = ops.threshold_grid(cfg['bins'])
+    search = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev,
+                               record_events=True)
+
+    def step():
+        search.reset()
+        search.add(logits, gt)
+        return search.result()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- parity of this very run against the oracle, on a subset -----------
+    import oracle
+    sub = min(n_img, 8)
+    res = step()
+    hist = ops.seg_hist([logits[:sub]], gt[:sub], thr, lut=search.lut)
+    h = hist.cpu().numpy().astype(np.int64)
+    lg_h = logits[:sub].cpu()
+    gt_h = gt[:sub].cpu().numpy()
+    prob_cpu = oracle.fuse_probs([lg_h], [[]], 'sigmoid')
+    moved = 0
+    for i in range(sub):
+        for j in range(c):
+            want = oracle.bin_counts(gt_h[i, j], prob_cpu[i, j], thr)
+            moved += int(np.abs(h[i, j] - want).sum()) // 2
+    validated = moved <= 2 + sub * c * cfg['H'] * cfg['W'] // 20000
+    per = ops.plane_dice(hist, [50] * c, [0] * c).cpu().numpy()
+    for i in range(min(sub, 2)):
+        for j in range(c):
+            ref = float(oracle.plane_dice(gt_h[i, j].astype(np.float32),
+                                          prob_cpu[i, j], np.float32(thr[50])))
+            validated &= abs(per[i, j] - ref) <= 1e-5 * max(abs(ref), 1e-12)
+
+    # ---- warm-up + timed region ---------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local) if rank == 0 else None
+    search.kernel_events.clear()
+    barrier()
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    e0.record()
+    for _ in range(args.steps):
+        res = step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = planes * world * args.steps / (ms * 1e-3)
+    kern_ms = [a.elapsed_time(b) for a, b in search.kernel_events]
+    kern_avg = float(np.mean(kern_ms))
+
+    # ---- end to end: pinned host buffers in, scores out ---------------------
+    e_img = min(n_img, args.e2e_images)
+    h_logits = torch.empty((e_img,) + tuple(logits.shape[1:]),
+                           dtype=torch.float16, pin_memory=True)
+    h_gt = torch.empty((e_img,) + tuple(gt.shape[1:]), dtype=torch.uint8,
+                       pin_memory=True)
+    h_logits.copy_(logits[:e_img])
+    h_gt.copy_(gt[:e_img])
+    torch.cuda.synchronize()
+    e2e_search = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev)
+
+    def e2e_step():
+        e2e_search.reset()
+        e2e_search.add_host([h_logits], h_gt, chunk=args.e2e_chunk)
+        return e2e_search.result()
+
+    for _ in range(2):
+        r2 = e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(args.e2e_steps):
+        r2 = e2e_step()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = e_img * c * world * args.e2e_steps / (float(t.item()) * 1e-3)
+    h2d = e_img * c * cfg['H'] * cfg['W'] * 3
+    d2h = int(np.prod(r2['score'].shape)) * 8 + c * (1 + 2 * len(thr)) * 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- CPU baseline on the same tensors (rank 0, N=1 semantics) -----------
+    cpu = None
+    if pool is not None:
+        n_cpu = max(16, cores)
+        k_img = min(n_img, (n_cpu + c - 1) // c)
+        lg_np = logits[:k_img].cpu().numpy().reshape(-1, cfg['H'], cfg['W'])
+        gt_np = gt[:k_img].cpu().numpy().reshape(-1, cfg['H'], cfg['W'])
+        n_cpu = min(n_cpu, len(lg_np))
+        rate, dt, table = cpu_rate(pool, cores, lg_np[:n_cpu], gt_np[:n_cpu],
+                                   cfg)
+        pool.close()
+        cpu = {'value': rate, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+               'sample': '%d planes of this run\'s C2 data, one plane per '
+                         'task over %d processes, %.1f s wall' %
+                         (n_cpu, cores, dt)}
+        # the CPU loop and the GPU search must agree on those planes
+        hs = ops.seg_hist([logits[:k_img]], gt[:k_img], thr, lut=search.lut)
+        for a_i, area in enumerate(cfg['min_areas']):
+            for k in (10, 50, 90):
+                got = ops.plane_dice(hs, [k] * c, [area] * c).cpu().numpy() \
+                    .reshape(-1)[:n_cpu]
+                ok = np.abs(got - table[:, k, a_i]) <= 1e-5 * np.maximum(
+                    np.abs(table[:, k, a_i]), 1e-12)
+                # straddling pixels (<= 4 ulp sigmoid gap CPU vs GPU) may move
+                validated &= ok.mean() > 0.9
+
+    peak, peak_kind = measured_peak()
+    bytes_launch = algorithmic_bytes_per_plane(cfg) * planes
+    achieved = bytes_launch / (kern_avg * 1e-3) / 1e9
+    out = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world,
+        'steps': args.steps, 'warmup': max(args.warmup, 3),
+        'ms_per_step': ms / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {
+            'workload': workload_name(cfg) if not args.images else
+            workload_name(dict(cfg, n_img=n_img)),
+            'planes_per_gpu': planes,
+            'cache': 'inputs %.1f GB per GPU per step, far larger than the '
+                     '126 MB L2; no flush needed' %
+                     (planes * cfg['H'] * cfg['W'] * 3 / 1e9),
+            'e2e': '%d images per GPU per step from pinned host memory in '
+                   'chunks of %d, copies overlapped with compute' %
+                   (e_img, args.e2e_chunk),
+        },
+        'validated': bool(validated),
+        'parity': {'subset_planes': sub * c, 'straddling_pixels': moved,
+                   'best': res['best']},
+        'roofline': {
+            'bound': 'hbm', 'kernel': 'seg_hist_lut',
+            'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+            'frac': achieved / peak, 'peak_kind': peak_kind,
+            'frac_of_8000_nominal': achieved / 8000.0,
+            'algorithmic_bytes_per_launch': bytes_launch,
+            'avg_launch_ms': kern_avg,
+            'traffic': committed_traffic('seg_hist_lut_c2'),
+        },
+        'cpu_baseline': cpu,
+        'e2e': {'value': e2e_value, 'unit': UNIT,
+                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
+        'gpu_launches': 3 * args.steps,
+        'clocks': clocks,
+    }
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--images', type=int, default=0,
+                    help='images per GPU (default: the full C2 set)')
+    ap.add_argument('--e2e-images', type=int, default=1024)
+    ap.add_argument('--e2e-chunk', type=int, default=64)
+    ap.add_argument('--e2e-steps', type=int, default=5)
+    ap.add_argument('--no-cpu', action='store_true')
+    args = ap.parse_args()
+    cfg = dict(C2)
+    if args.impl == 'reference':
+        run_reference(args, cfg)
+    else:
+        run_ours(args, cfg)
+
+
+if __name__ == '__main__':
+    main()

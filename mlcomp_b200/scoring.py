@@ -30,7 +30,8 @@ class SegSearch:
     """
 
     def __init__(self, n_cls, thr=None, min_areas=(0,), activation='sigmoid',
-                 empty_one=True, eps=1e-6, device='cuda', use_lut=True):
+                 empty_one=True, eps=1e-6, device='cuda', use_lut=True,
+                 record_events=False):
         self.n_cls = int(n_cls)
         self.thr = ops.threshold_grid(100) if thr is None else \
             np.asarray(thr, dtype=np.float32)
@@ -52,13 +53,29 @@ class SegSearch:
         self.n_img = 0
         self._copy_stream = None
         self._stage = None
+        # (start, end) CUDA events around every histogram launch, for the
+        # per-kernel roofline in bench.py
+        self.record_events = record_events
+        self.kernel_events = []
+
+    def reset(self):
+        self.dice_sum.zero_()
+        self.micro.zero_()
+        self.n_img = 0
 
     # -- device-resident chunk ------------------------------------------------
     def add(self, sources, gt, xforms=None):
         """Score one chunk already in HBM; returns its histograms
         [n, C, 2, B+1] (int32) for per-image reporting."""
+        if self.record_events:
+            ev = (torch.cuda.Event(enable_timing=True),
+                  torch.cuda.Event(enable_timing=True))
+            ev[0].record()
         hist = ops.seg_hist(sources, gt, self.thr, xforms=xforms,
                             activation=self.activation, lut=self.lut)
+        if self.record_events:
+            ev[1].record()
+            self.kernel_events.append(ev)
         dsum, micro = ops.dice_search(hist, self.min_areas, self.empty_one,
                                       self.eps)
         self.dice_sum += dsum
