@@ -132,6 +132,32 @@ int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img, int n_cls,
                     int64_t *micro_dev, void *work_dev, size_t work_bytes,
                     void *stream);
 
+/* mlc_dice_search without a workspace argument, for callers that cannot
+ * allocate device memory: a scoring loop sharing the GPU with an inference
+ * engine that reserved the whole card at start-up, or a thin ctypes binding
+ * from the reference's worker that is handed its input/output buffers and has
+ * no device allocator of its own.  (No counterpart in the reference: it is an
+ * addition of this library, same arithmetic and same results as
+ * mlc_dice_search.)
+ *  - The scratch is a 4 MiB array built into the library image; every GPU
+ *    that loads the library holds it until the process exits.
+ *  - Limit: mlc_dice_search_workspace(n_img, n_cls, n_thr, n_area) must be
+ *    <= 4 MiB (4 194 304 bytes); for a large image count that means about
+ *    n_thr * n_area <= 880 (the C2 grid, 100 thresholds x 5 areas over 4
+ *    classes, needs 2.4 MB).  Larger searches return MLC_ERR_CAPACITY and
+ *    must use mlc_dice_search.
+ *  - The first call on each device looks up the array's device address
+ *    (cudaGetSymbolAddress) before enqueueing work; make that first call
+ *    outside any stream capture.  No call allocates or frees anything.
+ *  - All calls on a device share the one array, and it keeps the previous
+ *    call's partial sums (each call overwrites what it reads, nothing needs
+ *    clearing).  Two calls whose kernels can overlap on the GPU (different
+ *    streams, different host threads) race on it: serialise them. */
+int mlc_dice_search_static(const uint32_t *hist_dev, int64_t n_img, int n_cls,
+                           int n_thr, const int32_t *min_area_host, int n_area,
+                           int empty_one, double eps, double *dice_sum_dev,
+                           int64_t *micro_dev, void *stream);
+
 /* Per-plane dice at one chosen (threshold index, min_area) per class:
  * dice_dev [n_img*n_cls] fp64 (the per-image `scores` the report builders
  * take, worker/reports/segmenation.py:148-150). */

@@ -265,3 +265,74 @@ extern "C" int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img,
   MLC_LAUNCH_CHECK("plane_dice_kernel");
   return MLC_OK;
 }
+
+// ---------------------------------------------------------------------------
+// mlc_dice_search_static: the same search for callers that own no workspace.
+//
+// mlc_dice_search needs a scratch buffer for its per-chunk partial sums and
+// expects the caller to allocate it.  Two kinds of caller of this library
+// cannot: a scoring loop that runs beside an inference engine whose memory
+// pool was sized to the whole card at start-up (any later cudaMalloc fails or
+// is forbidden by the deployment), and a thin binding from the reference's
+// worker process (ctypes + NumPy), which receives its input
+// and output buffers from somebody else and has no device allocator at all.
+// For them the scratch is this fixed array inside the library image: every
+// GPU that loads libmlcomp_b200.so carries these 4 MiB until the process
+// exits, whether or not the entry point is ever called.
+//
+// The array's name is only meaningful to device code; host code must not
+// pass it to a kernel.  The device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and cached.
+// ---------------------------------------------------------------------------
+namespace mlc {
+constexpr size_t kStaticPartialDoubles = 512 * 1024;  // 4 MiB
+static __device__ __align__(256) double g_dice_partials[kStaticPartialDoubles];
+
+// Device address of g_dice_partials on the CURRENT device, or nullptr with
+// *err set.  First use on a device performs the symbol look-up.
+static double *static_partials(cudaError_t *err) {
+  static double *cache[64] = {nullptr};
+  int dev = 0;
+  *err = cudaGetDevice(&dev);
+  if (*err != cudaSuccess) return nullptr;
+  if (dev < 0 || dev >= 64) {
+    *err = cudaErrorInvalidDevice;
+    return nullptr;
+  }
+  if (cache[dev] == nullptr) {
+    void *p = nullptr;
+    *err = cudaGetSymbolAddress(&p, g_dice_partials);
+    if (*err != cudaSuccess) return nullptr;
+    cache[dev] = static_cast<double *>(p);
+  }
+  return cache[dev];
+}
+}  // namespace mlc
+
+extern "C" int mlc_dice_search_static(const uint32_t *hist_dev, int64_t n_img,
+                                      int n_cls, int n_thr,
+                                      const int32_t *min_area_host, int n_area,
+                                      int empty_one, double eps,
+                                      double *dice_sum_dev, int64_t *micro_dev,
+                                      void *stream) {
+  const size_t cap = kStaticPartialDoubles * sizeof(double);
+  // shape errors are reported by mlc_dice_search below; here only the size
+  const size_t need = mlc_dice_search_workspace(n_img, n_cls, n_thr, n_area);
+  if (need > cap) {
+    set_error("mlc_dice_search_static: this search needs %zu bytes of scratch "
+              "but the built-in array holds %zu (n_cls*n_thr*n_area = %lld "
+              "cells); use mlc_dice_search with a caller-provided workspace",
+              need, cap, (long long)n_cls * n_thr * n_area);
+    return MLC_ERR_CAPACITY;
+  }
+  cudaError_t e = cudaSuccess;
+  double *scratch = static_partials(&e);
+  if (scratch == nullptr)
+    return cuda_fail(e, "cudaGetSymbolAddress(g_dice_partials)");
+  // Nothing in the array has to start at zero: dice_search_kernel overwrites
+  // every partial that dice_reduce_kernel reads back (empty chunks write
+  // zeros), and micro_dev is cleared by mlc_dice_search itself.
+  return mlc_dice_search(hist_dev, n_img, n_cls, n_thr, min_area_host, n_area,
+                         empty_one, eps, dice_sum_dev, micro_dev, scratch, cap,
+                         stream);
+}
