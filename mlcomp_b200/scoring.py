@@ -13,12 +13,38 @@ import torch
 
 from . import ops
 
-__all__ = ['SegSearch', 'ClassifyScore', 'shard_range']
+__all__ = ['SegSearch', 'ClassifyScore', 'shard_range', 'combine_ranks']
 
 
 def shard_range(n, rank, world):
     """Contiguous image range of ``rank``: [lo, hi)."""
     return (n * rank) // world, (n * (rank + 1)) // world
+
+
+def combine_ranks(dice_sum, micro, n_img, group=None):
+    """The one exchange step of the sharded path.
+
+    ``micro`` (int64 counts) and ``n_img``: all_reduce(SUM) - exact and
+    order-independent.  ``dice_sum`` (fp64): all_gather, then summed in rank
+    order on every rank, so every rank (and every rerun at the same world
+    size) holds bit-identical scores.  Works on whatever device the tensors
+    live on (NCCL for CUDA, gloo for the CPU tests).  No-op without an
+    initialised process group or at world size 1."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or \
+            dist.get_world_size(group) == 1:
+        return dice_sum, micro, n_img
+    world = dist.get_world_size(group)
+    ints = torch.cat([micro.reshape(-1),
+                      torch.tensor([n_img], dtype=torch.int64,
+                                   device=micro.device)])
+    dist.all_reduce(ints, op=dist.ReduceOp.SUM, group=group)
+    parts = [torch.empty_like(dice_sum) for _ in range(world)]
+    dist.all_gather(parts, dice_sum.contiguous(), group=group)
+    total = parts[0].clone()
+    for p in parts[1:]:
+        total += p
+    return total, ints[:-1].reshape(micro.shape), int(ints[-1].item())
 
 
 class SegSearch:
@@ -122,26 +148,9 @@ class SegSearch:
 
     # -- combine + search -------------------------------------------------------
     def result(self, group=None):
-        """Combine ranks (if torch.distributed is initialised / ``group``
-        given) and search the grid.  Integer counts: one all_reduce(SUM),
-        exact.  fp64 dice sums: all_gather then summed in rank order on every
-        rank, so all ranks (and reruns) get bit-identical scores."""
-        import torch.distributed as dist
-        dice_sum, micro, n_img = self.dice_sum, self.micro, self.n_img
-        if dist.is_available() and dist.is_initialized() and \
-                dist.get_world_size(group) > 1:
-            world = dist.get_world_size(group)
-            ints = torch.cat([micro.reshape(-1),
-                              torch.tensor([n_img], dtype=torch.int64,
-                                           device=micro.device)])
-            dist.all_reduce(ints, op=dist.ReduceOp.SUM, group=group)
-            micro = ints[:-1].reshape(micro.shape)
-            n_img = int(ints[-1].item())
-            parts = [torch.empty_like(dice_sum) for _ in range(world)]
-            dist.all_gather(parts, dice_sum, group=group)
-            dice_sum = parts[0].clone()
-            for p in parts[1:]:
-                dice_sum += p
+        """Combine ranks (``combine_ranks``) and search the grid."""
+        dice_sum, micro, n_img = combine_ranks(self.dice_sum, self.micro,
+                                               self.n_img, group)
         score = (dice_sum / max(n_img, 1)).cpu().numpy()      # [C, B, A]
         m = micro.cpu().numpy()
         b = len(self.thr)

@@ -1,0 +1,98 @@
+"""GPU-resident counterparts of mlcomp/utils/torch.py:11-70.
+
+The reference applies the activation, un-flips, then copies every probability
+to the host (``.detach().cpu().numpy()``, torch.py:29,43).  Here ``infer``
+keeps the raw logits on the device and only *records* the activation and the
+test-time transforms in a ``LogitSource``; the scoring kernels apply both
+while they read (mlc_seg_hist / mlc_rle_encode / mlc_seg_prob).
+"""
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import torch
+
+from mlcomp_b200 import ops
+
+
+@dataclass
+class LogitSource:
+    """Raw model output of one TTA variant / ensemble member."""
+    tensor: torch.Tensor                 # [n, C, Hs, Ws] or [n, C], on device
+    tags: List[str] = field(default_factory=list)    # TtaWrap.tfms
+    activation: Optional[str] = None
+
+    def __len__(self):
+        return self.tensor.shape[0]
+
+    def __getitem__(self, sl):
+        return LogitSource(self.tensor[sl], self.tags, self.activation)
+
+    def prob(self):
+        """Materialise what the reference's ``_infer`` returns."""
+        return fuse([self])
+
+
+def fuse(sources):
+    """Mean of activated, un-transformed sources as fp32 [n, C, H, W]."""
+    act = sources[0].activation
+    ts = [s.tensor.contiguous() for s in sources]
+    if ts[0].dim() == 2:                           # classification logits
+        ts = [t[None, None] for t in ts]
+        return ops.seg_prob(ts, None, act)[0, 0]
+    return ops.seg_prob(ts, [s.tags for s in sources], act)
+
+
+def apply_activation(x, activation):
+    """utils/torch.py:11-18 on the device: falsy -> x, 'sigmoid' through the
+    fused kernel, 'softmax' over dim 1 (classification only, torch op),
+    anything else raises the reference's error."""
+    if not activation:
+        return x
+    if activation == 'sigmoid':
+        if not x.is_cuda:
+            raise TypeError('x must be a CUDA tensor (mlcomp_b200 has no CPU '
+                            'path)')
+        shape = x.shape
+        y = x.contiguous()
+        y = y.reshape(1, 1, -1, shape[-1]) if y.dim() != 4 else y
+        return ops.seg_prob([y], None, 'sigmoid').reshape(shape)
+    if activation == 'softmax':
+        return torch.softmax(x, 1)
+    raise Exception(f'unknown activation = {activation}')
+
+
+def _tags_of(dataset):
+    from mlcomp_b200.contrib.transform.tta import TtaWrap
+    return list(dataset.tags) if isinstance(dataset, TtaWrap) else []
+
+
+def _forward(model, loader, activation, tags):
+    for batch in loader:
+        features = batch['features'].cuda(non_blocking=True)
+        with torch.no_grad():
+            logits = model(features)
+        yield LogitSource(logits.detach(), tags, activation), batch
+
+
+def infer(x, file: str, batch_size: int = 1, batch_mode: bool = False,
+          activation=None, num_workers: int = 1):
+    """utils/torch.py:51-70 with the result left on the device.
+
+    Returns a ``LogitSource`` over the whole dataset, or - ``batch_mode`` - a
+    generator of ``{'prob': LogitSource, 'count': n, **batch}``."""
+    from torch.jit import load
+    from torch.utils.data import DataLoader
+    if activation not in (None, '', 'sigmoid', 'softmax'):
+        raise Exception(f'unknown activation = {activation}')
+    loader = DataLoader(x, batch_size=batch_size, shuffle=False,
+                        num_workers=num_workers, pin_memory=True)
+    model = load(file).cuda()
+    tags = _tags_of(x)
+    if batch_mode:
+        return ({'prob': src, 'count': len(src), **batch}
+                for src, batch in _forward(model, loader, activation, tags))
+    parts = [src.tensor for src, _ in _forward(model, loader, activation, tags)]
+    return LogitSource(torch.cat(parts), tags, activation)
+
+
+__all__ = ['infer', 'apply_activation', 'LogitSource', 'fuse']

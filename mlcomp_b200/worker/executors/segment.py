@@ -1,0 +1,195 @@
+"""Ready-made segmentation executors on the GPU path (``type: valid_segment``
+/ ``type: infer_segment`` in a DAG YAML).
+
+The reference ships no segmentation subclass of Valid / Infer; SURVEY.md 3.3
+reconstructs the flow from the leaves (TtaWrap + infer -> mean -> dice_numpy
+over thresholds x min-areas -> report -> mask2rle -> csv).  These two classes
+are that flow with every pixel pass inside the CUDA kernels.
+
+Inputs are either equations (``y: torch(x, file='unet.pth', ...)`` returning
+``LogitSource``s) or arrays / ``.npy`` paths given as ``logits`` (one entry
+per TTA variant / ensemble member, each [N, C, H, W] fp16|fp32), ``tta`` (one
+tag list per entry) and ``targets`` ([N, C, H, W] one-hot).
+"""
+import os
+
+import numpy as np
+import torch
+
+from mlcomp_b200 import ops, scoring
+from mlcomp_b200.utils.torch import LogitSource
+from .base import Executor
+from .infer import Infer
+from .valid import Valid
+
+
+def _open(x):
+    if isinstance(x, str):
+        return np.load(x, mmap_mode='r')
+    return x
+
+
+def _to_device(x, dtype=None):
+    if isinstance(x, LogitSource):
+        x = x.tensor
+    if not torch.is_tensor(x):
+        x = torch.from_numpy(np.ascontiguousarray(x))
+    if dtype is not None and x.dtype != dtype:
+        x = x.to(dtype)
+    elif dtype is None and x.dtype not in (torch.float16, torch.float32):
+        x = x.float()
+    return x.cuda(non_blocking=True).contiguous()
+
+
+class _SegInputs:
+    """Shared plumbing: sources, tags, part slicing."""
+
+    def _init_inputs(self, logits, tta, activation):
+        self.sources = [_open(s) for s in (logits or [])]
+        self.tta = [list(t) for t in (tta or [[]] * len(self.sources))]
+        self.activation = activation
+
+    def count(self):
+        if self.sources:
+            return len(self.sources[0])
+        return len(self.x)          # dataset attribute used by equations
+
+    def solve(self, name):
+        if name == 'y' and 'y' not in self.equations:
+            lo, hi = self.part
+            return [LogitSource(_to_device(s[lo:hi]), t, self.activation)
+                    for s, t in zip(self.sources, self.tta)]
+        return super().solve(name)
+
+    @staticmethod
+    def _as_sources(preds):
+        if isinstance(preds, LogitSource):
+            preds = [preds]
+        tensors = [_to_device(p) for p in preds]
+        tags = [list(getattr(p, 'tags', [])) for p in preds]
+        act = getattr(preds[0], 'activation', 'sigmoid')
+        return tensors, tags, act
+
+
+@Executor.register
+class ValidSegment(_SegInputs, Valid):
+    def __init__(self, logits=None, tta=None, targets=None, imgs=None,
+                 bins=100, min_areas=(0,), activation='sigmoid',
+                 report_threshold=0.5, colors=None, **kwargs):
+        kwargs.setdefault('layout', 'img_segment')
+        super().__init__(**kwargs)
+        self._init_inputs(logits, tta, activation)
+        self.targets = _open(targets)
+        self.imgs = imgs
+        self.thr = ops.threshold_grid(int(bins))
+        self.min_areas = min_areas
+        self.report_k = int(np.searchsorted(self.thr,
+                                            np.float32(report_threshold)))
+        self.report_k = min(self.report_k, len(self.thr) - 1)
+        self.colors = colors
+        self.search = None
+        self.builder = None
+        self.scores = []
+        self.best = None
+
+    def create_base(self):
+        if self.session is not None and self.task is not None:
+            from mlcomp_b200.worker.reports import SegmentationReportBuilder
+            self.builder = SegmentationReportBuilder(
+                session=self.session, task=self.task, layout=self.layout,
+                name=self.name, plot_count=self.plot_count,
+                colors=self.colors)
+
+    def score(self, preds):
+        tensors, tags, act = self._as_sources(preds)
+        n_cls = tensors[0].shape[1]
+        if self.search is None:
+            self.search = scoring.SegSearch(n_cls, self.thr, self.min_areas,
+                                            activation=act)
+        lo, hi = self.part
+        gt = _to_device(self.targets[lo:hi], torch.uint8)
+        hist = self.search.add(tensors, gt, tags)
+        per_plane = ops.plane_dice(hist, [self.report_k] * n_cls, [0] * n_cls)
+        res = per_plane.mean(dim=1).cpu().numpy()
+        self.scores.extend(res.tolist())
+        return res
+
+    def score_final(self):
+        out = self.search.result()
+        self.best = out['best']
+        return out['dice']
+
+    def plot(self, preds, scores):
+        if self.builder is None or self.builder.plot_count <= 0 or \
+                self.imgs is None:
+            return
+        lo, hi = self.part
+        k = min(hi - lo, self.builder.plot_count)
+        tensors, tags, act = self._as_sources(preds)
+        prob = ops.seg_prob([t[:k].contiguous() for t in tensors], tags, act)
+        mask = (prob >= float(self.thr[self.report_k])).to(torch.uint8)
+        self.builder.process_pred(
+            imgs=self.imgs[lo:lo + k], preds={'pred': mask.cpu().numpy()},
+            targets=np.asarray(self.targets[lo:lo + k]),
+            scores={'dice': scores})
+
+    def plot_final(self, score):
+        if self.builder is not None:
+            self.builder.process_scores({'dice': score})
+
+    def result_extra(self):
+        return {'thresholds': [b['threshold'] for b in self.best],
+                'min_areas': [b['min_area'] for b in self.best],
+                'dice_per_class': [b['dice'] for b in self.best]}
+
+
+@Executor.register
+class InferSegment(_SegInputs, Infer):
+    def __init__(self, logits=None, tta=None, names=None, thresholds=None,
+                 min_areas=None, activation='sigmoid', id_column='ImageId',
+                 rle_column='EncodedPixels', **kwargs):
+        kwargs.setdefault('layout', 'img_segment')
+        super().__init__(**kwargs)
+        self._init_inputs(logits, tta, activation)
+        self.names = names
+        self.thresholds = thresholds
+        self.min_areas = min_areas
+        self.id_column = id_column
+        self.rle_column = rle_column
+        self.rows = []
+
+    def create_base(self):
+        if self.thresholds is None and self.task_provider is not None:
+            for res in self.dependent_results().values():
+                if res and 'thresholds' in res:      # a Valid upstream
+                    self.thresholds = res['thresholds']
+                    self.min_areas = res.get('min_areas')
+                    break
+        if self.thresholds is None:
+            self.thresholds = 0.5
+        if self.min_areas is None:
+            self.min_areas = 0
+
+    def submit(self, preds):
+        tensors, tags, act = self._as_sources(preds)
+        runs, off, cnt, _ = ops.rle_encode(tensors, self.thresholds,
+                                           self.min_areas, xforms=tags,
+                                           activation=act)
+        strings = ops.rle_strings(runs, off, cnt)
+        lo, _ = self.part
+        n, c = tensors[0].shape[:2]
+        for i in range(n):
+            name = self.names[lo + i] if self.names is not None else lo + i
+            for j in range(c):
+                self.rows.append({self.id_column: f'{name}_{j + 1}',
+                                  self.rle_column: strings[i * c + j]})
+
+    def submit_final(self, folder):
+        import pandas as pd
+        path = os.path.join(folder, f'{self.model_name}_{self.suffix}.csv')
+        pd.DataFrame(self.rows, columns=[self.id_column, self.rle_column]) \
+            .to_csv(path, index=False)
+        return path
+
+
+__all__ = ['ValidSegment', 'InferSegment']
