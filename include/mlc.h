@@ -55,7 +55,7 @@ extern "C" {
 #define MLC_MAX_THR      255  /* thresholds in one search grid              */
 #define MLC_MAX_AREAS    8    /* min-area candidates per class              */
 #define MLC_MAX_CLASSES_SEG 64
-#define MLC_LUT_BYTES    65536
+#define MLC_LUT_BYTES    69632 /* 64 KiB byte table + 4 KiB cell table   */
 
 int mlc_version(void);
 const char *mlc_last_error(void);
@@ -95,7 +95,9 @@ int mlc_confusion(const void *preds_dev, int dtype, int64_t n, int n_cls,
  *   thr_host    [n_thr] fp32 ascending, n_thr <= MLC_MAX_THR
  *   lut_dev     NULL, or MLC_LUT_BYTES made by mlc_seg_lut_build with the
  *               same thr/act: enables the table path for a single
- *               untransformed fp16 source (results are identical)
+ *               untransformed fp16 source (results are identical).  Holds
+ *               cnt(act(x)) for each of the 65 536 fp16 codes, then a
+ *               2 048-entry summary of it (one entry per 32 codes)
  */
 int mlc_seg_lut_build(const float *thr_host, int n_thr, int act,
                       uint8_t *lut_dev, void *stream);

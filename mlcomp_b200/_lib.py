@@ -18,7 +18,7 @@ MLC_ACT_NONE, MLC_ACT_SIGMOID = 0, 1
 MLC_XF_HFLIP, MLC_XF_VFLIP, MLC_XF_TRANSPOSE = 1, 2, 4
 MLC_MAX_SOURCES, MLC_MAX_THR, MLC_MAX_AREAS = 32, 255, 8
 MLC_MAX_CLASSES_SEG = 64
-MLC_LUT_BYTES = 65536
+MLC_LUT_BYTES = 69632
 
 # every symbol include/mlc.h declares: (restype, argtypes)
 SIGNATURES = {

@@ -10,6 +10,8 @@
 // before a lane column can reach 65 535.
 #include "mlc_common.cuh"
 
+#include <cstdlib>
+
 namespace mlc {
 
 constexpr int kHistThreads = 512;
@@ -133,12 +135,11 @@ seg_hist_lut(const __grid_constant__ HistArgs a) {
   extern __shared__ uint32_t smem[];
   const int nbins = a.B + 1;
   uint8_t *lut = reinterpret_cast<uint8_t *>(smem);   // 64 KiB
-  uint32_t *cnt = smem + MLC_LUT_BYTES / 4;           // [nbins][32]
+  uint32_t *cnt = smem + 65536 / 4;                   // [nbins][32]
   {
     const uint4 *g = reinterpret_cast<const uint4 *>(a.lut);
     uint4 *s = reinterpret_cast<uint4 *>(lut);
-    for (int i = threadIdx.x; i < MLC_LUT_BYTES / 16; i += blockDim.x)
-      s[i] = g[i];
+    for (int i = threadIdx.x; i < 65536 / 16; i += blockDim.x) s[i] = g[i];
     for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) cnt[i] = 0;
   }
   __syncthreads();
@@ -190,6 +191,187 @@ seg_hist_lut(const __grid_constant__ HistArgs a) {
   }
 }
 
+// ---- cell-table kernel: the same job with conflict-free look-ups ----------
+// ncu on seg_hist_lut (profiles/README.md): the LSU data pipe is 95 % busy
+// because 32 random byte look-ups hit 32 random banks (3.3 wavefronts per
+// LDS).  Neighbouring fp16 codes almost always share a bin, so a table with
+// one 16-bit entry per CELL of 32 consecutive codes (2 048 cells, 4 KiB) is
+// enough: entry = base_bin * 32 + c, bin = (entry + pos) >> 5, where pos is
+// the code's position inside the cell counted in the direction of increasing
+// x (low five bits, inverted for negative codes) and c = 32 - (position of
+// the single bin edge inside the cell), 0 if there is none.  One 32-bit word
+// now covers 64 codes, the codes of one warp fall into a few dozen adjacent
+// words, and adjacent words live in different banks: ~1 wavefront per LDS.
+// Cells with more than one edge or a non-monotone sequence (the +-inf / NaN
+// cells, or a very dense custom threshold table) hold 0xFFFF and send the
+// pixel to the byte table in global memory, so results stay identical to
+// seg_hist_lut / seg_hist_generic for ANY table.
+constexpr int kCells = 2048;
+constexpr int kCellBytes = kCells * 2;
+
+__global__ void cell_build(uint8_t *lut) {
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= kCells) return;
+  const bool neg = cell >= kCells / 2;  // code bit 15
+  const uint8_t *src = lut + cell * 32;
+  const int base = src[neg ? 31 : 0];
+  int edge = 32;
+  bool ok = true;
+  for (int j = 1; j < 32; ++j) {
+    const int v = src[neg ? 31 - j : j];
+    if (edge == 32) {
+      if (v == base + 1) edge = j;
+      else if (v != base) ok = false;
+    } else if (v != base + 1) {
+      ok = false;
+    }
+  }
+  uint16_t *cells = reinterpret_cast<uint16_t *>(lut + 65536);
+  cells[cell] = ok ? (uint16_t)(base * 32 + (edge < 32 ? 32 - edge : 0))
+                   : (uint16_t)0xFFFF;
+}
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+  return d;
+}
+
+constexpr int kCellUnroll = 4;
+
+// Static shared memory on purpose: its addresses are link-time constants, so
+// every LDS / ATOMS below is [register + immediate] with no address add.
+struct CellSmem {
+  uint16_t cells[kCells];                 // entries x4, 0xFFFF = escape
+  uint32_t cnt[(MLC_MAX_THR + 1) * 32];   // [bin][lane]
+};
+
+// Shared-state-space accessors: with a 32-bit .shared address the hardware
+// needs no window base, and the static array's address folds into the
+// instruction's immediate ([reg + imm]).  Going through generic pointers
+// costs one address add per access here.
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
+  uint16_t v;
+  asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void red_shared_add(uint32_t addr, uint32_t v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// Slow path of one 8-pixel item: at least one of its cells escaped to the
+// exact byte table in global memory (inf/NaN cells, very dense tables).
+// Taken per ITEM, not per pixel: a per-pixel test gets if-converted and its
+// predicated instructions then sit in the issue stream of every pixel.
+__device__ __forceinline__ void cell_item_slow(const uint8_t *lut, uint4 v,
+                                            uint2 g, uint32_t cnt_sa,
+                                            uint32_t lane4) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const uint32_t code = (i & 1) ? w[i >> 1] >> 16 : w[i >> 1] & 0xFFFFu;
+    const uint32_t gb = ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
+    const uint32_t bin = __ldg(lut + code);
+    red_shared_add(cnt_sa + ((bin << 7) | lane4), gb ? 0x10000u : 1u);
+  }
+}
+
+// Fast path of one item; ALL_BG = its 8 truth bytes are zero (the common
+// case): the increment is the constant 1.
+template <bool ALL_BG>
+__device__ __forceinline__ void cell_item_fast(const uint32_t t[4],
+                                               const uint32_t e[8], uint2 g,
+                                               uint32_t cnt_sa,
+                                               uint32_t lane4) {
+  uint32_t nz[2] = {0u, 0u};
+  if (!ALL_BG) {
+    nz[0] = __vcmpne4(g.x, 0u) & 0x01010101u;
+    nz[1] = __vcmpne4(g.y, 0u) & 0x01010101u;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const uint32_t tt = t[i >> 1];
+    const uint32_t pos4 = (i & 1) ? (tt >> 14) & 0x7Cu : (tt << 2) & 0x7Cu;
+    const uint32_t x4 = e[i] + pos4;
+    uint32_t inc = 1u;
+    if (!ALL_BG)
+      inc = prmt(nz[i >> 2], 0u, 0x4440u | (i & 3)) * 0xFFFFu + 1u;
+    red_shared_add(cnt_sa + ((x4 & ~127u) | lane4), inc);
+  }
+}
+
+__global__ void __launch_bounds__(kHistThreads, 2)
+seg_hist_cell(const __grid_constant__ HistArgs a) {
+  __shared__ __align__(16) CellSmem sm;
+  const int nbins = a.B + 1;
+  {
+    // entries x4: entry4 + pos*4 = 4*(base*32 + c + pos), and
+    // (that & ~127) = bin * 128 = byte offset of the bin's row of counters
+    const uint16_t *g = reinterpret_cast<const uint16_t *>(a.lut + 65536);
+    for (int i = threadIdx.x; i < kCells; i += blockDim.x) {
+      const uint16_t e = g[i];
+      sm.cells[i] = e == 0xFFFFu ? e : (uint16_t)(e * 4u);
+    }
+    for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) sm.cnt[i] = 0;
+  }
+  __syncthreads();
+  const uint32_t lane4 = (threadIdx.x & 31) * 4;
+  const uint32_t cells_sa = (uint32_t)__cvta_generic_to_shared(sm.cells);
+  const uint32_t cnt_sa = (uint32_t)__cvta_generic_to_shared(sm.cnt);
+  const long long n_units = a.n_planes * a.units_per_plane;
+  const __half *src = static_cast<const __half *>(a.src.ptr[0]);
+
+  for (long long unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+    const long long plane = unit / a.units_per_plane;
+    const int sub = (int)(unit - plane * a.units_per_plane);
+    const size_t plane_off = (size_t)plane * a.plane_px;
+    const uint4 *lg = reinterpret_cast<const uint4 *>(src + plane_off);
+    const uint2 *gt = reinterpret_cast<const uint2 *>(a.gt + plane_off);
+    const long long i0 = (long long)sub * a.items_per_unit;
+    const long long i1 = min(a.items_per_plane, i0 + a.items_per_unit);
+
+    for (long long base = i0; base < i1;
+         base += (long long)kCellUnroll * kHistThreads) {
+      uint4 v[kCellUnroll];
+      uint2 g[kCellUnroll];
+#pragma unroll
+      for (int u = 0; u < kCellUnroll; ++u) {
+        const long long it = base + u * kHistThreads + threadIdx.x;
+        if (it < i1) {
+          v[u] = ldg_stream16(lg + it);
+          g[u] = ldg_stream8(gt + it);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kCellUnroll; ++u) {
+        const long long it = base + u * kHistThreads + threadIdx.x;
+        if (it >= i1) continue;
+        const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+        uint32_t t[4], e[8];
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          // sign mask per half, then invert the low 5 bits of negative
+          // codes so that `pos` runs in the direction of increasing x
+          const uint32_t m = prmt(w[h], 0u, 0xBB99u);
+          t[h] = w[h] ^ (m & 0x001F001Fu);
+          e[2 * h] = lds_u16(cells_sa + ((t[h] >> 4) & 0xFFEu));
+          e[2 * h + 1] = lds_u16(cells_sa + ((t[h] >> 20) & 0xFFEu));
+        }
+        const uint32_t any = (e[0] | e[1] | e[2]) | (e[3] | e[4] | e[5]) |
+                             (e[6] | e[7]);
+        if (any & 0x8000u)
+          cell_item_slow(a.lut, v[u], g[u], cnt_sa, lane4);
+        else if ((g[u].x | g[u].y) == 0u)
+          cell_item_fast<true>(t, e, g[u], cnt_sa, lane4);
+        else
+          cell_item_fast<false>(t, e, g[u], cnt_sa, lane4);
+      }
+    }
+    uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
+    flush_bins(sm.cnt, nbins, out, a.units_per_plane > 1);
+  }
+}
+
 // ---- fused probabilities only --------------------------------------------
 struct ProbArgs {
   SrcSet src;
@@ -221,6 +403,13 @@ seg_prob_kernel(const __grid_constant__ ProbArgs a) {
   }
 }
 
+// Developer switch for A/B runs: MLC_HIST_VARIANT=1 forces the byte-table
+// kernel (seg_hist_lut) where the cell-table kernel would be used.
+static int hist_variant() {
+  const char *e = getenv("MLC_HIST_VARIANT");
+  return e ? atoi(e) : 0;
+}
+
 static int check_thr(const float *thr, int n_thr) {
   MLC_REQUIRE(thr != nullptr, "thr_host is null");
   MLC_REQUIRE(n_thr >= 1 && n_thr <= MLC_MAX_THR,
@@ -248,6 +437,8 @@ extern "C" int mlc_seg_lut_build(const float *thr_host, int n_thr, int act,
   lut_build<<<65536 / 256, 256, 0, (cudaStream_t)stream>>>(t, n_thr, act,
                                                            lut_dev);
   MLC_LAUNCH_CHECK("lut_build");
+  cell_build<<<kCells / 256, 256, 0, (cudaStream_t)stream>>>(lut_dev);
+  MLC_LAUNCH_CHECK("cell_build");
   return MLC_OK;
 }
 
@@ -319,12 +510,16 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   if (units > 1) MLC_CUDA(cudaMemsetAsync(hist_dev, 0, hist_bytes, st));
   const long long n_units = a.n_planes * units;
 
-  if (table) {
-    const size_t smem = MLC_LUT_BYTES + (size_t)(n_thr + 1) * 32 * 4;
+  if (table && hist_variant() != 1) {
+    const int grid = (int)min(n_units, 2ll * sms);
+    seg_hist_cell<<<grid, kHistThreads, 0, st>>>(a);
+    MLC_LAUNCH_CHECK("seg_hist_cell");
+  } else if (table) {
+    const size_t smem = 65536 + (size_t)(n_thr + 1) * 32 * 4;
     // per-device attribute, cheap: set on every call rather than cache
     MLC_CUDA(cudaFuncSetAttribute(seg_hist_lut,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  MLC_LUT_BYTES + (MLC_MAX_THR + 1) * 128));
+                                  65536 + (MLC_MAX_THR + 1) * 128));
     const int grid = (int)min(n_units, 2ll * sms);
     seg_hist_lut<<<grid, kHistThreads, smem, st>>>(a);
     MLC_LAUNCH_CHECK("seg_hist_lut");

@@ -268,7 +268,18 @@ def test_lut_path_equals_generic_on_every_fp16_code(ops):
         p = ops.seg_prob([x]).cpu().numpy().ravel()
         want = np.searchsorted(thr, p, side='right')
         want[np.isnan(p)] = 0
-        assert np.array_equal(lut.cpu().numpy(), want)
+        table = lut.cpu().numpy()
+        assert np.array_equal(table[:65536], want)
+        # the 2 048-cell summary reproduces the byte table wherever it does
+        # not escape (0xFFFF), and escapes are rare for a uniform grid
+        cells = table[65536:].view(np.uint16).astype(np.int64)
+        codes = np.arange(65536)
+        pos = np.where(codes >= 32768, 31 - (codes & 31), codes & 31)
+        e = cells[codes >> 5]
+        live = e != 0xFFFF
+        assert np.array_equal(((e + pos) >> 5)[live], want[live])
+        if len(thr) <= 100:
+            assert (cells == 0xFFFF).sum() <= 4
 
 
 def test_lut_path_matches_oracle_and_splits_big_planes(ops):
