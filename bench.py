@@ -413,13 +413,13 @@ def run_ours(args, cfg):
         'parity': {'subset_planes': sub * c, 'straddling_pixels': moved,
                    'best': res['best']},
         'roofline': {
-            'bound': 'hbm', 'kernel': 'seg_hist_lut',
+            'bound': 'hbm', 'kernel': 'seg_hist_cell',
             'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
             'frac': achieved / peak, 'peak_kind': peak_kind,
             'frac_of_8000_nominal': achieved / 8000.0,
             'algorithmic_bytes_per_launch': bytes_launch,
             'avg_launch_ms': kern_avg,
-            'traffic': committed_traffic('seg_hist_lut_c2'),
+            'traffic': committed_traffic('seg_hist_c2'),
         },
         'cpu_baseline': cpu,
         'e2e': {'value': e2e_value, 'unit': UNIT,

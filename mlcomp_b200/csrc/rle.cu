@@ -73,6 +73,7 @@ rle_kernel(const __grid_constant__ RleArgs a) {
     const int c = (int)(plane % a.C);
     const float thr = a.thr[c];
     const size_t plane_off = (size_t)plane * H * W;
+    const bool inner = plane > 0 && plane + 1 < a.n_planes;
 
     // ---- phase 1: column-major bit plane ---------------------------------
     for (int tile = warp; tile < n_tiles; tile += n_warps) {
@@ -84,8 +85,8 @@ rle_kernel(const __grid_constant__ RleArgs a) {
         const int rows = min(32, H - yb * 32);
         for (int r = 0; r < rows; ++r) {
           float p[8];
-          fused_prob8<T>(a.src, plane_off, H, W, yb * 32 + r, x0, nv, a.act,
-                         p);
+          fused_prob8<T>(a.src, plane_off, H, W, yb * 32 + r, x0, nv, inner,
+                         a.act, p);
 #pragma unroll
           for (int i = 0; i < 8; ++i)
             word[i] |= (uint32_t)(i < nv && p[i] >= thr) << r;

@@ -61,23 +61,37 @@ __device__ __forceinline__ void flush_bins(uint32_t *cnt, int nbins,
 }
 
 // ---- generic kernel: any number of sources, flips, f16/f32 ---------------
+// Binning: cnt(p) = #{k : p >= thr[k]}.  A linear first guess c is checked
+// against ONE 8-byte shared-memory entry pair[c] = (thr[c-1], thr[c]) (with
+// -inf / +inf sentinels): cnt == c  <=>  thr[c-1] <= p < thr[c].  Only when
+// the check fails (guess off by one, NaN, +inf, irregular table) does the
+// pixel walk the table (count_ge), so the result is exact for any ascending
+// table and costs one LDS.64 on a near-uniform one.
 template <typename T>
-__global__ void __launch_bounds__(kHistThreads)
+__global__ void __launch_bounds__(kHistThreads, 2)
 seg_hist_generic(const __grid_constant__ HistArgs a) {
   extern __shared__ uint32_t smem[];
-  const int nbins = a.B + 1;
-  uint32_t *cnt = smem;                                   // [nbins][32]
-  float *thr = reinterpret_cast<float *>(smem + nbins * 32);  // [B]
+  const int B = a.B, nbins = B + 1;
+  const float scale = a.scale, bias = a.bias;
+  uint32_t *cnt = smem;                                        // [nbins][32]
+  float2 *pair = reinterpret_cast<float2 *>(smem + nbins * 32);  // [nbins]
+  float *thr = reinterpret_cast<float *>(pair + nbins);          // [B]
   for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) cnt[i] = 0;
-  for (int i = threadIdx.x; i < a.B; i += blockDim.x) thr[i] = a.thr.v[i];
+  for (int i = threadIdx.x; i < B; i += blockDim.x) thr[i] = a.thr.v[i];
+  for (int i = threadIdx.x; i < nbins; i += blockDim.x)
+    pair[i] = make_float2(i > 0 ? a.thr.v[i - 1] : -INFINITY,
+                          i < B ? a.thr.v[i] : INFINITY);
   __syncthreads();
-  const int lane = threadIdx.x & 31;
+  const uint32_t lane4 = (threadIdx.x & 31) * 4;
+  const uint32_t cnt_sa = (uint32_t)__cvta_generic_to_shared(cnt);
+  const uint32_t pair_sa = (uint32_t)__cvta_generic_to_shared(pair);
   const long long n_units = a.n_planes * a.units_per_plane;
 
   for (long long unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
     const long long plane = unit / a.units_per_plane;
     const int sub = (int)(unit - plane * a.units_per_plane);
     const size_t plane_off = (size_t)plane * a.plane_px;
+    const bool inner = plane > 0 && plane + 1 < a.n_planes;
     const uint8_t *gtp = a.gt + plane_off;
     const int shift = a.flat ? (int)(plane_off & 7) : 0;
     const long long n_items =
@@ -92,19 +106,37 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
         x0 = it == 0 ? 0 : (int)(it * 8 - shift);
         nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
       } else {
-        y = (int)(it / a.items_per_row);
-        x0 = (int)(it - (long long)y * a.items_per_row) * 8;
+        y = (int)((unsigned)it / (unsigned)a.items_per_row);
+        x0 = ((int)it - y * a.items_per_row) * 8;
         nv = min(8, a.W - x0);
       }
       float p[8];
-      fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, a.act, p);
-      float g[8];
-      fetch8<uint8_t>(gtp, 0, a.H, a.W, y, x0, nv, g);
+      fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, inner, a.act, p);
+      const uint2 g = fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner);
+      int c[8];
+      bool ok = nv == 8;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        if (i < nv) {
-          const int c = count_ge(p[i], thr, a.B, a.scale, a.bias);
-          atomicAdd(&cnt[c * 32 + lane], g[i] != 0.f ? 0x10000u : 1u);
+        c[i] = max(0, min(__float2int_rd(fmaf(p[i], scale, bias)), B));
+        const float2 e = lds_f2(pair_sa + c[i] * 8);
+        ok &= p[i] >= e.x && p[i] < e.y;
+      }
+      if (ok) {  // all 8 guesses verified: the common case
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t gb = ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
+          red_shared_add(cnt_sa + ((c[i] << 7) | lane4),
+                         gb ? 0x10000u : 1u);
+        }
+      } else {  // partial item, guess off by one, NaN / +inf, odd table
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (i < nv) {
+            const int cc = count_ge(p[i], thr, B, scale, bias);
+            const uint32_t gb =
+                ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
+            red_shared_add(cnt_sa + ((cc << 7) | lane4), gb ? 0x10000u : 1u);
+          }
         }
       }
     }
@@ -207,7 +239,6 @@ seg_hist_lut(const __grid_constant__ HistArgs a) {
 // pixel to the byte table in global memory, so results stay identical to
 // seg_hist_lut / seg_hist_generic for ANY table.
 constexpr int kCells = 2048;
-constexpr int kCellBytes = kCells * 2;
 
 __global__ void cell_build(uint8_t *lut) {
   const int cell = blockIdx.x * blockDim.x + threadIdx.x;
@@ -245,19 +276,6 @@ struct CellSmem {
   uint16_t cells[kCells];                 // entries x4, 0xFFFF = escape
   uint32_t cnt[(MLC_MAX_THR + 1) * 32];   // [bin][lane]
 };
-
-// Shared-state-space accessors: with a 32-bit .shared address the hardware
-// needs no window base, and the static array's address folds into the
-// instruction's immediate ([reg + imm]).  Going through generic pointers
-// costs one address add per access here.
-__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
-  uint16_t v;
-  asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ void red_shared_add(uint32_t addr, uint32_t v) {
-  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
 
 // Slow path of one 8-pixel item: at least one of its cells escaped to the
 // exact byte table in global memory (inf/NaN cells, very dense tables).
@@ -397,7 +415,8 @@ seg_prob_kernel(const __grid_constant__ ProbArgs a) {
     const int nv = min(8, a.W - x0);
     float p[8];
     const size_t plane_off = (size_t)plane * a.plane_px;
-    fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, a.act, p);
+    const bool inner = plane > 0 && plane + 1 < a.n_planes;
+    fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, inner, a.act, p);
     float *o = a.prob + plane_off + (size_t)y * a.W + x0;
     for (int i = 0; i < nv; ++i) o[i] = p[i];
   }
@@ -524,8 +543,8 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
     seg_hist_lut<<<grid, kHistThreads, smem, st>>>(a);
     MLC_LAUNCH_CHECK("seg_hist_lut");
   } else {
-    const size_t smem = (size_t)(n_thr + 1) * 32 * 4 + (size_t)n_thr * 4;
-    const int grid = (int)min(n_units, 4ll * sms);
+    const size_t smem = (size_t)(n_thr + 1) * (32 * 4 + 8) + (size_t)n_thr * 4;
+    const int grid = (int)min(n_units, 2ll * sms);
     if (dtype == MLC_F16)
       seg_hist_generic<__half><<<grid, kHistThreads, smem, st>>>(a);
     else
