@@ -30,6 +30,7 @@ struct RleArgs {
   long long n_planes;
   int C, H, W, Hw;
   int act;
+  int vec_ok;  // single source, 16-byte aligned, rows a multiple of 8 px
 };
 
 __device__ __forceinline__ int block_excl_scan(int v, int *warp_tot,
@@ -55,12 +56,44 @@ __device__ __forceinline__ int block_excl_scan(int v, int *warp_tot,
   return add + inc - v;
 }
 
-template <typename T>
+// fp16 code -> 16-bit key whose unsigned order is the order of the values
+// (-NaN < -inf < ... < -0 < +0 < ... < +inf < +NaN).
+__device__ __forceinline__ uint32_t half_key(uint32_t code) {
+  return code ^ ((code & 0x8000u) ? 0xFFFFu : 0x8000u);
+}
+constexpr uint32_t kKeyNegInf = 0x03FFu, kKeyPosInf = 0xFC00u;
+
+// CODE: one untransformed fp16 source.  act(x) >= thr is then a statement
+// about the 16-bit code alone, and because the activation evaluated here is
+// non-decreasing over the fp16 values (all 63 488 finite codes, asserted by
+// tests/test_gpu_parity.py::test_sigmoid_is_monotone_over_fp16) it equals
+// key(code) in [key_c, key(+inf)], with key_c found once per CTA and class by
+// a 16-step bisection with the exact activation.  No MUFU work per pixel.
+template <typename T, bool CODE>
 __global__ void __launch_bounds__(kRleThreads)
 rle_kernel(const __grid_constant__ RleArgs a) {
   extern __shared__ uint32_t bits[];  // [W][Hw]
   __shared__ int warp_tot[kRleThreads / 32];
   __shared__ long long s_base;
+  __shared__ uint32_t key_thr[MLC_MAX_CLASSES_SEG];
+  if (CODE) {
+    if ((int)threadIdx.x < a.C) {
+      const float thr = a.thr[threadIdx.x];
+      // smallest key in [key(-inf), key(+inf)] whose value passes; one past
+      // +inf if none does
+      uint32_t lo = kKeyNegInf, hi = kKeyPosInf + 1;
+      while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        const uint32_t code = mid ^ ((mid & 0x8000u) ? 0x8000u : 0xFFFFu);
+        const float x =
+            __half2float(__ushort_as_half((unsigned short)code));
+        if (activate(x, a.act) >= thr) hi = mid;
+        else lo = mid + 1;
+      }
+      key_thr[threadIdx.x] = lo;
+    }
+    __syncthreads();
+  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n_warps = kRleThreads / 32;
   const int H = a.H, W = a.W, Hw = a.Hw;
@@ -83,13 +116,36 @@ rle_kernel(const __grid_constant__ RleArgs a) {
       uint32_t word[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       if (nv > 0) {
         const int rows = min(32, H - yb * 32);
-        for (int r = 0; r < rows; ++r) {
-          float p[8];
-          fused_prob8<T>(a.src, plane_off, H, W, yb * 32 + r, x0, nv, inner,
-                         a.act, p);
+        if (CODE && nv == 8 && (W & 7) == 0 && a.vec_ok) {
+          // rows are 16-byte aligned: one 128-bit load per row, keys compared
+          // as integers; (key - key_c) <= span also rejects NaN codes
+          const uint32_t kc = key_thr[c], span = kKeyPosInf - kc;
+          const bool any = kc <= kKeyPosInf;
+          const __half *row0 = static_cast<const __half *>(a.src.ptr[0]) +
+                               plane_off + (size_t)(yb * 32) * W + x0;
+#pragma unroll 4
+          for (int r = 0; r < rows; ++r) {
+            const uint4 v = ldg_stream16(row0 + (size_t)r * W);
+            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            word[i] |= (uint32_t)(i < nv && p[i] >= thr) << r;
+            for (int h = 0; h < 4; ++h) {
+              // per half: negative -> flip all bits, else flip the sign bit
+              const uint32_t m = prmt32(w4[h], 0u, 0xBB99u);
+              const uint32_t k2 = w4[h] ^ (m | 0x80008000u);
+              const uint32_t klo = k2 & 0xFFFFu, khi = k2 >> 16;
+              word[2 * h] |= (uint32_t)(any && klo - kc <= span) << r;
+              word[2 * h + 1] |= (uint32_t)(any && khi - kc <= span) << r;
+            }
+          }
+        } else {
+          for (int r = 0; r < rows; ++r) {
+            float p[8];
+            fused_prob8<T>(a.src, plane_off, H, W, yb * 32 + r, x0, nv, inner,
+                           a.act, p);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              word[i] |= (uint32_t)(i < nv && p[i] >= thr) << r;
+          }
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i)
@@ -99,7 +155,8 @@ rle_kernel(const __grid_constant__ RleArgs a) {
     __syncthreads();
 
     // ---- phase 2: runs -----------------------------------------------------
-    const int per = (nW + kRleThreads - 1) / kRleThreads;
+    // odd chunk length: consecutive threads start in different banks
+    const int per = ((nW + kRleThreads - 1) / kRleThreads) | 1;
     const int q0 = min(nW, (int)threadIdx.x * per);
     const int q1 = min(nW, q0 + per);
     int n_starts = 0, n_px = 0;
@@ -220,9 +277,13 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
               H, W, smem, kRleMaxSmem);
     return MLC_ERR_UNSUPPORTED;
   }
-  void (*kern)(RleArgs) = dtype == MLC_F16   ? rle_kernel<__half>
-                          : dtype == MLC_F32 ? rle_kernel<float>
-                                             : rle_kernel<uint8_t>;
+  const bool code = dtype == MLC_F16 && n_src == 1 && a.src.any_xf == 0;
+  a.vec_ok = code && ((uintptr_t)src_dev_ptrs[0] % 16) == 0 && (W % 8) == 0;
+  void (*kern)(RleArgs) = dtype == MLC_F16
+                              ? (code ? rle_kernel<__half, true>
+                                      : rle_kernel<__half, false>)
+                          : dtype == MLC_F32 ? rle_kernel<float, false>
+                                             : rle_kernel<uint8_t, false>;
   MLC_CUDA(cudaFuncSetAttribute(kern,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)kRleMaxSmem));

@@ -67,7 +67,9 @@ __device__ __forceinline__ void flush_bins(uint32_t *cnt, int nbins,
 // the check fails (guess off by one, NaN, +inf, irregular table) does the
 // pixel walk the table (count_ge), so the result is exact for any ascending
 // table and costs one LDS.64 on a near-uniform one.
-template <typename T>
+// VEC: flat mode with 16-byte-aligned tensors - every full item after the
+// first of a plane is loaded with fused_flat8.
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(kHistThreads, 2)
 seg_hist_generic(const __grid_constant__ HistArgs a) {
   extern __shared__ uint32_t smem[];
@@ -111,8 +113,15 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
         nv = min(8, a.W - x0);
       }
       float p[8];
-      fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, inner, a.act, p);
-      const uint2 g = fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner);
+      uint2 g;
+      if (VEC && it > 0 && nv == 8) {
+        fused_flat8<T>(a.src, plane_off + x0, a.act, p);
+        mean8(p, a.src.n);
+        g = ldg_stream8(gtp + x0);
+      } else {
+        fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, inner, a.act, p);
+        g = fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner);
+      }
       int c[8];
       bool ok = nv == 8;
 #pragma unroll
@@ -545,10 +554,16 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   } else {
     const size_t smem = (size_t)(n_thr + 1) * (32 * 4 + 8) + (size_t)n_thr * 4;
     const int grid = (int)min(n_units, 2ll * sms);
-    if (dtype == MLC_F16)
-      seg_hist_generic<__half><<<grid, kHistThreads, smem, st>>>(a);
-    else
-      seg_hist_generic<float><<<grid, kHistThreads, smem, st>>>(a);
+    bool vec = a.flat && ((uintptr_t)gt_dev % 16) == 0;
+    for (int i = 0; i < n_src; ++i)
+      vec = vec && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
+    if (dtype == MLC_F16) {
+      if (vec) seg_hist_generic<__half, true><<<grid, kHistThreads, smem, st>>>(a);
+      else seg_hist_generic<__half, false><<<grid, kHistThreads, smem, st>>>(a);
+    } else {
+      if (vec) seg_hist_generic<float, true><<<grid, kHistThreads, smem, st>>>(a);
+      else seg_hist_generic<float, false><<<grid, kHistThreads, smem, st>>>(a);
+    }
     MLC_LAUNCH_CHECK("seg_hist_generic");
   }
   return MLC_OK;

@@ -127,6 +127,38 @@ def test_sigmoid_bit_equal_to_torch_cuda_all_fp16_codes(ops):
     assert d.max() <= 4
 
 
+def test_sigmoid_is_monotone_over_fp16(ops):
+    """The RLE fast path turns `sigmoid(x) >= t` into an integer compare on
+    the fp16 code; that is only valid if the device's sigmoid never decreases
+    from one finite fp16 value to the next."""
+    codes = np.arange(65536, dtype=np.uint16)
+    x = torch.from_numpy(codes.view(np.float16).copy()).reshape(1, 1, 256, 256)
+    p = ops.seg_prob([x.to(DEV)]).cpu().numpy().ravel()
+    vals = codes.view(np.float16).astype(np.float32)
+    fin = ~np.isnan(vals)
+    order = np.argsort(vals[fin], kind='stable')
+    assert (np.diff(p[fin][order]) >= 0).all()
+
+
+def test_rle_code_path_thresholds_on_every_fp16_code(ops):
+    """Single fp16 source: the mask must equal `sigmoid(x) >= t` for every
+    code (NaN -> 0), at ordinary, extreme and exactly-hit thresholds."""
+    codes = np.arange(65536, dtype=np.uint16)
+    x = torch.from_numpy(codes.view(np.float16).copy()).reshape(1, 1, 256, 256)
+    xd = x.to(DEV)
+    p = ops.seg_prob([xd]).cpu().numpy()[0, 0]
+    some = np.float32(p[12, 200])
+    for t in (0.5, 0.01, 0.99, 0.0, 1.0, 1.5, -1.0, float(some),
+              float(np.nextafter(some, np.float32(2)))):
+        runs, off, cnt, area = ops.rle_encode([xd], t, 0)
+        want = oracle.rle_submission(p, np.float32(t), 0)
+        assert ops.rle_strings(runs, off, cnt)[0] == want, t
+        assert int(area[0, 0]) == int((p >= np.float32(t)).sum())
+    raw, off, cnt, _ = ops.rle_encode([xd], 0.25, 0, activation=None)
+    v = codes.view(np.float16).astype(np.float32).reshape(256, 256)
+    assert ops.rle_strings(raw, off, cnt)[0] == oracle.rle_submission(v, 0.25)
+
+
 @pytest.mark.parametrize('dtype', [torch.float16, torch.float32])
 @pytest.mark.parametrize('tags', [
     [[]], [['hflip']], [['vflip']], [['hflip', 'vflip']],
