@@ -14,7 +14,6 @@
 
 namespace mlc {
 
-constexpr int kRleThreads = 512;
 constexpr size_t kRleMaxSmem = 200 * 1024;
 
 struct RleArgs {
@@ -70,8 +69,11 @@ constexpr uint32_t kKeyNegInf = 0x03FFu, kKeyPosInf = 0xFC00u;
 // key(code) in [key_c, key(+inf)], with key_c found once per CTA and class by
 // a 16-step bisection with the exact activation.  No MUFU work per pixel.
 template <typename T, bool CODE>
-__global__ void __launch_bounds__(kRleThreads)
+__global__ void __launch_bounds__(CODE ? 1024 : 512)
 rle_kernel(const __grid_constant__ RleArgs a) {
+  // the code path is light on registers: twice the threads, twice the loads
+  // in flight per SM (one CTA per SM when the bit plane is 128 KiB)
+  constexpr int kRleThreads = CODE ? 1024 : 512;
   extern __shared__ uint32_t bits[];  // [W][Hw]
   __shared__ int warp_tot[kRleThreads / 32];
   __shared__ long long s_base;
@@ -123,7 +125,7 @@ rle_kernel(const __grid_constant__ RleArgs a) {
           const bool any = kc <= kKeyPosInf;
           const __half *row0 = static_cast<const __half *>(a.src.ptr[0]) +
                                plane_off + (size_t)(yb * 32) * W + x0;
-#pragma unroll 4
+#pragma unroll 8
           for (int r = 0; r < rows; ++r) {
             const uint4 v = ldg_stream16(row0 + (size_t)r * W);
             const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
@@ -289,7 +291,7 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
                                 (int)kRleMaxSmem));
   const int per_sm = (int)max((size_t)1, min((size_t)4, (220 * 1024) / (smem + 1024)));
   const int grid = (int)min(a.n_planes, (long long)per_sm * sm_count());
-  kern<<<grid, kRleThreads, smem, st>>>(a);
+  kern<<<grid, code ? 1024 : 512, smem, st>>>(a);
   MLC_LAUNCH_CHECK("rle_kernel");
   return MLC_OK;
 }

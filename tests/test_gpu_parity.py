@@ -329,6 +329,21 @@ def test_lut_path_matches_oracle_and_splits_big_planes(ops):
                           oracle.bin_counts(gt[0, 0].numpy(), p[0, 0], thr))
 
 
+def test_table_kernel_variants_agree(ops, monkeypatch):
+    """Byte table, cell table (default) and the bulk-copy-fed cell table are
+    three schedules of the same arithmetic."""
+    srcs, gt = synth_seg(6, 2, 128, 256, seed=77, empty=0.2)
+    x, g = srcs[0].to(DEV), gt.to(DEV)
+    x[0, 0, 0, :8] = torch.tensor([float('inf'), float('-inf'), float('nan'),
+                                   0.0, -0.0, 65504.0, -65504.0, 6e-8])
+    thr = oracle.threshold_grid(100)
+    lut = ops.seg_lut(thr)
+    want = ops.seg_hist([x], g, thr)
+    for variant in ('0', '1', '3'):
+        monkeypatch.setenv('MLC_HIST_VARIANT', variant)
+        assert torch.equal(ops.seg_hist([x], g, thr, lut=lut), want), variant
+
+
 # ---------------------------------------------------------------- dice grid
 def test_dice_search_matches_dice_numpy_loop(ops):
     n, c, h, w = 5, 3, 24, 40
