@@ -154,6 +154,147 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
   }
 }
 
+// ---- activation-table kernel: any number of fp16 sources -----------------
+// seg_hist_generic with act() of every source value read from the shared-
+// memory table of mlc_common.cuh (act8_table) instead of evaluated: the
+// multi-source configurations (4-flip TTA, 5-model ensemble) are otherwise
+// bound by the sigmoid arithmetic (2 MUFU + ~14 instructions per value), not
+// by HBM.  One 1024-thread CTA per SM; the counters, the (thr[c-1], thr[c])
+// pairs and the threshold table live in the hole of the table's layout.
+constexpr int kTabThreads = 1024;
+
+template <bool VEC>
+__global__ void __launch_bounds__(kTabThreads, 1)
+seg_hist_tab(const __grid_constant__ HistArgs a) {
+  extern __shared__ __align__(16) unsigned char tab_smem[];
+  const int B = a.B, nbins = B + 1;
+  const float scale = a.scale, bias = a.bias;
+  uint32_t *cnt = reinterpret_cast<uint32_t *>(tab_smem + kActTabHoleOff);
+  float2 *pair = reinterpret_cast<float2 *>(cnt + nbins * 32);
+  float *thr = reinterpret_cast<float *>(pair + nbins);
+  act_table_build(tab_smem, a.act);
+  for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) cnt[i] = 0;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) thr[i] = a.thr.v[i];
+  for (int i = threadIdx.x; i < nbins; i += blockDim.x)
+    pair[i] = make_float2(i > 0 ? a.thr.v[i - 1] : -INFINITY,
+                          i < B ? a.thr.v[i] : INFINITY);
+  __syncthreads();
+  const uint32_t lane4 = (threadIdx.x & 31) * 4;
+  const uint32_t tab_sa = (uint32_t)__cvta_generic_to_shared(tab_smem);
+  const uint32_t cnt_sa = (uint32_t)__cvta_generic_to_shared(cnt);
+  const uint32_t pair_sa = (uint32_t)__cvta_generic_to_shared(pair);
+  const long long n_units = a.n_planes * a.units_per_plane;
+  const int S = a.src.n;
+
+  for (long long unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+    const long long plane = unit / a.units_per_plane;
+    const int sub = (int)(unit - plane * a.units_per_plane);
+    const size_t plane_off = (size_t)plane * a.plane_px;
+    const bool inner = plane > 0 && plane + 1 < a.n_planes;
+    const uint8_t *gtp = a.gt + plane_off;
+    const int shift = a.flat ? (int)(plane_off & 7) : 0;
+    const long long n_items =
+        a.flat ? (a.plane_px + shift + 7) / 8 : a.items_per_plane;
+    const long long i0 = (long long)sub * a.items_per_unit;
+    const long long i1 = min(n_items, i0 + a.items_per_unit);
+
+    for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x) {
+      int y, x0, nv;
+      if (a.flat) {
+        y = 0;
+        x0 = it == 0 ? 0 : (int)(it * 8 - shift);
+        nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
+      } else {
+        y = (int)((unsigned)it / (unsigned)a.items_per_row);
+        x0 = ((int)it - y * a.items_per_row) * 8;
+        nv = min(8, a.W - x0);
+      }
+      float p[8];
+      uint2 g;
+      if (VEC && it > 0 && nv == 8) {
+        // aligned flat item: one 128-bit load per source, 4 sources in flight
+        const size_t e0 = plane_off + x0;
+        for (int k0 = 0; k0 < S; k0 += 4) {
+          uint4 r[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (k0 + j < S)
+              r[j] = ldg_stream16(
+                  static_cast<const __half *>(a.src.ptr[k0 + j]) + e0);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (k0 + j < S) {
+              const uint32_t w[4] = {r[j].x, r[j].y, r[j].z, r[j].w};
+              float v[8];
+              act8_table(w, tab_sa, a.act, v);
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                p[i] = (k0 + j == 0) ? v[i] : p[i] + v[i];
+            }
+          }
+        }
+        g = ldg_stream8(gtp + x0);
+      } else {
+        for (int k = 0; k < S; ++k) {
+          const __half *pl = static_cast<const __half *>(a.src.ptr[k]) +
+                             plane_off;
+          const int xf = a.src.xf[k];
+          float v[8];
+          bool done = false;
+          if (!(xf & MLC_XF_TRANSPOSE) && nv == 8) {
+            const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+            const bool rev = (xf & MLC_XF_HFLIP) != 0;
+            const long long s0 =
+                (long long)ys * a.W + (rev ? a.W - 8 - x0 : x0);
+            if (inner || (s0 >= 8 && s0 + 16 <= a.plane_px)) {
+              uint32_t w[4];
+              window8_packed(pl + s0, rev, w);
+              act8_table(w, tab_sa, a.act, v);
+              done = true;
+            }
+          }
+          if (!done) {
+            fetch8<__half>(pl, xf, a.H, a.W, y, x0, nv, inner, v);
+            activate8(v, a.act);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) p[i] = k == 0 ? v[i] : p[i] + v[i];
+        }
+        g = fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner);
+      }
+      mean8(p, S);
+      int c[8];
+      bool ok = nv == 8;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        c[i] = max(0, min(__float2int_rd(fmaf(p[i], scale, bias)), B));
+        const float2 e = lds_f2(pair_sa + c[i] * 8);
+        ok &= p[i] >= e.x && p[i] < e.y;
+      }
+      if (ok) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t gb = ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
+          red_shared_add(cnt_sa + ((c[i] << 7) | lane4),
+                         gb ? 0x10000u : 1u);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (i < nv) {
+            const int cc = count_ge(p[i], thr, B, scale, bias);
+            const uint32_t gb =
+                ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
+            red_shared_add(cnt_sa + ((cc << 7) | lane4), gb ? 0x10000u : 1u);
+          }
+        }
+      }
+    }
+    uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
+    flush_bins(cnt, nbins, out, a.units_per_plane > 1);
+  }
+}
+
 // ---- table kernel: ONE untransformed fp16 source --------------------------
 // sigmoid is a function of the 16-bit code alone, so cnt(sigmoid(x)) is a
 // 64 Ki-entry byte table (built once per threshold grid by lut_build with the
@@ -613,7 +754,9 @@ seg_prob_kernel(const __grid_constant__ ProbArgs a) {
 // bulk async copies (seg_hist_cell_tma; measured 7 % slower on C2 than the
 // default: per-chunk mbarrier traffic outweighs the freed registers),
 // default: cell-table kernel with register-staged 128-bit loads
-// (seg_hist_cell).
+// (seg_hist_cell).  =4: multi-source fp16 jobs evaluate the sigmoid instead
+// of reading it from the shared-memory activation table (seg_hist_generic
+// where seg_hist_tab would run).
 static int hist_variant() {
   const char *e = getenv("MLC_HIST_VARIANT");
   return e ? atoi(e) : 0;
@@ -747,7 +890,25 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
     bool vec = a.flat && ((uintptr_t)gt_dev % 16) == 0;
     for (int i = 0; i < n_src; ++i)
       vec = vec && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
-    if (dtype == MLC_F16) {
+    if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID && hist_variant() != 4) {
+      // activation table in shared memory: one 1024-thread CTA per SM
+      const size_t tab_smem = kActTabBytes;
+      static_assert((MLC_MAX_THR + 1) * (32 * 4 + 8) + MLC_MAX_THR * 4 <=
+                        kActTabHoleBytes,
+                    "counters do not fit the hole of the activation table");
+      const int tgrid = (int)min(n_units, (long long)sms);
+      if (vec) {
+        MLC_CUDA(cudaFuncSetAttribute(
+            seg_hist_tab<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            (int)tab_smem));
+        seg_hist_tab<true><<<tgrid, kTabThreads, tab_smem, st>>>(a);
+      } else {
+        MLC_CUDA(cudaFuncSetAttribute(
+            seg_hist_tab<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            (int)tab_smem));
+        seg_hist_tab<false><<<tgrid, kTabThreads, tab_smem, st>>>(a);
+      }
+    } else if (dtype == MLC_F16) {
       if (vec) seg_hist_generic<__half, true><<<grid, kHistThreads, smem, st>>>(a);
       else seg_hist_generic<__half, false><<<grid, kHistThreads, smem, st>>>(a);
     } else {
