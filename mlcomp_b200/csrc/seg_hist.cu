@@ -31,7 +31,8 @@ struct HistArgs {
   int units_per_plane;
   long long items_per_unit;  // items of 8 px
   long long items_per_plane;
-  int items_per_row;
+  long long full_items;  // row mode: H * (W / 8)
+  int items_per_row;     // row mode: W / 8 full items per row
   int flat;
   float scale, bias;
 };
@@ -107,10 +108,14 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
         y = 0;
         x0 = it == 0 ? 0 : (int)(it * 8 - shift);
         nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
-      } else {
+      } else if (it < a.full_items) {  // the W/8 full items of each row first
         y = (int)((unsigned)it / (unsigned)a.items_per_row);
         x0 = ((int)it - y * a.items_per_row) * 8;
-        nv = min(8, a.W - x0);
+        nv = 8;
+      } else {  // then the H row tails together: warps do not mix the two
+        y = (int)(it - a.full_items);
+        x0 = a.items_per_row * 8;
+        nv = a.W & 7;
       }
       float p[8];
       uint2 g;
@@ -204,10 +209,14 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
         y = 0;
         x0 = it == 0 ? 0 : (int)(it * 8 - shift);
         nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
-      } else {
+      } else if (it < a.full_items) {  // the W/8 full items of each row first
         y = (int)((unsigned)it / (unsigned)a.items_per_row);
         x0 = ((int)it - y * a.items_per_row) * 8;
-        nv = min(8, a.W - x0);
+        nv = 8;
+      } else {  // then the H row tails together: warps do not mix the two
+        y = (int)(it - a.full_items);
+        x0 = a.items_per_row * 8;
+        nv = a.W & 7;
       }
       float p[8];
       uint2 g;
@@ -828,7 +837,8 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   a.flat = a.src.any_xf == 0;
   a.H = a.flat ? 1 : H;
   a.W = a.flat ? (int)a.plane_px : W;
-  a.items_per_row = (a.W + 7) / 8;
+  a.items_per_row = a.W / 8;
+  a.full_items = (long long)a.items_per_row * H;
   // linear first guess for count_ge: k ~ (p - thr[0]) * (B-1)/(thr[B-1]-thr[0])
   const float span = thr_host[n_thr - 1] - thr_host[0];
   a.scale = (n_thr > 1 && span > 0) ? (float)(n_thr - 1) / span : 0.f;
@@ -841,7 +851,7 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
                      ((uintptr_t)gt_dev % 8) == 0;
   // flat mode may prepend one partial item to reach 16-byte alignment
   a.items_per_plane = a.flat ? (a.plane_px + 7 + 7) / 8
-                             : (long long)a.items_per_row * H;
+                             : a.full_items + ((a.W & 7) ? H : 0);
   if (table) a.items_per_plane = a.plane_px / 8;
   // split planes into units so that (a) a lane column stays below 65 536 and
   // (b) small jobs still fill the machine
