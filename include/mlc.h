@@ -187,6 +187,21 @@ int mlc_rle_encode(const void *const *src_dev_ptrs, const int32_t *xform,
                    int32_t *cnt_dev, int32_t *area_dev, int64_t *total_dev,
                    void *stream);
 
+/* Text of the run-length strings, replacing the ' '.join(str(x) for x in
+ * runs) of contrib/transform/rle.py:13 (and what
+ * examples/digit-recognizer/executors/infer.py:76-78 then writes to the csv
+ * the Submit executor reads, worker/executors/kaggle.py:100-110).
+ *   runs_dev/off_dev/cnt_dev  the outputs of mlc_rle_encode
+ *   chars_dev   char[capacity]: ASCII decimal values separated by single
+ *               blanks, no terminator; plane p owns
+ *               chars_dev[str_off[p] .. str_off[p]+str_len[p]) ('' -> len 0)
+ *   total_dev   [1] int64 characters needed; planes that did not fit have
+ *               str_off = -1 and the caller retries with a larger buffer */
+int mlc_rle_format(const int32_t *runs_dev, const int64_t *off_dev,
+                   const int32_t *cnt_dev, int64_t n_planes, char *chars_dev,
+                   int64_t capacity, int64_t *str_off_dev, int32_t *str_len_dev,
+                   int64_t *total_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,6 +51,9 @@ SIGNATURES = {
                                POINTER(c_float), POINTER(c_int32), c_int,
                                c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p]),
+    'mlc_rle_format': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
+                               c_int64, c_void_p, c_void_p, c_void_p,
+                               c_void_p]),
 }
 
 _lib = None

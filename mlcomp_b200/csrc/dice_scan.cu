@@ -72,13 +72,23 @@ dice_search_kernel(const __grid_constant__ SearchArgs a) {
   for (int m = 0; m < MLC_MAX_AREAS; ++m)
     area[m] = m < a.A ? a.areas.v[c * a.A + m] : 0;
 
+  // the loop is a chain of dependent global loads (one image after the
+  // other): fetch image n+1 while image n is scanned
+  unsigned nh0 = 0, nh1 = 0;
+  if (j < nb && n0 < n1) {
+    const uint32_t *h = a.hist + ((size_t)n0 * a.C + c) * 2 * nb;
+    nh0 = h[j];
+    nh1 = h[nb + j];
+  }
   for (long long n = n0; n < n1; ++n) {
-    const uint32_t *h = a.hist + ((size_t)n * a.C + c) * 2 * nb;
-    unsigned long long v = 0;
-    if (j < nb) {
-      const unsigned h0 = h[j], h1 = h[nb + j];
-      v = ((unsigned long long)(h0 + h1) << 32) | h1;
+    const unsigned h0 = nh0, h1 = nh1;
+    if (j < nb && n + 1 < n1) {
+      const uint32_t *h = a.hist + ((size_t)(n + 1) * a.C + c) * 2 * nb;
+      nh0 = h[j];
+      nh1 = h[nb + j];
     }
+    unsigned long long v = 0;
+    if (j < nb) v = ((unsigned long long)(h0 + h1) << 32) | h1;
     const unsigned long long s = block_suffix_sum(v, warp_tot);
     if (j < nb) S[j] = s;
     if (j == 0) S[nb] = 0ull;

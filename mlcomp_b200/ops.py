@@ -17,7 +17,8 @@ from ._lib import (MLC_ACT_NONE, MLC_ACT_SIGMOID, MLC_F16, MLC_F32, MLC_U8,
 
 __all__ = ['activation_code', 'compose_tta', 'confusion', 'seg_lut',
            'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
-           'threshold_grid', 'counts_from_hist', 'rle_strings']
+           'threshold_grid', 'counts_from_hist', 'rle_strings',
+           'rle_strings_host']
 
 
 def _stream():
@@ -319,17 +320,38 @@ def rle_encode(sources, thr_per_class, min_area_per_class=0, xforms=None,
 
 
 def rle_strings(runs, off, cnt):
-    """Format device run pairs as the reference's strings
-    (contrib/transform/rle.py:13: ' '.join(str(x) for x in runs)); one string
-    per plane, '' for an empty mask.  Host-side formatting of integers the
-    GPU produced."""
+    """The reference's strings (contrib/transform/rle.py:13:
+    ' '.join(str(x) for x in runs)), one per plane, '' for an empty mask.
+    The decimal text is produced on the device (mlc_rle_format); the host
+    only slices one byte buffer.  Synchronises (it returns Python strings)."""
+    lib = _lib.load()
+    dev = off.device
+    planes = off.numel()
+    str_off = torch.empty(planes, dtype=torch.int64, device=dev)
+    str_len = torch.empty(planes, dtype=torch.int32, device=dev)
+    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    capacity = max(64, 8 * int(runs.numel()))
+    while True:
+        chars = torch.empty(capacity, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.mlc_rle_format(_ptr(runs), _ptr(off), _ptr(cnt), planes,
+                                     _ptr(chars), capacity, _ptr(str_off),
+                                     _ptr(str_len), _ptr(total), _stream()))
+        need = int(total.item())
+        if need <= capacity:
+            break
+        capacity = need
+    text = chars[:need].cpu().numpy().tobytes()
+    o = str_off.cpu().numpy()
+    n = str_len.cpu().numpy()
+    return [text[a:a + b].decode('ascii') for a, b in zip(o, n)]
+
+
+def rle_strings_host(runs, off, cnt):
+    """Host-side formatting of the same integers (used by the tests to check
+    the device formatter)."""
     runs_h = runs.cpu().numpy()
     off_h = off.cpu().numpy().ravel()
     cnt_h = cnt.cpu().numpy().ravel()
-    out = []
-    for o, k in zip(off_h, cnt_h):
-        if k == 0:
-            out.append('')
-        else:
-            out.append(' '.join(map(str, runs_h[o:o + 2 * k].tolist())))
-    return out
+    return [' '.join(map(str, runs_h[o:o + 2 * k].tolist())) if k else ''
+            for o, k in zip(off_h, cnt_h)]

@@ -459,6 +459,30 @@ def test_rle_edge_masks_and_retry(ops):
     assert got[0] == '' and got[1] == f'1 {h * w}'
 
 
+def test_device_string_formatter(ops):
+    """mlc_rle_format on hand-made pairs: 1..10 digit values, an empty plane,
+    a plane that did not fit the encoder's buffer (off = -1), several tiles."""
+    rng = np.random.default_rng(12)
+    planes = []
+    planes.append(np.array([1, 9, 10, 99, 100, 999, 1000, 2147483647],
+                           np.int32))
+    planes.append(np.zeros(0, np.int32))
+    planes.append(rng.integers(1, 10 ** 9, 2 * 3001).astype(np.int32))
+    planes.append(np.array([7, 7], np.int32))
+    planes.append(rng.integers(1, 2000, 2 * 5000).astype(np.int32))
+    runs = torch.from_numpy(np.concatenate(planes)).to(DEV)
+    cnt = torch.tensor([len(p) // 2 for p in planes], dtype=torch.int32,
+                       device=DEV)
+    off = torch.tensor(np.cumsum([0] + [len(p) for p in planes[:-1]]),
+                       dtype=torch.int64, device=DEV)
+    got = ops.rle_strings(runs, off, cnt)
+    want = [' '.join(str(v) for v in p) for p in planes]
+    assert got == want
+    assert got == ops.rle_strings_host(runs, off, cnt)
+    off[3] = -1                       # "did not fit": formatted as empty
+    assert ops.rle_strings(runs, off, cnt)[3] == ''
+
+
 def test_errors_are_loud(ops):
     from mlcomp_b200._lib import MlcError
     x = torch.zeros(1, 1, 8, 8, dtype=torch.float16, device=DEV)
