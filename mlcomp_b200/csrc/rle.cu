@@ -62,12 +62,60 @@ __device__ __forceinline__ uint32_t half_key(uint32_t code) {
 }
 constexpr uint32_t kKeyNegInf = 0x03FFu, kKeyPosInf = 0xFC00u;
 
+// 8 columns x `rows` rows of one fp16 plane -> 8 column words (bit r = row r
+// passes).  RAW: compare the raw codes, else their order-preserving keys.
+template <bool RAW>
+__device__ __forceinline__ void code_rows(const __half *row0, int W, int rows,
+                                          uint32_t sub, uint32_t lim_lo,
+                                          uint32_t lim_hi, uint32_t word[8]) {
+  for (int r0 = 0; r0 < rows; r0 += 4) {
+    uint4 v[4];  // four rows in flight before any compare
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      v[q] = r0 + q < rows ? ldg_stream16(row0 + (size_t)(r0 + q) * W)
+                           : make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t w4[4] = {v[q].x, v[q].y, v[q].z, v[q].w};
+      const uint32_t bit = r0 + q < rows ? 1u << (r0 + q) : 0u;
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        uint32_t k2 = w4[h];
+        if (!RAW) {
+          // per half: negative -> flip all bits, else flip the sign bit
+          const uint32_t m = prmt32(k2, 0u, 0xBB99u);
+          k2 ^= m | 0x80008000u;
+        }
+        if ((k2 << 16) - sub <= lim_lo) word[2 * h] |= bit;
+        if (k2 - sub <= lim_hi) word[2 * h + 1] |= bit;
+      }
+    }
+  }
+}
+
 // CODE: one untransformed fp16 source.  act(x) >= thr is then a statement
 // about the 16-bit code alone, and because the activation evaluated here is
 // non-decreasing over the fp16 values (all 63 488 finite codes, asserted by
 // tests/test_gpu_parity.py::test_sigmoid_is_monotone_over_fp16) it equals
 // key(code) in [key_c, key(+inf)], with key_c found once per CTA and class by
 // a 16-step bisection with the exact activation.  No MUFU work per pixel.
+__device__ __forceinline__ int block_excl_max(int v, int *warp_tot) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc = max(inc, t);
+  }
+  if (lane == 31) warp_tot[w] = inc;
+  __syncthreads();
+  int before = 0;
+  for (int k = 0; k < w; ++k) before = max(before, warp_tot[k]);
+  __syncthreads();
+  const int up = __shfl_up_sync(0xffffffffu, inc, 1);
+  return max(before, lane ? up : 0);
+}
+
 template <typename T, bool CODE>
 __global__ void __launch_bounds__(CODE ? 1024 : 512)
 rle_kernel(const __grid_constant__ RleArgs a) {
@@ -99,6 +147,7 @@ rle_kernel(const __grid_constant__ RleArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n_warps = kRleThreads / 32;
   const int H = a.H, W = a.W, Hw = a.Hw;
+  const int Hp = Hw | 1;  // odd column pitch: see the phase-1 store below
   const int nW = W * Hw;
   const int hl = (H - 1) & 31;  // top valid bit of a column's last word
   const int xchunks = (W + 255) / 256;
@@ -119,25 +168,27 @@ rle_kernel(const __grid_constant__ RleArgs a) {
       if (nv > 0) {
         const int rows = min(32, H - yb * 32);
         if (CODE && nv == 8 && (W & 7) == 0 && a.vec_ok) {
-          // rows are 16-byte aligned: one 128-bit load per row, keys compared
-          // as integers; (key - key_c) <= span also rejects NaN codes
-          const uint32_t kc = key_thr[c], span = kKeyPosInf - kc;
+          // rows are 16-byte aligned: one 128-bit load per row.  A pixel
+          // passes iff key(code) lies in [key_c, key(+inf)] (NaN keys fall
+          // outside); both halves of a packed pair are tested in place:
+          //   high half: (k2 - (kc << 16))       <= (span << 16 | 0xFFFF)
+          //   low half : ((k2 << 16) - (kc << 16)) <= (span << 16)
+          // When the class threshold is a non-negative logit the passing
+          // codes [code_c, 0x7C00] are already one unsigned range of the RAW
+          // code and the key transform is skipped (flip == 0).
+          const uint32_t kc = key_thr[c];
           const bool any = kc <= kKeyPosInf;
+          const bool raw = kc >= 0x8000u;           // x_c >= +0
+          const uint32_t lo_c = raw ? kc ^ 0x8000u : kc;
+          const uint32_t hi_c = raw ? 0x7C00u : kKeyPosInf;
+          const uint32_t sub = lo_c << 16;
+          const uint32_t lim_lo = (hi_c - lo_c) << 16;
+          const uint32_t lim_hi = lim_lo | 0xFFFFu;
           const __half *row0 = static_cast<const __half *>(a.src.ptr[0]) +
                                plane_off + (size_t)(yb * 32) * W + x0;
-#pragma unroll 8
-          for (int r = 0; r < rows; ++r) {
-            const uint4 v = ldg_stream16(row0 + (size_t)r * W);
-            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              // per half: negative -> flip all bits, else flip the sign bit
-              const uint32_t m = prmt32(w4[h], 0u, 0xBB99u);
-              const uint32_t k2 = w4[h] ^ (m | 0x80008000u);
-              const uint32_t klo = k2 & 0xFFFFu, khi = k2 >> 16;
-              word[2 * h] |= (uint32_t)(any && klo - kc <= span) << r;
-              word[2 * h + 1] |= (uint32_t)(any && khi - kc <= span) << r;
-            }
+          if (any) {
+            if (raw) code_rows<true>(row0, W, rows, sub, lim_lo, lim_hi, word);
+            else code_rows<false>(row0, W, rows, sub, lim_lo, lim_hi, word);
           }
         } else {
           for (int r = 0; r < rows; ++r) {
@@ -149,30 +200,75 @@ rle_kernel(const __grid_constant__ RleArgs a) {
               word[i] |= (uint32_t)(i < nv && p[i] >= thr) << r;
           }
         }
+        // Conflict-free store: with an odd column pitch the bank of
+        // (x, yb) is (x * Hp + yb) % 32, and lane l writing column
+        // 8l + ((s + l/4) & 7) in step s makes the 32 banks of a step
+        // distinct (8*Hp*l spreads l%4 over the multiples of 8, Hp*j spreads
+        // j over the residues mod 8).  The register array is rotated by l/4
+        // with three conditional-swap stages instead of indexed dynamically.
+        const int rot = (lane >> 2) & 7;
+        if (rot & 4) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          if (i < nv) bits[(x0 + i) * Hw + yb] = word[i];
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t t = word[i];
+            word[i] = word[i + 4];
+            word[i + 4] = t;
+          }
+        }
+        if (rot & 2) {
+          const uint32_t t0 = word[0], t1 = word[1];
+#pragma unroll
+          for (int i = 0; i < 6; ++i) word[i] = word[i + 2];
+          word[6] = t0;
+          word[7] = t1;
+        }
+        if (rot & 1) {
+          const uint32_t t0 = word[0];
+#pragma unroll
+          for (int i = 0; i < 7; ++i) word[i] = word[i + 1];
+          word[7] = t0;
+        }
+#pragma unroll
+        for (int s2 = 0; s2 < 8; ++s2) {  // word[s2] is column (s2 + rot) & 7
+          const int j = (s2 + rot) & 7;
+          if (j < nv) bits[(x0 + j) * Hp + yb] = word[s2];
+        }
       }
     }
     __syncthreads();
 
     // ---- phase 2: runs -----------------------------------------------------
-    // odd chunk length: consecutive threads start in different banks
+    // Logical word q = x * Hw + yb lives at bits[x * Hp + yb].  Every thread
+    // owns `per` consecutive logical words (odd: neighbouring threads start
+    // in different banks).
     const int per = ((nW + kRleThreads - 1) / kRleThreads) | 1;
     const int q0 = min(nW, (int)threadIdx.x * per);
     const int q1 = min(nW, q0 + per);
-    int n_starts = 0, n_px = 0;
-    for (int q = q0; q < q1; ++q) {
-      const uint32_t w = bits[q];
-      const int yb = q % Hw;
-      uint32_t prev = 0;
-      if (q > 0) prev = yb > 0 ? bits[q - 1] >> 31 : (bits[q - 1] >> hl) & 1u;
-      n_starts += __popc(w & ~((w << 1) | prev));
-      n_px += __popc(w);
+    const int xq0 = q0 / Hw, ybq0 = q0 - xq0 * Hw;
+    int n_starts = 0, n_px = 0, last_start = 0;
+    uint32_t open0 = 0;  // a run is open across the start of my chunk
+    {
+      int x = xq0, yb = ybq0;
+      for (int q = q0; q < q1; ++q) {
+        const int ad = x * Hp + yb;
+        const uint32_t w = bits[ad];
+        uint32_t prev = 0;
+        if (yb > 0) prev = bits[ad - 1] >> 31;
+        else if (x > 0) prev = (bits[ad - Hp + Hw - 1] >> hl) & 1u;
+        const uint32_t starts = w & ~((w << 1) | prev);
+        if (q == q0) open0 = prev & w & 1u;
+        n_starts += __popc(starts);
+        n_px += __popc(w);
+        if (starts) last_start = x * H + yb * 32 + 32 - __clz(starts);  // 1-based
+        if (++yb == Hw) { yb = 0; ++x; }
+      }
     }
     int tot_runs, tot_px;
     const int my_first = block_excl_scan(n_starts, warp_tot, &tot_runs);
     (void)block_excl_scan(n_px, warp_tot, &tot_px);
+    // start of the run that is open where my chunk begins = the latest start
+    // anywhere before it
+    const int carry = block_excl_max(last_start, warp_tot);
     const int min_area = a.min_area[c];
     if (min_area > 0 && tot_px < min_area) tot_runs = 0;  // dice.py:13-15 rule
     if (threadIdx.x == 0) {
@@ -186,35 +282,34 @@ rle_kernel(const __grid_constant__ RleArgs a) {
     __syncthreads();
     const long long base = s_base;
     if (tot_runs > 0 && base >= 0) {
-      int32_t *out = a.runs + base;
-      int si = my_first;
+      // complete (start, length) pairs, one 8-byte store each, emitted by the
+      // thread in whose chunk the run ENDS (rle.py:11-12)
+      int2 *out = reinterpret_cast<int2 *>(a.runs + base);
+      int ei = my_first - (int)open0;  // runs ended before my chunk
+      int cur = carry;                 // start of the currently open run
+      int x = xq0, yb = ybq0;
       for (int q = q0; q < q1; ++q) {
-        const uint32_t w = bits[q];
-        const int x = q / Hw, yb = q - x * Hw;
+        const int ad = x * Hp + yb;
+        const uint32_t w = bits[ad];
         uint32_t prev = 0, next = 0;
-        if (q > 0) prev = yb > 0 ? bits[q - 1] >> 31 : (bits[q - 1] >> hl) & 1u;
-        if (q + 1 < nW) next = bits[q + 1] & 1u;
+        if (yb > 0) prev = bits[ad - 1] >> 31;
+        else if (x > 0) prev = (bits[ad - Hp + Hw - 1] >> hl) & 1u;
+        if (yb < Hw - 1) next = bits[ad + 1] & 1u;
+        else if (x < W - 1) next = bits[ad + Hp - (Hw - 1)] & 1u;
         const int top = yb == Hw - 1 ? hl : 31;
-        uint32_t starts = w & ~((w << 1) | prev);
+        const uint32_t starts = w & ~((w << 1) | prev);
         uint32_t ends = w & ~((w >> 1) | (next << top));
         const int pos0 = x * H + yb * 32 + 1;  // 1-based, column-major
-        // ends before this word = starts before it, minus the run (if any)
-        // that is still open across the word boundary
-        int ei = si - (int)(prev & w & 1u);
-        while (starts) {
-          const int b = __ffs(starts) - 1;
-          starts &= starts - 1;
-          out[2 * (si++)] = pos0 + b;
-        }
         while (ends) {
-          const int b = __ffs(ends) - 1;
+          const int e = __ffs(ends) - 1;
           ends &= ends - 1;
-          out[2 * (ei++) + 1] = pos0 + b + 1;  // exclusive end
+          const uint32_t s_le = starts & (0xFFFFFFFFu >> (31 - e));
+          const int st = s_le ? pos0 + 31 - __clz(s_le) : cur;
+          out[ei++] = make_int2(st, pos0 + e - st + 1);
         }
+        if (starts) cur = pos0 + 31 - __clz(starts);
+        if (++yb == Hw) { yb = 0; ++x; }
       }
-      __syncthreads();
-      for (int j = threadIdx.x; j < tot_runs; j += kRleThreads)
-        out[2 * j + 1] -= out[2 * j];  // rle.py:12 runs[1::2] -= runs[::2]
     }
     __syncthreads();
   }
@@ -247,6 +342,8 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   MLC_REQUIRE(off_dev && cnt_dev && total_dev, "off/cnt/total is null");
   MLC_REQUIRE(capacity >= 0 && (runs_dev || capacity == 0),
               "runs_dev is null with capacity %lld", (long long)capacity);
+  MLC_REQUIRE(((uintptr_t)runs_dev % 8) == 0,
+              "runs_dev must be 8-byte aligned (pairs are stored whole)");
   RleArgs a;
   const int eb = dtype == MLC_F16 ? 2 : dtype == MLC_F32 ? 4 : 1;
   if (int rc = fill_srcset(a.src, src_dev_ptrs, xform, n_src, eb, H, W))
@@ -272,7 +369,7 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   a.W = W;
   a.Hw = (H + 31) / 32;
   a.act = act;
-  const size_t smem = (size_t)W * a.Hw * 4;
+  const size_t smem = (size_t)W * (a.Hw | 1) * 4;
   if (smem > kRleMaxSmem) {
     set_error("plane %d x %d needs %zu bytes of shared memory for its bit "
               "plane; this build supports up to %zu",
