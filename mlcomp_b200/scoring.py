@@ -24,27 +24,33 @@ def shard_range(n, rank, world):
 def combine_ranks(dice_sum, micro, n_img, group=None):
     """The one exchange step of the sharded path.
 
-    ``micro`` (int64 counts) and ``n_img``: all_reduce(SUM) - exact and
-    order-independent.  ``dice_sum`` (fp64): all_gather, then summed in rank
-    order on every rank, so every rank (and every rerun at the same world
-    size) holds bit-identical scores.  Works on whatever device the tensors
-    live on (NCCL for CUDA, gloo for the CPU tests).  No-op without an
-    initialised process group or at world size 1."""
+    ONE all_gather of a packed int64 buffer per rank: the fp64 ``dice_sum``
+    (bit pattern), the int64 ``micro`` counts and ``n_img``.  Integers are
+    then summed (exact, order-independent); the fp64 partial sums are added
+    in rank order on every rank, so every rank (and every rerun at the same
+    world size) holds bit-identical scores.  Works on whatever device the
+    tensors live on (NCCL for CUDA, gloo for the CPU tests).  No-op without
+    an initialised process group or at world size 1."""
     import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized()) or \
             dist.get_world_size(group) == 1:
         return dice_sum, micro, n_img
     world = dist.get_world_size(group)
-    ints = torch.cat([micro.reshape(-1),
+    nd, nm = dice_sum.numel(), micro.numel()
+    mine = torch.cat([dice_sum.contiguous().view(torch.int64).reshape(-1),
+                      micro.reshape(-1),
                       torch.tensor([n_img], dtype=torch.int64,
                                    device=micro.device)])
-    dist.all_reduce(ints, op=dist.ReduceOp.SUM, group=group)
-    parts = [torch.empty_like(dice_sum) for _ in range(world)]
-    dist.all_gather(parts, dice_sum.contiguous(), group=group)
+    rows = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(rows, mine, group=group)
+    everyone = torch.stack(rows)
+    parts = everyone[:, :nd].contiguous().view(torch.float64)
     total = parts[0].clone()
-    for p in parts[1:]:
-        total += p
-    return total, ints[:-1].reshape(micro.shape), int(ints[-1].item())
+    for r in range(1, world):
+        total += parts[r]
+    ints = everyone[:, nd:].sum(dim=0)
+    return (total.reshape(dice_sum.shape), ints[:nm].reshape(micro.shape),
+            ints[nm])
 
 
 class SegSearch:
@@ -77,6 +83,7 @@ class SegSearch:
         self.micro = torch.zeros((self.n_cls, 1 + 2 * b), dtype=torch.int64,
                                  device=self.device)
         self.n_img = 0
+        self._fresh = False
         self._copy_stream = None
         self._stage = None
         # (start, end) CUDA events around every histogram launch, for the
@@ -85,8 +92,9 @@ class SegSearch:
         self.kernel_events = []
 
     def reset(self):
-        self.dice_sum.zero_()
-        self.micro.zero_()
+        # the next add() adopts its results instead of accumulating into
+        # zeroed tables (no memset / add kernels for a one-chunk pass)
+        self._fresh = True
         self.n_img = 0
 
     # -- device-resident chunk ------------------------------------------------
@@ -104,8 +112,12 @@ class SegSearch:
             self.kernel_events.append(ev)
         dsum, micro = ops.dice_search(hist, self.min_areas, self.empty_one,
                                       self.eps)
-        self.dice_sum += dsum
-        self.micro += micro
+        if self._fresh:
+            self.dice_sum, self.micro = dsum, micro
+            self._fresh = False
+        else:
+            self.dice_sum += dsum
+            self.micro += micro
         self.n_img += hist.shape[0]
         return hist
 
@@ -151,8 +163,16 @@ class SegSearch:
         """Combine ranks (``combine_ranks``) and search the grid."""
         dice_sum, micro, n_img = combine_ranks(self.dice_sum, self.micro,
                                                self.n_img, group)
-        score = (dice_sum / max(n_img, 1)).cpu().numpy()      # [C, B, A]
-        m = micro.cpu().numpy()
+        # one device->host copy for everything the host-side search needs
+        packed = torch.cat([
+            dice_sum.reshape(-1).view(torch.int64), micro.reshape(-1),
+            torch.as_tensor(n_img, dtype=torch.int64,
+                            device=micro.device).reshape(1)]).cpu().numpy()
+        nd = dice_sum.numel()
+        n_img = int(packed[-1])
+        score = packed[:nd].view(np.float64).reshape(dice_sum.shape) / \
+            max(n_img, 1)                                     # [C, B, A]
+        m = packed[nd:-1].reshape(micro.shape)
         b = len(self.thr)
         t_sum, p_sum, i_sum = m[:, 0], m[:, 1:1 + b], m[:, 1 + b:]
         best = []

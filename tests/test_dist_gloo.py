@@ -31,7 +31,7 @@ def _worker(rank, world, port, out_dir):
     tot, m, n = combine_ranks(dsum, micro, hi - lo)
     np.save(os.path.join(out_dir, f'dice_{rank}.npy'), tot.numpy())
     np.save(os.path.join(out_dir, f'micro_{rank}.npy'), m.numpy())
-    np.save(os.path.join(out_dir, f'n_{rank}.npy'), np.array([n, lo, hi]))
+    np.save(os.path.join(out_dir, f'n_{rank}.npy'), np.array([int(n), lo, hi]))
     dist.destroy_process_group()
 
 
