@@ -97,10 +97,15 @@ dice_search_kernel(const __grid_constant__ SearchArgs a) {
       const unsigned long long up = S[j + 1];  // bins above threshold j
       const unsigned p = (unsigned)(up >> 32), i = (unsigned)up;
       const unsigned t = (unsigned)S[0];
+      // One divide per (plane, threshold): the min-area rule only switches
+      // between the full dice and the dice of an emptied prediction
+      // (dice.py:13-18), so the candidates differ by a select.
+      const double d_full = dice_point(t, p, i, 0, a.empty_one, a.eps);
+      const double d_zero = (a.empty_one && t == 0) ? 1.0 : 0.0;
 #pragma unroll
       for (int m = 0; m < MLC_MAX_AREAS; ++m)
         if (m < a.A)
-          acc[m] += dice_point(t, p, i, area[m], a.empty_one, a.eps);
+          acc[m] += (area[m] > 0 && p < (unsigned)area[m]) ? d_zero : d_full;
       sumP += p;
       sumI += i;
       if (j == 0) sumT += t;
