@@ -381,6 +381,30 @@ def test_dice_search_matches_dice_numpy_loop(ops):
     np.testing.assert_allclose(d2.cpu().numpy(), t2.sum(axis=0), rtol=1e-13)
 
 
+def test_min_area_boundary_and_empty_rules(ops):
+    """P == min_area - 1 / min_area / min_area + 1 at the chosen threshold,
+    with and without ground truth, empty_one on and off (dice.py:13-18)."""
+    h, w = 16, 32
+    thr = np.array([0.5], np.float32)
+    for n_pred in (0, 6, 7, 8):
+        for n_gt in (0, 5):
+            prob = np.zeros((h, w), np.float32)
+            prob.ravel()[:n_pred] = 0.9
+            gt = np.zeros((h, w), np.uint8)
+            gt.ravel()[3:3 + n_gt] = 1
+            hist = ops.seg_hist([torch.from_numpy(prob)[None, None].to(DEV)],
+                                torch.from_numpy(gt)[None, None].to(DEV), thr,
+                                activation=None)
+            for area in (0, 7, 8):
+                for eo in (True, False):
+                    got = ops.plane_dice(hist, [0], [area], empty_one=eo)
+                    ref = oracle.plane_dice(gt.astype(np.float32), prob,
+                                            np.float32(0.5), area, eo)
+                    assert float(got[0, 0]) == float(ref), (n_pred, n_gt, area, eo)
+                    ds, _ = ops.dice_search(hist, [area], empty_one=eo)
+                    assert float(ds[0, 0, 0]) == float(ref)
+
+
 def test_dice_search_many_images_is_reproducible(ops):
     n, c = 700, 4
     rng = np.random.default_rng(1)
