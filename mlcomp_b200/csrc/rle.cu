@@ -246,21 +246,29 @@ rle_kernel(const __grid_constant__ RleArgs a) {
     const int q1 = min(nW, q0 + per);
     const int xq0 = q0 / Hw, ybq0 = q0 - xq0 * Hw;
     int n_starts = 0, n_px = 0, last_start = 0;
+    // Sliding window over the chunk: one LDS per word; the edge bit of the
+    // previous logical word (its top valid bit) is carried in a register.
+    uint32_t pbit0 = 0;  // edge bit of the logical word before q0
+    if (q0 > 0 && q0 < nW) {
+      const int xp = ybq0 > 0 ? xq0 : xq0 - 1;
+      const int yp = ybq0 > 0 ? ybq0 - 1 : Hw - 1;
+      pbit0 = (bits[xp * Hp + yp] >> (yp == Hw - 1 ? hl : 31)) & 1u;
+    }
     uint32_t open0 = 0;  // a run is open across the start of my chunk
     {
       int x = xq0, yb = ybq0;
+      uint32_t pb = pbit0;
+      uint32_t w = q0 < q1 ? bits[x * Hp + yb] : 0u;
+      open0 = pb & w & 1u;
       for (int q = q0; q < q1; ++q) {
-        const int ad = x * Hp + yb;
-        const uint32_t w = bits[ad];
-        uint32_t prev = 0;
-        if (yb > 0) prev = bits[ad - 1] >> 31;
-        else if (x > 0) prev = (bits[ad - Hp + Hw - 1] >> hl) & 1u;
-        const uint32_t starts = w & ~((w << 1) | prev);
-        if (q == q0) open0 = prev & w & 1u;
+        const int top = yb == Hw - 1 ? hl : 31;
+        const uint32_t starts = w & ~((w << 1) | pb);
         n_starts += __popc(starts);
         n_px += __popc(w);
         if (starts) last_start = x * H + yb * 32 + 32 - __clz(starts);  // 1-based
+        pb = (w >> top) & 1u;
         if (++yb == Hw) { yb = 0; ++x; }
+        w = q + 1 < q1 ? bits[x * Hp + yb] : 0u;
       }
     }
     int tot_runs, tot_px;
@@ -288,18 +296,16 @@ rle_kernel(const __grid_constant__ RleArgs a) {
       int ei = my_first - (int)open0;  // runs ended before my chunk
       int cur = carry;                 // start of the currently open run
       int x = xq0, yb = ybq0;
+      uint32_t pb = pbit0;
+      uint32_t w = q0 < q1 ? bits[x * Hp + yb] : 0u;
       for (int q = q0; q < q1; ++q) {
-        const int ad = x * Hp + yb;
-        const uint32_t w = bits[ad];
-        uint32_t prev = 0, next = 0;
-        if (yb > 0) prev = bits[ad - 1] >> 31;
-        else if (x > 0) prev = (bits[ad - Hp + Hw - 1] >> hl) & 1u;
-        if (yb < Hw - 1) next = bits[ad + 1] & 1u;
-        else if (x < W - 1) next = bits[ad + Hp - (Hw - 1)] & 1u;
         const int top = yb == Hw - 1 ? hl : 31;
-        const uint32_t starts = w & ~((w << 1) | prev);
-        uint32_t ends = w & ~((w >> 1) | (next << top));
         const int pos0 = x * H + yb * 32 + 1;  // 1-based, column-major
+        if (++yb == Hw) { yb = 0; ++x; }
+        // next logical word (possibly the neighbour thread's first one)
+        const uint32_t wn = q + 1 < nW ? bits[x * Hp + yb] : 0u;
+        const uint32_t starts = w & ~((w << 1) | pb);
+        uint32_t ends = w & ~((w >> 1) | ((wn & 1u) << top));
         while (ends) {
           const int e = __ffs(ends) - 1;
           ends &= ends - 1;
@@ -308,7 +314,8 @@ rle_kernel(const __grid_constant__ RleArgs a) {
           out[ei++] = make_int2(st, pos0 + e - st + 1);
         }
         if (starts) cur = pos0 + 31 - __clz(starts);
-        if (++yb == Hw) { yb = 0; ++x; }
+        pb = (w >> top) & 1u;
+        w = wn;
       }
     }
     __syncthreads();
