@@ -41,6 +41,7 @@ extern "C" {
 /* activation: utils/torch.py:11-18 apply_activation */
 #define MLC_ACT_NONE    0
 #define MLC_ACT_SIGMOID 1
+#define MLC_ACT_SOFTMAX 2  /* over the class dim (dim 1) of each source */
 
 /* Composed inverse test-time transform of one source, i.e. what
  * TtaWrap.inverse (contrib/transform/tta.py:20-31) does to it:
@@ -94,8 +95,8 @@ int mlc_confusion(const void *preds_dev, int dtype, int64_t n, int n_cls,
  *               (contrib/dataset/segment.py:36-56 builds them as fp32)
  *   thr_host    [n_thr] fp32 ascending, n_thr <= MLC_MAX_THR
  *   lut_dev     NULL, or MLC_LUT_BYTES made by mlc_seg_lut_build with the
- *               same thr/act: enables the table path for a single
- *               untransformed fp16 source (results are identical).  Holds
+ *               same thr/act (NONE or SIGMOID): enables the table path for
+ *               a single untransformed fp16 source (results are identical).  Holds
  *               cnt(act(x)) for each of the 65 536 fp16 codes, then a
  *               2 048-entry summary of it (one entry per 32 codes)
  */

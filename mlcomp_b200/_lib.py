@@ -14,7 +14,7 @@ from . import build as _build
 MLC_OK = 0
 MLC_ERR_ARG, MLC_ERR_CUDA, MLC_ERR_UNSUPPORTED, MLC_ERR_CAPACITY = -1, -2, -3, -4
 MLC_F16, MLC_F32, MLC_U8 = 0, 1, 2
-MLC_ACT_NONE, MLC_ACT_SIGMOID = 0, 1
+MLC_ACT_NONE, MLC_ACT_SIGMOID, MLC_ACT_SOFTMAX = 0, 1, 2
 MLC_XF_HFLIP, MLC_XF_VFLIP, MLC_XF_TRANSPOSE = 1, 2, 4
 MLC_MAX_SOURCES, MLC_MAX_THR, MLC_MAX_AREAS = 32, 255, 8
 MLC_MAX_CLASSES_SEG = 64

@@ -116,7 +116,7 @@ __device__ __forceinline__ int block_excl_max(int v, int *warp_tot) {
   return max(before, lane ? up : 0);
 }
 
-template <typename T, bool CODE>
+template <typename T, bool CODE, bool SM>
 __global__ void __launch_bounds__(CODE ? 1024 : 512)
 rle_kernel(const __grid_constant__ RleArgs a) {
   // the code path is light on registers: twice the threads, twice the loads
@@ -193,8 +193,9 @@ rle_kernel(const __grid_constant__ RleArgs a) {
         } else {
           for (int r = 0; r < rows; ++r) {
             float p[8];
-            fused_prob8<T>(a.src, plane_off, H, W, yb * 32 + r, x0, nv, inner,
-                           a.act, p);
+            const PlaneCtx cx = {plane, a.n_planes, (long long)H * W, a.C};
+            fused_prob8<T, SM>(a.src, plane_off, cx, H, W, yb * 32 + r, x0, nv,
+                           inner, a.act, p);
 #pragma unroll
             for (int i = 0; i < 8; ++i)
               word[i] |= (uint32_t)(i < nv && p[i] >= thr) << r;
@@ -337,7 +338,8 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
                               void *stream) {
   MLC_REQUIRE(dtype == MLC_F16 || dtype == MLC_F32 || dtype == MLC_U8,
               "dtype %d is not MLC_F16/MLC_F32/MLC_U8", dtype);
-  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID,
+  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID ||
+                  act == MLC_ACT_SOFTMAX,
               "unknown activation code %d", act);
   MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && n_cls <= MLC_MAX_CLASSES_SEG &&
                   H >= 1 && W >= 1,
@@ -383,13 +385,18 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
               H, W, smem, kRleMaxSmem);
     return MLC_ERR_UNSUPPORTED;
   }
-  const bool code = dtype == MLC_F16 && n_src == 1 && a.src.any_xf == 0;
+  const bool code = dtype == MLC_F16 && n_src == 1 && a.src.any_xf == 0 &&
+                    act != MLC_ACT_SOFTMAX;
   a.vec_ok = code && ((uintptr_t)src_dev_ptrs[0] % 16) == 0 && (W % 8) == 0;
-  void (*kern)(RleArgs) = dtype == MLC_F16
-                              ? (code ? rle_kernel<__half, true>
-                                      : rle_kernel<__half, false>)
-                          : dtype == MLC_F32 ? rle_kernel<float, false>
-                                             : rle_kernel<uint8_t, false>;
+  const bool sm = act == MLC_ACT_SOFTMAX;
+  void (*kern)(RleArgs) =
+      dtype == MLC_F16
+          ? (code ? rle_kernel<__half, true, false>
+                  : sm ? rle_kernel<__half, false, true>
+                       : rle_kernel<__half, false, false>)
+      : dtype == MLC_F32 ? (sm ? rle_kernel<float, false, true>
+                               : rle_kernel<float, false, false>)
+                         : rle_kernel<uint8_t, false, false>;
   MLC_CUDA(cudaFuncSetAttribute(kern,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)kRleMaxSmem));

@@ -25,6 +25,7 @@ struct HistArgs {
   const uint8_t *lut;
   long long n_planes;
   long long plane_px;  // H*W
+  int n_cls;
   int H, W;            // geometry used for fetches (flat mode: 1, H*W)
   int B;
   int act;
@@ -70,7 +71,7 @@ __device__ __forceinline__ void flush_bins(uint32_t *cnt, int nbins,
 // table and costs one LDS.64 on a near-uniform one.
 // VEC: flat mode with 16-byte-aligned tensors - every full item after the
 // first of a plane is loaded with fused_flat8.
-template <typename T, bool VEC>
+template <typename T, bool VEC, bool SM>
 __global__ void __launch_bounds__(kHistThreads, 2)
 seg_hist_generic(const __grid_constant__ HistArgs a) {
   extern __shared__ uint32_t smem[];
@@ -119,12 +120,14 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
       }
       float p[8];
       uint2 g;
-      if (VEC && it > 0 && nv == 8) {
+      if (VEC && !SM && it > 0 && nv == 8) {
         fused_flat8<T>(a.src, plane_off + x0, a.act, p);
         mean8(p, a.src.n);
         g = ldg_stream8(gtp + x0);
       } else {
-        fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, inner, a.act, p);
+        const PlaneCtx cx = {plane, a.n_planes, a.plane_px, a.n_cls};
+        fused_prob8<T, SM>(a.src, plane_off, cx, a.H, a.W, y, x0, nv, inner,
+                           a.act, p);
         g = fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner);
       }
       int c[8];
@@ -734,13 +737,14 @@ struct ProbArgs {
   float *prob;
   long long n_planes;
   long long plane_px;
+  int n_cls;
   int H, W;
   int act;
   int items_per_row;
   long long items_per_plane;
 };
 
-template <typename T>
+template <typename T, bool SM>
 __global__ void __launch_bounds__(256)
 seg_prob_kernel(const __grid_constant__ ProbArgs a) {
   const long long total = a.n_planes * a.items_per_plane;
@@ -754,7 +758,9 @@ seg_prob_kernel(const __grid_constant__ ProbArgs a) {
     float p[8];
     const size_t plane_off = (size_t)plane * a.plane_px;
     const bool inner = plane > 0 && plane + 1 < a.n_planes;
-    fused_prob8<T>(a.src, plane_off, a.H, a.W, y, x0, nv, inner, a.act, p);
+    const PlaneCtx cx = {plane, a.n_planes, a.plane_px, a.n_cls};
+    fused_prob8<T, SM>(a.src, plane_off, cx, a.H, a.W, y, x0, nv, inner, a.act,
+                       p);
     float *o = a.prob + plane_off + (size_t)y * a.W + x0;
     for (int i = 0; i < nv; ++i) o[i] = p[i];
   }
@@ -814,7 +820,8 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   if (int rc = check_thr(thr_host, n_thr)) return rc;
   MLC_REQUIRE(dtype == MLC_F16 || dtype == MLC_F32,
               "dtype %d is not MLC_F16/MLC_F32", dtype);
-  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID,
+  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID ||
+                  act == MLC_ACT_SOFTMAX,
               "unknown activation code %d", act);
   MLC_REQUIRE(gt_dev && hist_dev, "gt_dev / hist_dev is null");
   MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && H >= 1 && W >= 1,
@@ -834,6 +841,7 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   a.lut = lut_dev;
   a.n_planes = (long long)n_img * n_cls;
   a.plane_px = (long long)H * W;
+  a.n_cls = n_cls;
   a.B = n_thr;
   a.act = act;
   a.flat = a.src.any_xf == 0;
@@ -847,7 +855,8 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   a.bias = 1.0f - thr_host[0] * a.scale;
 
   const int sms = sm_count();
-  const bool table = lut_dev && n_src == 1 && dtype == MLC_F16 && a.flat &&
+  const bool table = lut_dev && act != MLC_ACT_SOFTMAX && n_src == 1 &&
+                     dtype == MLC_F16 && a.flat &&
                      (a.plane_px % 8) == 0 &&
                      ((uintptr_t)src_dev_ptrs[0] % 16) == 0 &&
                      ((uintptr_t)gt_dev % 8) == 0;
@@ -930,12 +939,17 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
             (int)tab_smem));
         seg_hist_tab<false><<<tgrid, kTabThreads, tab_smem, st>>>(a);
       }
+    } else if (act == MLC_ACT_SOFTMAX) {
+      if (dtype == MLC_F16)
+        seg_hist_generic<__half, false, true><<<grid, kHistThreads, smem, st>>>(a);
+      else
+        seg_hist_generic<float, false, true><<<grid, kHistThreads, smem, st>>>(a);
     } else if (dtype == MLC_F16) {
-      if (vec) seg_hist_generic<__half, true><<<grid, kHistThreads, smem, st>>>(a);
-      else seg_hist_generic<__half, false><<<grid, kHistThreads, smem, st>>>(a);
+      if (vec) seg_hist_generic<__half, true, false><<<grid, kHistThreads, smem, st>>>(a);
+      else seg_hist_generic<__half, false, false><<<grid, kHistThreads, smem, st>>>(a);
     } else {
-      if (vec) seg_hist_generic<float, true><<<grid, kHistThreads, smem, st>>>(a);
-      else seg_hist_generic<float, false><<<grid, kHistThreads, smem, st>>>(a);
+      if (vec) seg_hist_generic<float, true, false><<<grid, kHistThreads, smem, st>>>(a);
+      else seg_hist_generic<float, false, false><<<grid, kHistThreads, smem, st>>>(a);
     }
     MLC_LAUNCH_CHECK("seg_hist_generic");
   }
@@ -948,7 +962,8 @@ extern "C" int mlc_seg_prob(const void *const *src_dev_ptrs,
                             float *prob_dev, void *stream) {
   MLC_REQUIRE(dtype == MLC_F16 || dtype == MLC_F32,
               "dtype %d is not MLC_F16/MLC_F32", dtype);
-  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID,
+  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID ||
+                  act == MLC_ACT_SOFTMAX,
               "unknown activation code %d", act);
   MLC_REQUIRE(prob_dev, "prob_dev is null");
   MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && H >= 1 && W >= 1,
@@ -962,6 +977,7 @@ extern "C" int mlc_seg_prob(const void *const *src_dev_ptrs,
   a.prob = prob_dev;
   a.n_planes = (long long)n_img * n_cls;
   a.plane_px = (long long)H * W;
+  a.n_cls = n_cls;
   a.H = H;
   a.W = W;
   a.act = act;
@@ -969,10 +985,14 @@ extern "C" int mlc_seg_prob(const void *const *src_dev_ptrs,
   a.items_per_plane = (long long)a.items_per_row * H;
   const long long total = a.n_planes * a.items_per_plane;
   const int grid = (int)min((total + 255) / 256, 32ll * sm_count());
-  if (dtype == MLC_F16)
-    seg_prob_kernel<__half><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
-  else
-    seg_prob_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (act == MLC_ACT_SOFTMAX) {
+    if (dtype == MLC_F16) seg_prob_kernel<__half, true><<<grid, 256, 0, st>>>(a);
+    else seg_prob_kernel<float, true><<<grid, 256, 0, st>>>(a);
+  } else {
+    if (dtype == MLC_F16) seg_prob_kernel<__half, false><<<grid, 256, 0, st>>>(a);
+    else seg_prob_kernel<float, false><<<grid, 256, 0, st>>>(a);
+  }
   MLC_LAUNCH_CHECK("seg_prob_kernel");
   return MLC_OK;
 }

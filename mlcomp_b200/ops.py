@@ -51,13 +51,15 @@ def _dtype_code(t):
 
 
 def activation_code(activation):
-    """utils/torch.py:11-18: falsy -> none, 'sigmoid'; anything else raises
-    with the reference's message ('softmax' over classes is not served by
-    the segmentation kernels)."""
+    """utils/torch.py:11-18: falsy -> none, 'sigmoid', 'softmax' (over the
+    class dim of every source); anything else raises the reference's
+    message."""
     if not activation:
         return MLC_ACT_NONE
     if activation == 'sigmoid':
         return MLC_ACT_SIGMOID
+    if activation == 'softmax':
+        return _lib.MLC_ACT_SOFTMAX
     raise Exception(f'unknown activation = {activation}')
 
 

@@ -75,8 +75,9 @@ class SegSearch:
         self.empty_one = empty_one
         self.eps = eps
         self.device = torch.device(device)
+        # the per-code table only exists for element-wise activations
         self.lut = ops.seg_lut(self.thr, activation, self.device) \
-            if use_lut else None
+            if use_lut and activation != 'softmax' else None
         b, a = len(self.thr), self.min_areas.shape[1]
         self.dice_sum = torch.zeros((self.n_cls, b, a), dtype=torch.float64,
                                     device=self.device)

@@ -44,8 +44,9 @@ def fuse(sources):
 
 def apply_activation(x, activation):
     """utils/torch.py:11-18 on the device: falsy -> x, 'sigmoid' through the
-    fused kernel, 'softmax' over dim 1 (classification only, torch op),
-    anything else raises the reference's error."""
+    fused kernel, 'softmax' over dim 1 (4-D segmentation logits through the
+    same kernel, 2-D classification logits through torch), anything else
+    raises the reference's error."""
     if not activation:
         return x
     if activation == 'sigmoid':
@@ -57,7 +58,10 @@ def apply_activation(x, activation):
         y = y.reshape(1, 1, -1, shape[-1]) if y.dim() != 4 else y
         return ops.seg_prob([y], None, 'sigmoid').reshape(shape)
     if activation == 'softmax':
-        return torch.softmax(x, 1)
+        if x.is_cuda and x.dim() == 4 and \
+                x.dtype in (torch.float16, torch.float32):
+            return ops.seg_prob([x.contiguous()], None, 'softmax')
+        return torch.softmax(x, 1)       # [n, C] classification logits
     raise Exception(f'unknown activation = {activation}')
 
 

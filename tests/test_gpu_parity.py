@@ -194,6 +194,48 @@ def test_fused_prob_matches_oracle(ops, dtype, tags, shape):
     assert np.array_equal(raw, oracle.fuse_probs(seen, tags, None))
 
 
+@pytest.mark.parametrize('dtype', [torch.float16, torch.float32])
+@pytest.mark.parametrize('shape,tags', [
+    ((3, 4, 32, 48), [[]]),
+    ((2, 5, 35, 53), [[], ['hflip'], ['vflip']]),
+    ((2, 2, 16, 16), [[], ['transpose']]),
+    ((1, 1, 8, 24), [[]]),
+])
+def test_softmax_activation(ops, dtype, shape, tags):
+    """apply_activation(x, 'softmax') = torch.softmax(x, 1) per source
+    (utils/torch.py:16-17), then inverse TTA and the mean, then the same
+    histogram / RLE machinery."""
+    n, c, h, w = shape
+    srcs, gt = synth_seg(n, c, h, w, seed=41 + c, dtype=dtype, n_src=len(tags))
+    seen = [forward_tta(s, t) for s, t in zip(srcs, tags)]
+    dev_src = [s.to(DEV) for s in seen]
+    got = ops.seg_prob(dev_src, xforms=tags, activation='softmax')
+    # torch on the device, same order of operations
+    acc = None
+    for s, t in zip(dev_src, tags):
+        q = oracle.tta_inverse(torch.softmax(s.float(), 1), t)
+        acc = q.clone() if acc is None else acc + q
+    dev = torch.div(acc, torch.full_like(acc, float(len(tags))))
+    d = ulp_diff(got.cpu().numpy(), dev.cpu().numpy())
+    assert d.max() <= 1, d.max()            # observed 0: same three steps
+    want = oracle.fuse_probs(seen, tags, 'softmax')
+    assert ulp_diff(got.cpu().numpy(), want).max() <= 8 * len(tags)
+    np.testing.assert_allclose(got.sum(dim=1).cpu().numpy(), 1.0, atol=1e-5)
+    thr = oracle.threshold_grid(100)
+    hist = ops.seg_hist(dev_src, gt.to(DEV), thr, xforms=tags,
+                        activation='softmax').cpu().numpy()
+    p = got.cpu().numpy()
+    for i in range(n):
+        for j in range(c):
+            assert np.array_equal(hist[i, j],
+                                  oracle.bin_counts(gt[i, j].numpy(), p[i, j], thr))
+    runs, off, cnt, _ = ops.rle_encode(dev_src, 0.4, 0, xforms=tags,
+                                       activation='softmax')
+    strings = ops.rle_strings(runs, off, cnt)
+    assert strings[0] == oracle.rle_submission(p[0, 0], 0.4)
+    assert strings[-1] == oracle.rle_submission(p[-1, -1], 0.4)
+
+
 def test_compose_tta_matches_inverse(ops):
     import itertools
     base = torch.arange(3 * 5, dtype=torch.float32).reshape(1, 1, 3, 5)
