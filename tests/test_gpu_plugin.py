@@ -81,6 +81,8 @@ def test_flip_tta_and_activation_dropins(golden_dir):
     lg = torch.randn(4, 3, 8, 8, device=DEV)
     assert torch.equal(apply_activation(lg, 'sigmoid'), torch.sigmoid(lg))
     assert apply_activation(lg, None) is lg
+    sm4 = apply_activation(lg, 'softmax')
+    assert (sm4 - torch.softmax(lg, 1)).abs().max() < 1e-6
     assert torch.equal(apply_activation(lg[:, :, 0, 0], 'softmax'),
                        torch.softmax(lg[:, :, 0, 0], 1))
     with pytest.raises(Exception, match='unknown activation = relu'):

@@ -155,6 +155,29 @@ def c4(n=2048):
            {'runs': n_runs, 'total_elems': int(total.item())})
 
 
+def c4s(n=512):
+    """C4 all the way to Python strings: encode + device formatting + D2H +
+    slicing (what Infer.submit needs), against mask2rle's 3.8 ms per plane."""
+    import time
+    c, h, w = 1, 1024, 1024
+    srcs, _ = synth(n, c, h, w, 1, 4, 0.78)
+    for _ in range(2):
+        runs, off, cnt, _a = ops.rle_encode(srcs, 0.5, 3500)
+        strs = ops.rle_strings(runs, off, cnt)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    runs, off, cnt, _a = ops.rle_encode(srcs, 0.5, 3500)
+    strs = ops.rle_strings(runs, off, cnt)
+    dt = time.perf_counter() - t0
+    chars = sum(len(x) for x in strs)
+    print(json.dumps({'config': 'C4 to strings: %d planes 1024x1024 -> rle '
+                      'pairs -> decimal text on device -> host str' % n,
+                      'ms_total': round(dt * 1e3, 2),
+                      'ms_per_plane': round(dt * 1e3 / n, 4),
+                      'chars': chars, 'runs': int(cnt.sum().item())}),
+          flush=True)
+
+
 if __name__ == '__main__':
     which = sys.argv[1:] or ['c1', 'c2g', 'c3', 'c4', 'c5']
     for k in which:
