@@ -386,6 +386,48 @@ def test_table_kernel_variants_agree(ops, monkeypatch):
         assert torch.equal(ops.seg_hist([x], g, thr, lut=lut), want), variant
 
 
+def test_table_path_without_activation(ops):
+    """activation=None on fp16 'probabilities': the per-code table must bin
+    the raw values."""
+    rng = np.random.default_rng(5)
+    p = torch.from_numpy(rng.random((2, 2, 64, 64)).astype(np.float32)).half()
+    g = torch.from_numpy((rng.random((2, 2, 64, 64)) < 0.5).astype(np.uint8))
+    thr = oracle.threshold_grid(100)
+    lut = ops.seg_lut(thr, activation=None)
+    a = ops.seg_hist([p.to(DEV)], g.to(DEV), thr, activation=None, lut=lut)
+    for i in range(2):
+        for j in range(2):
+            want = oracle.bin_counts(g[i, j].numpy(),
+                                     p[i, j].float().numpy(), thr)
+            assert np.array_equal(a[i, j].cpu().numpy(), want)
+
+
+def test_host_chunked_search_equals_device_search(ops):
+    """SegSearch.add_host (pinned buffers, copies overlapped with compute,
+    ragged last chunk) == SegSearch.add on the same data."""
+    from mlcomp_b200 import scoring
+    srcs, gt = synth_seg(11, 2, 64, 96, seed=88, n_src=2)
+    tags = [[], ['hflip']]
+    areas = [0, 20, 200]
+    a = scoring.SegSearch(2, min_areas=areas)
+    a.add([s.to(DEV) for s in srcs], gt.to(DEV), tags)
+    b = scoring.SegSearch(2, min_areas=areas)
+    b.add_host([s.pin_memory() for s in srcs], gt.pin_memory(), tags, chunk=4)
+    ra, rb = a.result(), b.result()
+    assert np.array_equal(ra['micro_P'], rb['micro_P'])
+    assert np.array_equal(ra['micro_I'], rb['micro_I'])
+    np.testing.assert_allclose(ra['score'], rb['score'], rtol=1e-12)
+    # chunking changes the fp64 summation order: indices equal, dice to 1e-12
+    for x, y in zip(ra['best'], rb['best']):
+        assert (x['threshold_index'], x['min_area']) == \
+            (y['threshold_index'], y['min_area'])
+        assert abs(x['dice'] - y['dice']) < 1e-12
+    assert ra['n_img'] == rb['n_img'] == 11
+    b.reset()
+    b.add_host([s.pin_memory() for s in srcs], gt.pin_memory(), tags, chunk=16)
+    np.testing.assert_allclose(b.result()['score'], ra['score'], rtol=1e-12)
+
+
 # ---------------------------------------------------------------- dice grid
 def test_dice_search_matches_dice_numpy_loop(ops):
     n, c, h, w = 5, 3, 24, 40
