@@ -203,6 +203,18 @@ int mlc_rle_format(const int32_t *runs_dev, const int64_t *off_dev,
                    int64_t capacity, int64_t *str_off_dev, int32_t *str_len_dev,
                    int64_t *total_dev, void *stream);
 
+/* Inverse of mlc_rle_encode, replacing rle2mask
+ * (contrib/transform/rle.py:16-31): column-major 1-based (start, length)
+ * pairs -> masks.  Used to turn the competition's RLE ground truth into the
+ * uint8 planes mlc_seg_hist reads.
+ *   runs_dev/off_dev/cnt_dev  as produced by mlc_rle_encode (or uploaded by
+ *               the caller after parsing the strings); off < 0 = empty plane;
+ *               runs may overlap and may run past the end (clipped)
+ *   mask_dev    [n_planes][H][W] uint8 {0,1}, overwritten */
+int mlc_rle_decode(const int32_t *runs_dev, const int64_t *off_dev,
+                   const int32_t *cnt_dev, int64_t n_planes, int H, int W,
+                   uint8_t *mask_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

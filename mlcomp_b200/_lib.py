@@ -54,6 +54,8 @@ SIGNATURES = {
     'mlc_rle_format': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
                                c_int64, c_void_p, c_void_p, c_void_p,
                                c_void_p]),
+    'mlc_rle_decode': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                               c_int, c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -39,4 +39,12 @@ def rle2mask(mask_rle, shape):
     return (np.cumsum(delta[:-1]) > 0).astype(np.uint8).reshape(shape).T
 
 
-__all__ = ['mask2rle', 'masks2rle', 'rle2mask']
+def rles2masks(strings, shape):
+    """Batched decoder on the device: list of RLE strings -> uint8 CUDA
+    tensor [len(strings), height, width]; ``shape`` = (width, height) as in
+    rle2mask."""
+    runs, off, cnt = ops.rle_parse(strings)
+    return ops.rle_decode(runs, off, cnt, int(shape[1]), int(shape[0]))
+
+
+__all__ = ['mask2rle', 'masks2rle', 'rle2mask', 'rles2masks']

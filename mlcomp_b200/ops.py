@@ -18,7 +18,7 @@ from ._lib import (MLC_ACT_NONE, MLC_ACT_SIGMOID, MLC_F16, MLC_F32, MLC_U8,
 __all__ = ['activation_code', 'compose_tta', 'confusion', 'seg_lut',
            'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
            'threshold_grid', 'counts_from_hist', 'rle_strings',
-           'rle_strings_host']
+           'rle_strings_host', 'rle_decode', 'rle_parse']
 
 
 def _stream():
@@ -357,3 +357,38 @@ def rle_strings_host(runs, off, cnt):
     cnt_h = cnt.cpu().numpy().ravel()
     return [' '.join(map(str, runs_h[o:o + 2 * k].tolist())) if k else ''
             for o, k in zip(off_h, cnt_h)]
+
+
+def rle_parse(strings, device='cuda'):
+    """Host side of decoding: split the reference's "start length ..."
+    strings (rle.py:22-26) into one int32 pair buffer + per-plane offsets /
+    counts on the device."""
+    arrays = [np.array(t.split(), dtype=np.int32) if t else
+              np.zeros(0, np.int32) for t in strings]
+    for a in arrays:
+        if a.size % 2:
+            raise ValueError('an RLE string needs an even number of values')
+    cnt = np.array([a.size // 2 for a in arrays], dtype=np.int32)
+    off = np.concatenate([[0], np.cumsum(2 * cnt.astype(np.int64))[:-1]]) \
+        if len(arrays) else np.zeros(0, np.int64)
+    flat = np.concatenate(arrays) if arrays else np.zeros(0, np.int32)
+    dev = torch.device(device)
+    return (torch.from_numpy(np.ascontiguousarray(flat)).to(dev),
+            torch.from_numpy(np.ascontiguousarray(off, dtype=np.int64)).to(dev),
+            torch.from_numpy(cnt).to(dev))
+
+
+def rle_decode(runs, off, cnt, h, w):
+    """(start, length) pairs -> uint8 masks [planes, h, w] on the device
+    (mlc_rle_decode): rle2mask for a whole set in one launch."""
+    lib = _lib.load()
+    dev = off.device
+    planes = off.numel()
+    if runs.numel() == 0:
+        runs = torch.zeros(2, dtype=torch.int32, device=dev)
+    out = torch.empty((planes, h, w), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.mlc_rle_decode(_ptr(runs.contiguous()), _ptr(off.contiguous()),
+                                 _ptr(cnt.contiguous()), planes, h, w,
+                                 _ptr(out), _stream()))
+    return out

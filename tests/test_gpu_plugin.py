@@ -60,6 +60,53 @@ def test_mask2rle_dropin_reproduces_reference_golden(golden_dir):
     assert got == want
 
 
+def test_rle_decode_on_device(golden_dir):
+    """mlc_rle_decode == rle2mask: the reference's golden strings, encoder
+    round trips on odd shapes, clipping, a plane too large for shared
+    memory."""
+    from mlcomp_b200 import ops
+    from mlcomp_b200.contrib.transform.rle import rles2masks
+    z = np.load(os.path.join(golden_dir, 'rle_masks.npz'))
+    rows = json.load(open(os.path.join(golden_dir, 'rle_rows.json')))
+    off = 0
+    by_shape = {}
+    for r in rows:
+        h, w = r['h'], r['w']
+        m = z['mask'][off:off + h * w].reshape(h, w)
+        off += h * w
+        by_shape.setdefault((h, w), []).append((r['rle'], m))
+    for (h, w), items in by_shape.items():
+        got = rles2masks([s for s, _ in items], (w, h)).cpu().numpy()
+        for k, (s, m) in enumerate(items):
+            assert np.array_equal(got[k], m), (h, w, k)
+            assert np.array_equal(got[k], oracle.rle_decode(s, (w, h)))
+    rng = np.random.default_rng(3)
+    for h, w in ((70, 45), (256, 320), (33, 1), (1, 65), (350, 525)):
+        masks = (rng.random((5, 1, h, w)) < 0.5).astype(np.uint8)
+        masks[0] = 0
+        masks[1] = 1
+        masks[2, 0, h // 2:, :] = 1
+        x = torch.from_numpy(masks).to(DEV)
+        runs, o, c, _ = ops.rle_encode([x], 0.5, 0, activation=None)
+        back = ops.rle_decode(runs, o.reshape(-1), c.reshape(-1), h, w)
+        assert torch.equal(back, x[:, 0])
+    # a run past the end is clipped like the reference's slice assignment
+    runs, o, c = ops.rle_parse(['3 100', '', '1 2 2 3'])
+    got = ops.rle_decode(runs, o, c, 4, 3).cpu().numpy()
+    assert np.array_equal(got[0], oracle.rle_decode('3 100', (3, 4)))
+    assert got[1].sum() == 0
+    assert np.array_equal(got[2], oracle.rle_decode('1 2 2 3', (3, 4)))
+    # 2048 x 2048: bit plane does not fit shared memory -> global path
+    big = torch.zeros((1, 1, 2048, 2048), dtype=torch.uint8, device=DEV)
+    big[0, 0, 100:1900, 7:2040:3] = 1
+    runs, o, c, _ = ops.rle_encode([big[:, :, :1024, :1024].contiguous()], 0.5,
+                                   0, activation=None)
+    small = ops.rle_decode(runs, o.reshape(-1), c.reshape(-1), 1024, 1024)
+    assert torch.equal(small[0], big[0, 0, :1024, :1024])
+    s = oracle.rle_encode(big[0, 0].cpu().numpy())
+    assert torch.equal(rles2masks([s], (2048, 2048))[0], big[0, 0])
+
+
 def test_flip_tta_and_activation_dropins(golden_dir):
     from mlcomp_b200.contrib.torch.tensors import flip
     from mlcomp_b200.contrib.transform.tta import TtaWrap
