@@ -279,7 +279,7 @@ def run_ours(args, cfg):
 
     # ---- parity of this very run against the oracle, on a subset -----------
     import oracle
-    sub = min(n_img, 8)
+    sub = min(n_img, 16)    # first 64 planes of the shard
     res = step()
     hist = ops.seg_hist([logits[:sub]], gt[:sub], thr, lut=search.lut)
     h = hist.cpu().numpy().astype(np.int64)
