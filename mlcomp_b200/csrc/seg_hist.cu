@@ -103,33 +103,8 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
     const long long i0 = (long long)sub * a.items_per_unit;
     const long long i1 = min(n_items, i0 + a.items_per_unit);
 
-    for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x) {
-      int y, x0, nv;
-      if (a.flat) {
-        y = 0;
-        x0 = it == 0 ? 0 : (int)(it * 8 - shift);
-        nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
-      } else if (it < a.full_items) {  // the W/8 full items of each row first
-        y = (int)((unsigned)it / (unsigned)a.items_per_row);
-        x0 = ((int)it - y * a.items_per_row) * 8;
-        nv = 8;
-      } else {  // then the H row tails together: warps do not mix the two
-        y = (int)(it - a.full_items);
-        x0 = a.items_per_row * 8;
-        nv = a.W & 7;
-      }
-      float p[8];
-      uint2 g;
-      if (VEC && !SM && it > 0 && nv == 8) {
-        fused_flat8<T>(a.src, plane_off + x0, a.act, p);
-        mean8(p, a.src.n);
-        g = ldg_stream8(gtp + x0);
-      } else {
-        const PlaneCtx cx = {plane, a.n_planes, a.plane_px, a.n_cls};
-        fused_prob8<T, SM>(a.src, plane_off, cx, a.H, a.W, y, x0, nv, inner,
-                           a.act, p);
-        g = fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner);
-      }
+    // bins of one item's eight probabilities -> the warp-lane counters
+    auto bin8 = [&](const float (&p)[8], const uint2 g, const int nv) {
       int c[8];
       bool ok = nv == 8;
 #pragma unroll
@@ -156,6 +131,51 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
           }
         }
       }
+    };
+    // one item through the bounds-checked loads (any mode, any alignment)
+    auto item_checked = [&](const long long it) {
+      int y, x0, nv;
+      if (a.flat) {
+        y = 0;
+        x0 = it == 0 ? 0 : (int)(it * 8 - shift);
+        nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
+      } else if (it < a.full_items) {  // the W/8 full items of each row first
+        y = (int)((unsigned)it / (unsigned)a.items_per_row);
+        x0 = ((int)it - y * a.items_per_row) * 8;
+        nv = 8;
+      } else {  // then the H row tails together: warps do not mix the two
+        y = (int)(it - a.full_items);
+        x0 = a.items_per_row * 8;
+        nv = a.W & 7;
+      }
+      float p[8];
+      const PlaneCtx cx = {plane, a.n_planes, a.plane_px, a.n_cls};
+      fused_prob8<T, SM>(a.src, plane_off, cx, a.H, a.W, y, x0, nv, inner,
+                         a.act, p);
+      bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner), nv);
+    };
+
+    if (VEC && !SM) {
+      // Aligned flat planes: every item but the plane's head (when the plane
+      // does not start on an 8-element boundary) and its partial tail is one
+      // 16-byte load per source and 8 label bytes, indexed in 32 bits.
+      const int f0 = shift ? 1 : 0;
+      const int f1 = (int)((a.plane_px + shift) >> 3);  // first non-full item
+      const int lo = max((int)i0, f0), hi = min((int)i1, f1);
+      for (int it = lo + (int)threadIdx.x; it < hi; it += blockDim.x) {
+        const int x0 = it * 8 - shift;
+        float p[8];
+        fused_flat8<T>(a.src, plane_off + x0, a.act, p);
+        mean8(p, a.src.n);
+        bin8(p, ldg_stream8(gtp + x0), 8);
+      }
+      if (threadIdx.x == 0 && f0 && i0 == 0) item_checked(0);
+      if (threadIdx.x == 32 && f1 >= f0 && f1 < n_items && f1 >= i0 &&
+          f1 < i1)
+        item_checked(f1);
+    } else {
+      for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x)
+        item_checked(it);
     }
     uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
     flush_bins(cnt, nbins, out, a.units_per_plane > 1);
