@@ -226,74 +226,7 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
     const long long i0 = (long long)sub * a.items_per_unit;
     const long long i1 = min(n_items, i0 + a.items_per_unit);
 
-    for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x) {
-      int y, x0, nv;
-      if (a.flat) {
-        y = 0;
-        x0 = it == 0 ? 0 : (int)(it * 8 - shift);
-        nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
-      } else if (it < a.full_items) {  // the W/8 full items of each row first
-        y = (int)((unsigned)it / (unsigned)a.items_per_row);
-        x0 = ((int)it - y * a.items_per_row) * 8;
-        nv = 8;
-      } else {  // then the H row tails together: warps do not mix the two
-        y = (int)(it - a.full_items);
-        x0 = a.items_per_row * 8;
-        nv = a.W & 7;
-      }
-      float p[8];
-      uint2 g;
-      if (VEC && it > 0 && nv == 8) {
-        // aligned flat item: one 128-bit load per source, 4 sources in flight
-        const size_t e0 = plane_off + x0;
-        for (int k0 = 0; k0 < S; k0 += 4) {
-          uint4 r[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (k0 + j < S)
-              r[j] = ldg_stream16(
-                  static_cast<const __half *>(a.src.ptr[k0 + j]) + e0);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (k0 + j < S) {
-              const uint32_t w[4] = {r[j].x, r[j].y, r[j].z, r[j].w};
-              float v[8];
-              act8_table(w, tab_sa, a.act, v);
-#pragma unroll
-              for (int i = 0; i < 8; ++i)
-                p[i] = (k0 + j == 0) ? v[i] : p[i] + v[i];
-            }
-          }
-        }
-        g = ldg_stream8(gtp + x0);
-      } else {
-        for (int k = 0; k < S; ++k) {
-          const __half *pl = static_cast<const __half *>(a.src.ptr[k]) +
-                             plane_off;
-          const int xf = a.src.xf[k];
-          float v[8];
-          bool done = false;
-          if (!(xf & MLC_XF_TRANSPOSE) && nv == 8) {
-            const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
-            const bool rev = (xf & MLC_XF_HFLIP) != 0;
-            const long long s0 =
-                (long long)ys * a.W + (rev ? a.W - 8 - x0 : x0);
-            if (inner || (s0 >= 8 && s0 + 16 <= a.plane_px)) {
-              uint32_t w[4];
-              window8_packed(pl + s0, rev, w);
-              act8_table(w, tab_sa, a.act, v);
-              done = true;
-            }
-          }
-          if (!done) {
-            fetch8<__half>(pl, xf, a.H, a.W, y, x0, nv, inner, v);
-            activate8(v, a.act);
-          }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) p[i] = k == 0 ? v[i] : p[i] + v[i];
-        }
-        g = fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner);
-      }
+    auto bin8 = [&](float (&p)[8], const uint2 g, const int nv) {
       mean8(p, S);
       int c[8];
       bool ok = nv == 8;
@@ -321,6 +254,90 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
           }
         }
       }
+    };
+    // one item through the window / bounds-checked loads (rows, flips, edges)
+    auto item_checked = [&](const long long it) {
+      int y, x0, nv;
+      if (a.flat) {
+        y = 0;
+        x0 = it == 0 ? 0 : (int)(it * 8 - shift);
+        nv = it == 0 ? min(8 - shift, a.W) : min(8, a.W - x0);
+      } else if (it < a.full_items) {  // the W/8 full items of each row first
+        y = (int)((unsigned)it / (unsigned)a.items_per_row);
+        x0 = ((int)it - y * a.items_per_row) * 8;
+        nv = 8;
+      } else {  // then the H row tails together: warps do not mix the two
+        y = (int)(it - a.full_items);
+        x0 = a.items_per_row * 8;
+        nv = a.W & 7;
+      }
+      float p[8];
+      for (int k = 0; k < S; ++k) {
+        const __half *pl = static_cast<const __half *>(a.src.ptr[k]) +
+                           plane_off;
+        const int xf = a.src.xf[k];
+        float v[8];
+        bool done = false;
+        if (!(xf & MLC_XF_TRANSPOSE) && nv == 8) {
+          const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+          const bool rev = (xf & MLC_XF_HFLIP) != 0;
+          const long long s0 =
+              (long long)ys * a.W + (rev ? a.W - 8 - x0 : x0);
+          if (inner || (s0 >= 8 && s0 + 16 <= a.plane_px)) {
+            uint32_t w[4];
+            window8_packed(pl + s0, rev, w);
+            act8_table(w, tab_sa, a.act, v);
+            done = true;
+          }
+        }
+        if (!done) {
+          fetch8<__half>(pl, xf, a.H, a.W, y, x0, nv, inner, v);
+          activate8(v, a.act);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) p[i] = k == 0 ? v[i] : p[i] + v[i];
+      }
+      bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner), nv);
+    };
+
+    if (VEC) {
+      // aligned flat planes: full items in a 32-bit-indexed loop, one 128-bit
+      // load per source with 4 sources in flight; head and tail items apart
+      const int f0 = shift ? 1 : 0;
+      const int f1 = (int)((a.plane_px + shift) >> 3);  // first non-full item
+      const int lo = max((int)i0, f0), hi = min((int)i1, f1);
+      for (int it = lo + (int)threadIdx.x; it < hi; it += blockDim.x) {
+        const int x0 = it * 8 - shift;
+        const size_t e0 = plane_off + x0;
+        float p[8];
+        for (int k0 = 0; k0 < S; k0 += 4) {
+          uint4 r[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (k0 + j < S)
+              r[j] = ldg_stream16(
+                  static_cast<const __half *>(a.src.ptr[k0 + j]) + e0);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (k0 + j < S) {
+              const uint32_t w[4] = {r[j].x, r[j].y, r[j].z, r[j].w};
+              float v[8];
+              act8_table(w, tab_sa, a.act, v);
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                p[i] = (k0 + j == 0) ? v[i] : p[i] + v[i];
+            }
+          }
+        }
+        bin8(p, ldg_stream8(gtp + x0), 8);
+      }
+      if (threadIdx.x == 0 && f0 && i0 == 0) item_checked(0);
+      if (threadIdx.x == 32 && f1 >= f0 && f1 < n_items && f1 >= i0 &&
+          f1 < i1)
+        item_checked(f1);
+    } else {
+      for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x)
+        item_checked(it);
     }
     uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
     flush_bins(cnt, nbins, out, a.units_per_plane > 1);
