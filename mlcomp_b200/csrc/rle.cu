@@ -29,7 +29,7 @@ struct RleArgs {
   long long n_planes;
   int C, H, W, Hw;
   int act;
-  int vec_ok;  // single source, 16-byte aligned, rows a multiple of 8 px
+  int vec_ok;  // fp16 sources 16-byte aligned, rows a multiple of 8 px
 };
 
 __device__ __forceinline__ int block_excl_scan(int v, int *warp_tot,
@@ -116,28 +116,142 @@ __device__ __forceinline__ int block_excl_max(int v, int *warp_tot) {
   return max(before, lane ? up : 0);
 }
 
-template <typename T, bool CODE, bool SM>
-__global__ void __launch_bounds__(CODE ? 1024 : 512)
+// BOUND (MODE 2): several fp16 sources and / or flips (TTA, ensembles), an
+// element-wise activation.  The mean of S activations is monotone in each of
+// them (fp32 add, multiply and divide round monotonically), so with x'_c the
+// smallest fp16 value for which S copies of act(x') average to >= thr
+// (bisection with the very arithmetic of fused_prob8):
+//   every source >= x'_c  =>  mean >= mean(act(x'_c) x S) >= thr      -> 1
+//   every source <  x'_c  =>  mean <= mean(act(pred x'_c) x S) < thr  -> 0
+// (NaN compares false: a pixel whose sources all fail is 0, as NaN >= thr
+// is.)  One packed fp16 compare per pixel pair and source decides the pixels
+// on which the variants agree; the others - the rims of the masks - are
+// collected as bits and evaluated exactly, one pixel at a time, afterwards.
+enum { kRleArith = 0, kRleCode = 1, kRleBound = 2 };
+
+// One source's share of a BOUND tile: bit r of wk[i] <- source pixel under
+// output pixel (y0 + r, x0 + i) >= x'_c, for the rows of `fastmask` (the
+// others stay 0).  Four rows are loaded before any is compared.  VEC: rows
+// are 16-byte aligned (W % 8 == 0, aligned tensors) - one 128-bit load per
+// row; otherwise five aligned words per row, shifted into place, for any
+// 2-byte alignment.  The 8-element window of an hflipped or partial item may
+// reach up to 8 elements into the neighbouring row: the caller keeps the
+// outermost rows of the tensor out of `fastmask`.
+template <bool VEC>
+__device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
+                                           int W, int y0, int x0,
+                                           uint32_t fastmask, __half2 t2,
+                                           uint32_t wk[8]) {
+  const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
+  const int xs = rev ? W - 8 - x0 : x0;
+  const int top = 32 - __clz(fastmask);  // rows beyond the last fast one
+  for (int r0 = 0; r0 < top; r0 += 4) {
+    uint32_t w[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int r = r0 + q;
+      const bool on = (fastmask >> r) & 1u;
+      const int ys = vf ? H - 1 - (y0 + r) : y0 + r;
+      const __half *p = plane + ((long long)ys * W + xs);
+      if (VEC) {
+        const uint4 v = on ? ldg_stream16(p) : make_uint4(0, 0, 0, 0);
+        w[q][0] = v.x; w[q][1] = v.y; w[q][2] = v.z; w[q][3] = v.w;
+      } else {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        const uint32_t *pw = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+        const uint32_t sh = (uint32_t)(a & 2) * 8;
+        uint32_t t[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) t[j] = on ? ldg_nc32(pw + j) : 0u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          w[q][j] = __funnelshift_r(t[j], t[j + 1], sh);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int r = r0 + q;
+      const uint32_t bit = ((fastmask >> r) & 1u) << r;
+      uint32_t u[4] = {w[q][0], w[q][1], w[q][2], w[q][3]};
+      if (rev) {
+        const uint32_t r0_ = prmt32(u[3], 0u, 0x1032u),
+                       r1_ = prmt32(u[2], 0u, 0x1032u),
+                       r2_ = prmt32(u[1], 0u, 0x1032u),
+                       r3_ = prmt32(u[0], 0u, 0x1032u);
+        u[0] = r0_; u[1] = r1_; u[2] = r2_; u[3] = r3_;
+      }
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const uint32_t m =
+            __hge2_mask(*reinterpret_cast<const __half2 *>(&u[h]), t2);
+        wk[2 * h] |= prmt32(m, 0u, 0x0000u) & bit;
+        wk[2 * h + 1] |= prmt32(m, 0u, 0x2222u) & bit;
+      }
+    }
+  }
+}
+
+// exact fused probability of ONE pixel: the scalar twin of fused_prob8 for
+// sources without transposes
+__device__ __forceinline__ float fused_prob1(const SrcSet &s, size_t plane_off,
+                                             int H, int W, int y, int x,
+                                             int act) {
+  float p = 0.f;
+  for (int k0 = 0; k0 < s.n; k0 += 4) {
+    float v[4];  // up to four sources' loads in flight together
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (k0 + j < s.n) {
+        const int xf = s.xf[k0 + j];
+        const int ys = (xf & MLC_XF_VFLIP) ? H - 1 - y : y;
+        const int xs = (xf & MLC_XF_HFLIP) ? W - 1 - x : x;
+        v[j] = __half2float(static_cast<const __half *>(
+            s.ptr[k0 + j])[plane_off + (size_t)ys * W + xs]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (k0 + j < s.n) {
+        float t = v[j];
+        if (act == MLC_ACT_SIGMOID)
+          t = t >= -86.0f ? sigmoid_in_range(t) : activate(t, act);
+        p = k0 + j == 0 ? t : p + t;
+      }
+    }
+  }
+  float q[8] = {p, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  mean8(q, s.n);
+  return q[0];
+}
+
+template <typename T, int MODE, bool SM>
+__global__ void __launch_bounds__((MODE == 1) ? 1024 : 512)
 rle_kernel(const __grid_constant__ RleArgs a) {
   // the code path is light on registers: twice the threads, twice the loads
   // in flight per SM (one CTA per SM when the bit plane is 128 KiB)
+  constexpr bool CODE = MODE == kRleCode;
+  constexpr bool BOUND = MODE == kRleBound;
   constexpr int kRleThreads = CODE ? 1024 : 512;
   extern __shared__ uint32_t bits[];  // [W][Hw]
   __shared__ int warp_tot[kRleThreads / 32];
   __shared__ long long s_base;
   __shared__ uint32_t key_thr[MLC_MAX_CLASSES_SEG];
-  if (CODE) {
+  if (CODE || BOUND) {
     if ((int)threadIdx.x < a.C) {
       const float thr = a.thr[threadIdx.x];
-      // smallest key in [key(-inf), key(+inf)] whose value passes; one past
-      // +inf if none does
+      // smallest key in [key(-inf), key(+inf)] whose value passes (as S equal
+      // sources); one past +inf if none does
       uint32_t lo = kKeyNegInf, hi = kKeyPosInf + 1;
       while (lo < hi) {
         const uint32_t mid = (lo + hi) >> 1;
         const uint32_t code = mid ^ ((mid & 0x8000u) ? 0x8000u : 0xFFFFu);
         const float x =
             __half2float(__ushort_as_half((unsigned short)code));
-        if (activate(x, a.act) >= thr) hi = mid;
+        const float v = activate(x, a.act);
+        float q[8] = {v, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int k = 1; k < a.src.n; ++k) q[0] = q[0] + v;
+        mean8(q, a.src.n);
+        if (q[0] >= thr) hi = mid;
         else lo = mid + 1;
       }
       key_thr[threadIdx.x] = lo;
@@ -189,6 +303,72 @@ rle_kernel(const __grid_constant__ RleArgs a) {
           if (any) {
             if (raw) code_rows<true>(row0, W, rows, sub, lim_lo, lim_hi, word);
             else code_rows<false>(row0, W, rows, sub, lim_lo, lim_hi, word);
+          }
+        } else if (BOUND) {
+          const uint32_t kc = key_thr[c];
+          if (kc <= kKeyPosInf) {
+            const uint32_t xc = kc ^ ((kc & 0x8000u) ? 0x8000u : 0xFFFFu);
+            const uint32_t xc2 = xc | (xc << 16);
+            const __half2 t2 = *reinterpret_cast<const __half2 *>(&xc2);
+            // rows whose windows stay inside the tensor for every flip
+            const uint32_t valid = rows == 32 ? ~0u : (1u << rows) - 1u;
+            uint32_t fastmask = valid;
+            if (!inner) {
+              if (yb == 0) fastmask &= ~1u;
+              if (yb == Hw - 1) fastmask &= ~(1u << hl);
+            }
+            uint32_t any[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) word[i] = fastmask;
+            if (fastmask) {
+              for (int k = 0; k < a.src.n; ++k) {
+                uint32_t wk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                const __half *pl =
+                    static_cast<const __half *>(a.src.ptr[k]) + plane_off;
+                if (a.vec_ok)
+                  bound_rows<true>(pl, a.src.xf[k], H, W, yb * 32, x0,
+                                   fastmask, t2, wk);
+                else
+                  bound_rows<false>(pl, a.src.xf[k], H, W, yb * 32, x0,
+                                    fastmask, t2, wk);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  word[i] &= wk[i];
+                  any[i] |= wk[i];
+                }
+              }
+            }
+            // undecided: the sources disagree, or the row was not compared
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              any[i] = i < nv ? (any[i] | (valid & ~fastmask)) : 0u;
+              if (i >= nv) word[i] = 0u;
+            }
+            // Undecided pixels (sources disagree, or not compared): exact,
+            // one pixel per lane and turn - ONE copy of the evaluation, each
+            // lane walking its own list whatever the column.
+#pragma unroll
+            for (int i = 0; i < 8; ++i) any[i] &= ~word[i];
+            while (true) {
+              int i = -1;
+              uint32_t m = 0;
+#pragma unroll
+              for (int j = 7; j >= 0; --j)
+                if (any[j]) {
+                  i = j;
+                  m = any[j];
+                }
+              if (i < 0) break;
+              const int r = __ffs(m) - 1;
+              const bool pass = fused_prob1(a.src, plane_off, H, W,
+                                            yb * 32 + r, x0 + i, a.act) >= thr;
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (j == i) {
+                  any[j] = m & (m - 1);
+                  if (pass) word[j] |= 1u << r;
+                }
+            }
           }
         } else {
           for (int r = 0; r < rows; ++r) {
@@ -327,6 +507,16 @@ rle_kernel(const __grid_constant__ RleArgs a) {
 
 using namespace mlc;
 
+// MLC_RLE_ARITH=1 keeps multi-source planes on the all-arithmetic path (A/B
+// measurements; results are identical).
+static bool arith_only() {
+  static const bool v = [] {
+    const char *e = getenv("MLC_RLE_ARITH");
+    return e && e[0] == '1';
+  }();
+  return v;
+}
+
 extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
                               const int32_t *xform, int n_src, int dtype,
                               int64_t n_img, int n_cls, int H, int W,
@@ -387,16 +577,23 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   }
   const bool code = dtype == MLC_F16 && n_src == 1 && a.src.any_xf == 0 &&
                     act != MLC_ACT_SOFTMAX;
-  a.vec_ok = code && ((uintptr_t)src_dev_ptrs[0] % 16) == 0 && (W % 8) == 0;
+  bool aligned = (W % 8) == 0;
+  for (int k = 0; k < n_src; ++k)
+    aligned = aligned && ((uintptr_t)src_dev_ptrs[k] % 16) == 0;
+  a.vec_ok = dtype == MLC_F16 && aligned;
   const bool sm = act == MLC_ACT_SOFTMAX;
+  // several sources / flips without a transpose: bounded by packed compares
+  const bool bound = dtype == MLC_F16 && !code && !sm && W >= 8 &&
+                     !(a.src.any_xf & MLC_XF_TRANSPOSE) && !arith_only();
   void (*kern)(RleArgs) =
       dtype == MLC_F16
-          ? (code ? rle_kernel<__half, true, false>
-                  : sm ? rle_kernel<__half, false, true>
-                       : rle_kernel<__half, false, false>)
-      : dtype == MLC_F32 ? (sm ? rle_kernel<float, false, true>
-                               : rle_kernel<float, false, false>)
-                         : rle_kernel<uint8_t, false, false>;
+          ? (code ? rle_kernel<__half, kRleCode, false>
+                  : bound ? rle_kernel<__half, kRleBound, false>
+                          : sm ? rle_kernel<__half, kRleArith, true>
+                               : rle_kernel<__half, kRleArith, false>)
+      : dtype == MLC_F32 ? (sm ? rle_kernel<float, kRleArith, true>
+                               : rle_kernel<float, kRleArith, false>)
+                         : rle_kernel<uint8_t, kRleArith, false>;
   MLC_CUDA(cudaFuncSetAttribute(kern,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)kRleMaxSmem));

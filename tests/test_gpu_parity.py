@@ -522,6 +522,13 @@ def test_dice_search_many_images_is_reproducible(ops):
     ((2, 1, 33, 300), [[]]),
     ((2, 3, 1, 40), [[]]),
     ((2, 3, 40, 1), [[]]),
+    # several sources / flips: the bounded-compare path (rle.cu, MODE 2)
+    ((2, 2, 64, 96), [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]),
+    ((2, 2, 40, 50), [[], [], []]),
+    ((1, 3, 67, 72), [['hflip']]),
+    ((2, 1, 33, 41), [['vflip'], [], ['vflip', 'hflip'], [], ['hflip']]),
+    ((1, 1, 3, 8), [[], ['vflip']]),
+    ((1, 2, 50, 7), [[], ['hflip']]),
 ])
 def test_rle_matches_mask2rle(ops, dtype, shape, tags):
     n, c, h, w = shape
@@ -541,6 +548,44 @@ def test_rle_matches_mask2rle(ops, dtype, shape, tags):
             assert got[k] == want, (i, j)
             assert int(area[i, j]) == int((prob[i, j] >= thr[j]).sum())
             k += 1
+
+
+@pytest.mark.parametrize('activation', ['sigmoid', None])
+def test_rle_bounded_path_special_values_and_thresholds(ops, activation):
+    """Multi-source fp16 planes with NaN / +-inf / +-0 sprinkled in and
+    thresholds from below 0 to above 1: the packed-compare decisions plus
+    the exact pass must equal (fused prob >= thr) everywhere."""
+    rng = np.random.default_rng(5)
+    n, c, h, w = 2, 4, 37, 64
+    tags = [[], ['hflip'], ['vflip']]
+    srcs = []
+    for k in range(3):
+        x = rng.normal(0, 3, (n, c, h, w)).astype(np.float16)
+        sp = rng.random((n, c, h, w))
+        x[sp < 0.01] = np.nan
+        x[(sp >= 0.01) & (sp < 0.02)] = np.inf
+        x[(sp >= 0.02) & (sp < 0.03)] = -np.inf
+        x[(sp >= 0.03) & (sp < 0.04)] = -0.0
+        x[(sp >= 0.04) & (sp < 0.05)] = 0.0
+        if activation is None:
+            x = (1 / (1 + np.exp(-x.astype(np.float32)))).astype(np.float16)
+        srcs.append(torch.from_numpy(x).to(DEV))
+    for thr in ([-0.5, 0.0, 0.5, 1.0], [0.25, 0.75, 1.5, 1e-3]):
+        thr = np.asarray(thr, np.float32)
+        runs, off, cnt, area = ops.rle_encode(srcs, thr, 0, xforms=tags,
+                                              activation=activation)
+        got = ops.rle_strings(runs, off, cnt)
+        prob = ops.seg_prob(srcs, xforms=tags,
+                            activation=activation).cpu().numpy()
+        k = 0
+        for i in range(n):
+            for j in range(c):
+                with np.errstate(invalid='ignore'):
+                    mask = prob[i, j] >= thr[j]
+                assert got[k] == oracle.rle_encode(mask.astype(np.uint8)), \
+                    (i, j, thr[j])
+                assert int(area[i, j]) == int(mask.sum())
+                k += 1
 
 
 def test_rle_edge_masks_and_retry(ops):
