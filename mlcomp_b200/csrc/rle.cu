@@ -127,7 +127,7 @@ __device__ __forceinline__ int block_excl_max(int v, int *warp_tot) {
 // is.)  One packed fp16 compare per pixel pair and source decides the pixels
 // on which the variants agree; the others - the rims of the masks - are
 // collected as bits and evaluated exactly, one pixel at a time, afterwards.
-enum { kRleArith = 0, kRleCode = 1, kRleBound = 2 };
+enum { kRleArith = 0, kRleCode = 1, kRleBound = 2, kRleBoundVec = 3 };
 
 // One source's share of a BOUND tile: bit r of wk[i] <- source pixel under
 // output pixel (y0 + r, x0 + i) >= x'_c, for the rows of `fastmask` (the
@@ -225,13 +225,13 @@ __device__ __forceinline__ float fused_prob1(const SrcSet &s, size_t plane_off,
 }
 
 template <typename T, int MODE, bool SM>
-__global__ void __launch_bounds__((MODE == 1) ? 1024 : 512)
+__global__ void __launch_bounds__((MODE >= 1) ? 1024 : 512)
 rle_kernel(const __grid_constant__ RleArgs a) {
   // the code path is light on registers: twice the threads, twice the loads
   // in flight per SM (one CTA per SM when the bit plane is 128 KiB)
   constexpr bool CODE = MODE == kRleCode;
-  constexpr bool BOUND = MODE == kRleBound;
-  constexpr int kRleThreads = CODE ? 1024 : 512;
+  constexpr bool BOUND = MODE == kRleBound || MODE == kRleBoundVec;
+  constexpr int kRleThreads = (CODE || BOUND) ? 1024 : 512;
   extern __shared__ uint32_t bits[];  // [W][Hw]
   __shared__ int warp_tot[kRleThreads / 32];
   __shared__ long long s_base;
@@ -325,12 +325,8 @@ rle_kernel(const __grid_constant__ RleArgs a) {
                 uint32_t wk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 const __half *pl =
                     static_cast<const __half *>(a.src.ptr[k]) + plane_off;
-                if (a.vec_ok)
-                  bound_rows<true>(pl, a.src.xf[k], H, W, yb * 32, x0,
-                                   fastmask, t2, wk);
-                else
-                  bound_rows<false>(pl, a.src.xf[k], H, W, yb * 32, x0,
-                                    fastmask, t2, wk);
+                bound_rows<MODE == kRleBoundVec>(pl, a.src.xf[k], H, W, yb * 32,
+                                                 x0, fastmask, t2, wk);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                   word[i] &= wk[i];
@@ -588,7 +584,8 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   void (*kern)(RleArgs) =
       dtype == MLC_F16
           ? (code ? rle_kernel<__half, kRleCode, false>
-                  : bound ? rle_kernel<__half, kRleBound, false>
+                  : bound ? (a.vec_ok ? rle_kernel<__half, kRleBoundVec, false>
+                                      : rle_kernel<__half, kRleBound, false>)
                           : sm ? rle_kernel<__half, kRleArith, true>
                                : rle_kernel<__half, kRleArith, false>)
       : dtype == MLC_F32 ? (sm ? rle_kernel<float, kRleArith, true>
@@ -599,7 +596,7 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
                                 (int)kRleMaxSmem));
   const int per_sm = (int)max((size_t)1, min((size_t)4, (220 * 1024) / (smem + 1024)));
   const int grid = (int)min(a.n_planes, (long long)per_sm * sm_count());
-  kern<<<grid, code ? 1024 : 512, smem, st>>>(a);
+  kern<<<grid, (code || bound) ? 1024 : 512, smem, st>>>(a);
   MLC_LAUNCH_CHECK("rle_kernel");
   return MLC_OK;
 }

@@ -191,9 +191,14 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
 // pairs and the threshold table live in the hole of the table's layout.
 constexpr int kTabThreads = 1024;
 
-template <bool VEC>
+// MODE 0: any geometry (window loads); 1: flat planes, aligned tensors;
+// 2: flipped sources (no transpose) whose rows are a whole number of aligned
+// 16-byte items - the flips are index arithmetic on items, every load is one
+// 128-bit load and up to four sources are in flight together.
+template <int MODE>
 __global__ void __launch_bounds__(kTabThreads, 1)
 seg_hist_tab(const __grid_constant__ HistArgs a) {
+  constexpr bool VEC = MODE == 1;
   extern __shared__ __align__(16) unsigned char tab_smem[];
   const int B = a.B, nbins = B + 1;
   const float scale = a.scale, bias = a.bias;
@@ -335,6 +340,52 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
       if (threadIdx.x == 32 && f1 >= f0 && f1 < n_items && f1 >= i0 &&
           f1 < i1)
         item_checked(f1);
+    } else if (MODE == 2) {
+      const int ipr = a.items_per_row;  // W / 8, every item full
+      const int dy = (int)blockDim.x / ipr, dx = (int)blockDim.x - dy * ipr;
+      int it = (int)i0 + (int)threadIdx.x;
+      int y = it / ipr, xi = it - y * ipr;
+      for (; it < (int)i1; it += blockDim.x) {
+        float p[8];
+        for (int k0 = 0; k0 < S; k0 += 4) {
+          uint4 r[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (k0 + j < S) {
+              const int xf = a.src.xf[k0 + j];
+              const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+              const int xs = (xf & MLC_XF_HFLIP) ? ipr - 1 - xi : xi;
+              r[j] = ldg_stream16(
+                  static_cast<const __half *>(a.src.ptr[k0 + j]) + plane_off +
+                  (size_t)(ys * ipr + xs) * 8);
+            }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (k0 + j < S) {
+              uint32_t w[4] = {r[j].x, r[j].y, r[j].z, r[j].w};
+              if (a.src.xf[k0 + j] & MLC_XF_HFLIP) {  // reverse the 8 halves
+                const uint32_t t0 = prmt32(w[3], 0u, 0x1032u),
+                               t1 = prmt32(w[2], 0u, 0x1032u),
+                               t2 = prmt32(w[1], 0u, 0x1032u),
+                               t3 = prmt32(w[0], 0u, 0x1032u);
+                w[0] = t0; w[1] = t1; w[2] = t2; w[3] = t3;
+              }
+              float v[8];
+              act8_table(w, tab_sa, a.act, v);
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                p[i] = (k0 + j == 0) ? v[i] : p[i] + v[i];
+            }
+          }
+        }
+        bin8(p, ldg_stream8(gtp + (size_t)it * 8), 8);
+        xi += dx;
+        y += dy;
+        if (xi >= ipr) {
+          xi -= ipr;
+          ++y;
+        }
+      }
     } else {
       for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x)
         item_checked(it);
@@ -965,17 +1016,17 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
       // kernel is LSU-bound, not balance-bound (grids of 2x / 4x / one CTA
       // per unit measured within 1 %)
       const int tgrid = (int)min(n_units, (long long)sms);
-      if (vec) {
-        MLC_CUDA(cudaFuncSetAttribute(
-            seg_hist_tab<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-            (int)tab_smem));
-        seg_hist_tab<true><<<tgrid, kTabThreads, tab_smem, st>>>(a);
-      } else {
-        MLC_CUDA(cudaFuncSetAttribute(
-            seg_hist_tab<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-            (int)tab_smem));
-        seg_hist_tab<false><<<tgrid, kTabThreads, tab_smem, st>>>(a);
-      }
+      // flipped rows of whole aligned items (e.g. 256 x 1600 TTA)
+      bool vrows = !a.flat && !(a.src.any_xf & MLC_XF_TRANSPOSE) &&
+                   (W % 8) == 0 && ((uintptr_t)gt_dev % 8) == 0 &&
+                   a.items_per_plane < (1ll << 31) - kTabThreads;
+      for (int i = 0; i < n_src; ++i)
+        vrows = vrows && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
+      void (*tk)(HistArgs) = vec ? seg_hist_tab<1>
+                             : vrows ? seg_hist_tab<2> : seg_hist_tab<0>;
+      MLC_CUDA(cudaFuncSetAttribute(
+          tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tab_smem));
+      tk<<<tgrid, kTabThreads, tab_smem, st>>>(a);
     } else if (act == MLC_ACT_SOFTMAX) {
       if (dtype == MLC_F16)
         seg_hist_generic<__half, false, true><<<grid, kHistThreads, smem, st>>>(a);
