@@ -224,14 +224,17 @@ __device__ __forceinline__ float fused_prob1(const SrcSet &s, size_t plane_off,
   return q[0];
 }
 
-template <typename T, int MODE, bool SM>
-__global__ void __launch_bounds__((MODE >= 1) ? 1024 : 512)
+// NT threads: the integer paths (MODE >= 1) need <= 64 registers and run as
+// ONE 1024-thread CTA per SM when the bit plane is large, else as TWO
+// 512-thread CTAs whose phases overlap (one streams while the other scans).
+template <typename T, int MODE, bool SM, int NT>
+__global__ void __launch_bounds__(NT, (MODE >= 1 && NT == 512) ? 2 : 1)
 rle_kernel(const __grid_constant__ RleArgs a) {
   // the code path is light on registers: twice the threads, twice the loads
   // in flight per SM (one CTA per SM when the bit plane is 128 KiB)
   constexpr bool CODE = MODE == kRleCode;
   constexpr bool BOUND = MODE == kRleBound || MODE == kRleBoundVec;
-  constexpr int kRleThreads = (CODE || BOUND) ? 1024 : 512;
+  constexpr int kRleThreads = NT;
   extern __shared__ uint32_t bits[];  // [W][Hw]
   __shared__ int warp_tot[kRleThreads / 32];
   __shared__ long long s_base;
@@ -581,22 +584,30 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   // several sources / flips without a transpose: bounded by packed compares
   const bool bound = dtype == MLC_F16 && !code && !sm && W >= 8 &&
                      !(a.src.any_xf & MLC_XF_TRANSPOSE) && !arith_only();
+  // two 512-thread CTAs per SM when two bit planes (+ slack) fit
+  const bool wide = (code || bound) && smem > 100 * 1024;
+  const int nt = wide ? 1024 : 512;
   void (*kern)(RleArgs) =
       dtype == MLC_F16
-          ? (code ? rle_kernel<__half, kRleCode, false>
-                  : bound ? (a.vec_ok ? rle_kernel<__half, kRleBoundVec, false>
-                                      : rle_kernel<__half, kRleBound, false>)
-                          : sm ? rle_kernel<__half, kRleArith, true>
-                               : rle_kernel<__half, kRleArith, false>)
-      : dtype == MLC_F32 ? (sm ? rle_kernel<float, kRleArith, true>
-                               : rle_kernel<float, kRleArith, false>)
-                         : rle_kernel<uint8_t, kRleArith, false>;
+          ? (code ? (wide ? rle_kernel<__half, kRleCode, false, 1024>
+                          : rle_kernel<__half, kRleCode, false, 512>)
+             : bound
+                 ? (a.vec_ok
+                        ? (wide ? rle_kernel<__half, kRleBoundVec, false, 1024>
+                                : rle_kernel<__half, kRleBoundVec, false, 512>)
+                        : (wide ? rle_kernel<__half, kRleBound, false, 1024>
+                                : rle_kernel<__half, kRleBound, false, 512>))
+                 : sm ? rle_kernel<__half, kRleArith, true, 512>
+                      : rle_kernel<__half, kRleArith, false, 512>)
+      : dtype == MLC_F32 ? (sm ? rle_kernel<float, kRleArith, true, 512>
+                               : rle_kernel<float, kRleArith, false, 512>)
+                         : rle_kernel<uint8_t, kRleArith, false, 512>;
   MLC_CUDA(cudaFuncSetAttribute(kern,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)kRleMaxSmem));
   const int per_sm = (int)max((size_t)1, min((size_t)4, (220 * 1024) / (smem + 1024)));
   const int grid = (int)min(a.n_planes, (long long)per_sm * sm_count());
-  kern<<<grid, (code || bound) ? 1024 : 512, smem, st>>>(a);
+  kern<<<grid, nt, smem, st>>>(a);
   MLC_LAUNCH_CHECK("rle_kernel");
   return MLC_OK;
 }
