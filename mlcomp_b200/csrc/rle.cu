@@ -93,6 +93,44 @@ __device__ __forceinline__ void code_rows(const __half *row0, int W, int rows,
   }
 }
 
+// Conflict-free store of a lane's 8 column words: with an odd column pitch
+// the bank of (x, yb) is (x * Hp + yb) % 32, and lane l writing column
+// 8l + ((s + l/4) & 7) in step s makes the 32 banks of a step distinct
+// (8*Hp*l spreads l%4 over the multiples of 8, Hp*j spreads j over the
+// residues mod 8).  The register array is rotated by l/4 with three
+// conditional-swap stages instead of indexed dynamically.
+__device__ __forceinline__ void store_columns(uint32_t *bits, int Hp, int x0,
+                                              int yb, int nv, int lane,
+                                              uint32_t word[8]) {
+  const int rot = (lane >> 2) & 7;
+  if (rot & 4) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t t = word[i];
+      word[i] = word[i + 4];
+      word[i + 4] = t;
+    }
+  }
+  if (rot & 2) {
+    const uint32_t t0 = word[0], t1 = word[1];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) word[i] = word[i + 2];
+    word[6] = t0;
+    word[7] = t1;
+  }
+  if (rot & 1) {
+    const uint32_t t0 = word[0];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) word[i] = word[i + 1];
+    word[7] = t0;
+  }
+#pragma unroll
+  for (int s2 = 0; s2 < 8; ++s2) {  // word[s2] is column (s2 + rot) & 7
+    const int j = (s2 + rot) & 7;
+    if (j < nv) bits[(x0 + j) * Hp + yb] = word[s2];
+  }
+}
+
 // CODE: one untransformed fp16 source.  act(x) >= thr is then a statement
 // about the 16-bit code alone, and because the activation evaluated here is
 // non-decreasing over the fp16 values (all 63 488 finite codes, asserted by
@@ -380,39 +418,7 @@ rle_kernel(const __grid_constant__ RleArgs a) {
               word[i] |= (uint32_t)(i < nv && p[i] >= thr) << r;
           }
         }
-        // Conflict-free store: with an odd column pitch the bank of
-        // (x, yb) is (x * Hp + yb) % 32, and lane l writing column
-        // 8l + ((s + l/4) & 7) in step s makes the 32 banks of a step
-        // distinct (8*Hp*l spreads l%4 over the multiples of 8, Hp*j spreads
-        // j over the residues mod 8).  The register array is rotated by l/4
-        // with three conditional-swap stages instead of indexed dynamically.
-        const int rot = (lane >> 2) & 7;
-        if (rot & 4) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint32_t t = word[i];
-            word[i] = word[i + 4];
-            word[i + 4] = t;
-          }
-        }
-        if (rot & 2) {
-          const uint32_t t0 = word[0], t1 = word[1];
-#pragma unroll
-          for (int i = 0; i < 6; ++i) word[i] = word[i + 2];
-          word[6] = t0;
-          word[7] = t1;
-        }
-        if (rot & 1) {
-          const uint32_t t0 = word[0];
-#pragma unroll
-          for (int i = 0; i < 7; ++i) word[i] = word[i + 1];
-          word[7] = t0;
-        }
-#pragma unroll
-        for (int s2 = 0; s2 < 8; ++s2) {  // word[s2] is column (s2 + rot) & 7
-          const int j = (s2 + rot) & 7;
-          if (j < nv) bits[(x0 + j) * Hp + yb] = word[s2];
-        }
+        store_columns(bits, Hp, x0, yb, nv, lane, word);
       }
     }
     __syncthreads();
@@ -584,8 +590,11 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   // several sources / flips without a transpose: bounded by packed compares
   const bool bound = dtype == MLC_F16 && !code && !sm && W >= 8 &&
                      !(a.src.any_xf & MLC_XF_TRANSPOSE) && !arith_only();
-  // two 512-thread CTAs per SM when two bit planes (+ slack) fit
-  const bool wide = (code || bound) && smem > 100 * 1024;
+  // CODE: two 512-thread CTAs per SM when two bit planes (+ slack) fit, so
+  // that one streams while the other scans.  BOUND: one 1024-thread CTA
+  // (measured: the exact pass of a 512-thread pair costs more than the
+  // overlap gains - 2.60 vs 2.36 ms on 512 Severstal 4-flip images).
+  const bool wide = bound || (code && smem > 100 * 1024);
   const int nt = wide ? 1024 : 512;
   void (*kern)(RleArgs) =
       dtype == MLC_F16
@@ -593,10 +602,8 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
                           : rle_kernel<__half, kRleCode, false, 512>)
              : bound
                  ? (a.vec_ok
-                        ? (wide ? rle_kernel<__half, kRleBoundVec, false, 1024>
-                                : rle_kernel<__half, kRleBoundVec, false, 512>)
-                        : (wide ? rle_kernel<__half, kRleBound, false, 1024>
-                                : rle_kernel<__half, kRleBound, false, 512>))
+                        ? rle_kernel<__half, kRleBoundVec, false, 1024>
+                        : rle_kernel<__half, kRleBound, false, 1024>)
                  : sm ? rle_kernel<__half, kRleArith, true, 512>
                       : rle_kernel<__half, kRleArith, false, 512>)
       : dtype == MLC_F32 ? (sm ? rle_kernel<float, kRleArith, true, 512>
