@@ -113,6 +113,16 @@ def cpu_rate(pool, cores, planes_logit, planes_gt, cfg):
     return len(tasks) / dt, dt, np.stack(out)
 
 
+def cpu_model():
+    try:
+        for line in open('/proc/cpuinfo'):
+            if line.startswith('model name'):
+                return line.split(':', 1)[1].strip()
+    except OSError:
+        pass
+    return 'unknown'
+
+
 def make_pool():
     cores = os.cpu_count() or 1
     try:
@@ -366,7 +376,7 @@ def run_ours(args, cfg):
     # ---- CPU baseline on the same tensors (rank 0, N=1 semantics) -----------
     cpu = None
     if pool is not None:
-        n_cpu = max(16, cores)
+        n_cpu = max(64, 4 * cores)     # ~20-30 core-seconds of the oracle
         k_img = min(n_img, (n_cpu + c - 1) // c)
         lg_np = logits[:k_img].cpu().numpy().reshape(-1, cfg['H'], cfg['W'])
         gt_np = gt[:k_img].cpu().numpy().reshape(-1, cfg['H'], cfg['W'])
@@ -374,7 +384,17 @@ def run_ours(args, cfg):
         rate, dt, table = cpu_rate(pool, cores, lg_np[:n_cpu], gt_np[:n_cpu],
                                    cfg)
         pool.close()
+        # the reference's own setting: one process, one thread
+        # (worker/tasks.py:122-126), on the first two planes
+        import torch as _t
+        _t.set_num_threads(1)
+        t0 = time.perf_counter()
+        for i in range(min(2, n_cpu)):
+            _cpu_plane((lg_np[i], gt_np[i], cfg['bins'],
+                        list(cfg['min_areas'])))
+        single = min(2, n_cpu) / (time.perf_counter() - t0)
         cpu = {'value': rate, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+               'single_core_value': single, 'cpu_model': cpu_model(),
                'sample': '%d planes of this run\'s C2 data, one plane per '
                          'task over %d processes, %.1f s wall' %
                          (n_cpu, cores, dt)}

@@ -215,6 +215,33 @@ int mlc_rle_decode(const int32_t *runs_dev, const int64_t *off_dev,
                    const int32_t *cnt_dev, int64_t n_planes, int H, int W,
                    uint8_t *mask_dev, void *stream);
 
+/* Colour composite of predicted masks, replacing
+ * SegmentationReportBuilder.encode_pred (worker/reports/segmenation.py:71-80):
+ *   out[i][y][x][ch] = sum over classes of uint8(mask[i][c][y][x] * color[c][ch])
+ * with numpy's uint8 wrap-around in the product and in the running sum.
+ *   mask_dev    [n_img][n_cls][H][W] uint8 (the reference passes {0,1})
+ *   colors_host [n_cls][3] uint8, or NULL = (255, 255, 255) for every class,
+ *               the reference's default (:75-77)
+ *   out_dev     [n_img][H][W][3] uint8, overwritten */
+int mlc_mask_composite(const uint8_t *mask_dev, int64_t n_img, int n_cls, int H,
+                       int W, const uint8_t *colors_host, uint8_t *out_dev,
+                       void *stream);
+
+/* Class outlines over images, replacing SegmentationReportBuilder.plot_mask
+ * (worker/reports/segmenation.py:82-96: cv2.findContours(RETR_LIST,
+ * CHAIN_APPROX_NONE) per class, then cv2.polylines(img, contour, True, color,
+ * 2) on the POINT array of each contour).  Pixel-exact against OpenCV 4.13:
+ * a pixel takes the colour of the last class that has a contour point (a
+ * mask pixel with a zero 4-neighbour, frame = zero) on it or on one of its
+ * four 4-neighbours.
+ *   img_dev     [n_img][H][W][3] uint8, updated in place (grey images are
+ *               replicated to 3 channels by the caller, :83-84)
+ *   mask_dev    [n_img][n_cls][H][W] uint8, non-zero = set
+ *   colors_host [n_cls][3] uint8 or NULL = (0, 255, 0), the default (:92) */
+int mlc_mask_outline(uint8_t *img_dev, const uint8_t *mask_dev, int64_t n_img,
+                     int n_cls, int H, int W, const uint8_t *colors_host,
+                     void *stream);
+
 #ifdef __cplusplus
 }
 #endif

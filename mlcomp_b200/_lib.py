@@ -56,6 +56,10 @@ SIGNATURES = {
                                c_void_p]),
     'mlc_rle_decode': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int,
                                c_int, c_void_p, c_void_p]),
+    'mlc_mask_composite': (c_int, [c_void_p, c_int64, c_int, c_int, c_int,
+                                   c_void_p, c_void_p, c_void_p]),
+    'mlc_mask_outline': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int,
+                                 c_int, c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, 'csrc')
 LIB_DIR = os.path.join(HERE, 'lib')
 LIB = os.path.join(LIB_DIR, 'libmlcomp_b200.so')
 SOURCES = ['common.cu', 'confusion.cu', 'seg_hist.cu', 'dice_scan.cu',
-           'rle.cu', 'rle_format.cu', 'rle_decode.cu']
+           'rle.cu', 'rle_format.cu', 'rle_decode.cu', 'composite.cu']
 
 
 def nvcc_path():

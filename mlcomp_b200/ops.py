@@ -18,7 +18,8 @@ from ._lib import (MLC_ACT_NONE, MLC_ACT_SIGMOID, MLC_F16, MLC_F32, MLC_U8,
 __all__ = ['activation_code', 'compose_tta', 'confusion', 'seg_lut',
            'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
            'threshold_grid', 'counts_from_hist', 'rle_strings',
-           'rle_strings_host', 'rle_decode', 'rle_parse']
+           'rle_strings_host', 'rle_decode', 'rle_parse', 'mask_composite',
+           'mask_outline']
 
 
 def _stream():
@@ -392,3 +393,57 @@ def rle_decode(runs, off, cnt, h, w):
                                  _ptr(cnt.contiguous()), planes, h, w,
                                  _ptr(out), _stream()))
     return out
+
+
+def _palette(colors, n_cls, wrap):
+    """[n_cls][3] uint8 host array for the C ABI, or None for the reference's
+    default colour.  ``wrap``: numpy's modulo-256 of encode_pred's uint8
+    product; otherwise OpenCV's saturation of a colour scalar."""
+    if colors is None:
+        return None, None
+    c = np.asarray(colors, dtype=np.int64).reshape(-1, 3)[:n_cls]
+    if c.shape[0] < n_cls:
+        raise IndexError('list index out of range')   # colors[i], as there
+    c = (c % 256) if wrap else np.clip(c, 0, 255)
+    c = np.ascontiguousarray(c, dtype=np.uint8)
+    return c, c.ctypes.data_as(c_void_p)
+
+
+def mask_composite(mask, colors=None):
+    """encode_pred (worker/reports/segmenation.py:71-80) for a batch:
+    mask [n, C, H, W] uint8 on the device -> [n, H, W, 3] uint8 colour
+    composite (mlc_mask_composite).  ``colors`` None = white."""
+    lib = _lib.load()
+    _need_cuda(mask, 'mask', (torch.uint8,))
+    if mask.dim() != 4:
+        raise ValueError('mask must be [n, C, H, W]')
+    mask = mask.contiguous()
+    n, c, h, w = mask.shape
+    keep, ptr = _palette(colors, c, wrap=True)
+    out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=mask.device)
+    with torch.cuda.device(mask.device):
+        check(lib.mlc_mask_composite(_ptr(mask), n, c, h, w, ptr, _ptr(out),
+                                     _stream()))
+    return out
+
+
+def mask_outline(img, mask, colors=None):
+    """plot_mask (worker/reports/segmenation.py:82-96) for a batch: draws the
+    outline of every class plane of mask [n, C, H, W] uint8 over
+    img [n, H, W, 3] uint8 IN PLACE (mlc_mask_outline) and returns img.
+    ``colors`` None (or empty, as the reference tests truthiness) = green."""
+    lib = _lib.load()
+    _need_cuda(img, 'img', (torch.uint8,))
+    _need_cuda(mask, 'mask', (torch.uint8,))
+    if mask.dim() != 4 or img.dim() != 4 or img.shape[3] != 3 or \
+            tuple(img.shape[:3]) != (mask.shape[0],) + tuple(mask.shape[2:]):
+        raise ValueError('img must be [n, H, W, 3] and mask [n, C, H, W]')
+    if not img.is_contiguous():
+        raise ValueError('img must be contiguous (it is updated in place)')
+    mask = mask.contiguous()
+    n, c, h, w = mask.shape
+    keep, ptr = _palette(colors if colors else None, c, wrap=False)
+    with torch.cuda.device(mask.device):
+        check(lib.mlc_mask_outline(_ptr(img), _ptr(mask), n, c, h, w, ptr,
+                                   _stream()))
+    return img

@@ -1,11 +1,16 @@
 """``SegmentationReportBuilder`` - mlcomp/worker/reports/segmenation.py (sic).
 
-Same constructor (it calls ``create_base`` itself, :53) and methods.  Only
-``plot_count`` images are ever drawn, so compositing / contours / JPEG stay
-on the CPU with OpenCV as in the reference.
+Same constructor (it calls ``create_base`` itself, :53) and methods.  The
+colour composite and the class outlines are CUDA kernels (csrc/composite.cu,
+pixel-exact against the reference's NumPy / OpenCV 4.13 results); resizing,
+stacking and JPEG encoding of the at most ``plot_count`` tiles stay OpenCV
+host code as in the reference.
 """
 import numpy as np
+import torch
 import yaml
+
+from mlcomp_b200 import ops
 
 from mlcomp_b200.worker.reports.classification import resize_saving_ratio
 from mlcomp_b200.worker.store import (Report, ReportImg, ReportSeries,
@@ -14,6 +19,17 @@ from mlcomp_b200.worker.store import (Report, ReportImg, ReportSeries,
 
 def _host(x):
     return x.detach().cpu().numpy() if hasattr(x, 'detach') else np.asarray(x)
+
+
+def _DEV():
+    return torch.device('cuda', torch.cuda.current_device())
+
+
+def _device_u8(mask):
+    """mask.astype(np.uint8) of the reference (:86), as a device tensor."""
+    if not hasattr(mask, 'detach'):
+        mask = torch.from_numpy(np.ascontiguousarray(mask))
+    return mask.to(_DEV()).to(torch.uint8)
 
 
 class SegmentationReportBuilder:
@@ -45,27 +61,22 @@ class SegmentationReportBuilder:
         self.session.update()
 
     def encode_pred(self, mask):             # segmenation.py:71-80
-        mask = _host(mask)
-        res = np.zeros((*mask.shape[1:], 3), dtype=np.uint8)
-        for i, plane in enumerate(mask):
-            color = self.colors[i] if self.colors is not None else \
-                (255, 255, 255)
-            res += (plane[:, :, None] * np.asarray(color)).astype(np.uint8)
-        return res
+        """(C, H, W) mask -> (H, W, 3) uint8 composite, on the device
+        (mlc_mask_composite); returned as numpy for the stacking / JPEG
+        steps, which stay OpenCV host code as in the reference."""
+        m = _device_u8(mask)
+        return ops.mask_composite(m[None], self.colors)[0].cpu().numpy()
 
     def plot_mask(self, img, mask):          # segmenation.py:82-96
-        import cv2
-        img, mask = _host(img), _host(mask)
-        if img.ndim == 2:
-            img = cv2.cvtColor(img, cv2.COLOR_GRAY2BGR)
-        img = np.ascontiguousarray(img.astype(np.uint8))
-        for i, plane in enumerate(mask.astype(np.uint8)):
-            contours, _ = cv2.findContours(plane, cv2.RETR_LIST,
-                                           cv2.CHAIN_APPROX_NONE)
-            color = self.colors[i] if self.colors else (0, 255, 0)
-            for contour in contours:
-                cv2.polylines(img, contour, True, color, 2)
-        return img
+        """Outlines of every class over the image (mlc_mask_outline)."""
+        img = _host(img)
+        if img.ndim == 2:                    # cv2.COLOR_GRAY2BGR
+            img = np.repeat(img[:, :, None], 3, axis=2)
+        dev_img = torch.from_numpy(np.ascontiguousarray(
+            img.astype(np.uint8))).to(_DEV())
+        out = ops.mask_outline(dev_img[None], _device_u8(mask)[None],
+                               self.colors)
+        return out[0].cpu().numpy()
 
     def process_scores(self, scores):        # segmenation.py:98-112
         for key, item in self.layout_dict['items'].items():

@@ -11,7 +11,10 @@ vectors, known-answer tests or fixtures for this path (its only test file is
 the outputs of the reference's own functions, executed in the build container
 by ``tests/golden/make_golden.py`` (which loads ``dice.py``, ``rle.py`` and
 ``tensors.py`` from ``/root/reference`` by file path) and committed as
-``tests/golden/*.npz``.  ``tests/test_oracle_golden.py`` replays them.
+``tests/golden/*.npz``; ``tests/golden/make_golden_composite.py`` does the same
+for ``encode_pred`` / ``plot_mask`` (the two methods are cut out of
+``segmenation.py`` with ``ast`` and run with this container's OpenCV 4.13).
+``tests/test_oracle_golden.py`` replays them.
 """
 from .scoring import *  # noqa: F401,F403
 from .scoring import __all__  # noqa: F401

@@ -18,7 +18,7 @@ __all__ = [
     'classify_scores', 'classify_score_final', 'threshold_grid',
     'fuse_probs', 'plane_counts', 'bin_counts', 'dice_from_counts',
     'dice_grid_slow', 'dice_grid_fast', 'grid_scores', 'best_point',
-    'micro_stats', 'rle_submission', 'encode_pred', 'TTA_TAGS',
+    'micro_stats', 'rle_submission', 'encode_pred', 'plot_mask', 'TTA_TAGS',
 ]
 
 TTA_TAGS = ('hflip', 'vflip', 'transpose')
@@ -320,3 +320,33 @@ def encode_pred(mask, colors=None):
         col = colors[idx] if colors is not None else (255, 255, 255)
         res += (rgb * col).astype(np.uint8)
     return res
+
+
+def plot_mask(img, mask, colors=None):
+    """Outline of every class plane drawn over ``img`` (segmenation.py:82-96).
+
+    The reference calls ``cv2.findContours(plane, RETR_LIST,
+    CHAIN_APPROX_NONE)`` and then ``cv2.polylines(img, contour, True, color,
+    2)`` with the contour's POINT array, i.e. one degenerate poly-line per
+    contour point.  Restated without OpenCV (pinned to OpenCV 4.13 outputs in
+    tests/golden/composite.npz):
+      * the contour points of all borders are the mask pixels that have a
+        zero 4-neighbour (the frame counts as zero);
+      * a thickness-2 line from a point to itself paints that pixel and its
+        four 4-neighbours (clipped to the image);
+      * classes are drawn in order, later ones over earlier ones.
+    A 2-D image is first replicated to three channels (cv2.COLOR_GRAY2BGR).
+    """
+    img = np.asarray(img)
+    if img.ndim == 2:
+        img = np.repeat(img[:, :, None], 3, axis=2)
+    img = img.astype(np.uint8).copy()
+    for idx, plane in enumerate(np.asarray(mask).astype(np.uint8)):
+        m = plane != 0
+        p = np.pad(m, 1)
+        border = m & ~(p[:-2, 1:-1] & p[2:, 1:-1] & p[1:-1, :-2] & p[1:-1, 2:])
+        b = np.pad(border, 1)
+        stamp = (b[1:-1, 1:-1] | b[:-2, 1:-1] | b[2:, 1:-1] | b[1:-1, :-2] |
+                 b[1:-1, 2:])
+        img[stamp] = colors[idx] if colors else (0, 255, 0)
+    return img

@@ -4,6 +4,8 @@ practice bit-equal); probabilities: bit-equal to torch's CUDA sigmoid (the
 reference's own device path, utils/torch.py:15,24-25) and within 4 ulp of the
 CPU oracle's torch.sigmoid, with threshold-straddling pixels counted and
 bounded."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -648,3 +650,44 @@ def test_errors_are_loud(ops):
         ops.seg_prob([x], xforms=[['rot90']])
     with pytest.raises(TypeError, match='CUDA tensor'):
         ops.seg_prob([x.cpu()])
+
+
+# ---------------------------------------------------------------- composites
+def test_composite_and_outline_match_reference_fixtures(ops, golden_dir):
+    """mlc_mask_composite / mlc_mask_outline against the outputs of the
+    reference's own encode_pred / plot_mask (NumPy + OpenCV 4.13)."""
+    z = np.load(os.path.join(golden_dir, 'composite.npz'))
+    for k in range(int(z['n_cases'])):
+        colors = [tuple(int(v) for v in c) for c in z[f'colors_{k}']] or None
+        mask = torch.from_numpy(z[f'mask_{k}']).to(DEV)
+        img = torch.from_numpy(z[f'img_{k}']).to(DEV)
+        enc = ops.mask_composite(mask[None], colors)[0].cpu().numpy()
+        assert np.array_equal(enc, z[f'encode_{k}']), k
+        out = ops.mask_outline(img.clone()[None], mask[None], colors)
+        assert np.array_equal(out[0].cpu().numpy(), z[f'plot_{k}']), k
+
+
+@pytest.mark.parametrize('shape', [(3, 4, 37, 53), (2, 1, 64, 64),
+                                   (1, 6, 5, 3), (2, 3, 1, 9), (1, 2, 128, 96)])
+def test_composite_and_outline_match_oracle(ops, shape):
+    n, c, h, w = shape
+    rng = np.random.default_rng(h * w)
+    mask = (rng.random(shape) < 0.35).astype(np.uint8)
+    mask[0, 0] = 1                                   # a full plane
+    if c > 1:
+        mask[0, 1] = 0                               # an empty one
+    mask[-1, -1] *= rng.integers(1, 255, (h, w)).astype(np.uint8)  # not {0,1}
+    colors = [tuple(int(v) for v in rng.integers(0, 400, 3)) for _ in range(c)]
+    img = rng.integers(0, 256, (n, h, w, 3)).astype(np.uint8)
+    dm = torch.from_numpy(mask).to(DEV)
+    for pal in (colors, None):
+        enc = ops.mask_composite(dm, pal).cpu().numpy()
+        out = ops.mask_outline(torch.from_numpy(img).to(DEV), dm,
+                               pal).cpu().numpy()
+        sat = [tuple(min(v, 255) for v in col) for col in pal] if pal else None
+        for i in range(n):
+            assert np.array_equal(enc[i], oracle.encode_pred(mask[i], pal))
+            assert np.array_equal(out[i], oracle.plot_mask(img[i], mask[i],
+                                                           sat))
+    with pytest.raises(IndexError):
+        ops.mask_composite(dm, colors[:c - 1] if c > 1 else [])

@@ -105,3 +105,18 @@ def test_activation_errors_like_reference():
         oracle.activate(torch.zeros(2, 2), 'relu')
     with pytest.raises(Exception, match='Unknwon augmentation'):
         oracle.tta_inverse(torch.zeros(1, 1, 2, 2), ['rot90'])
+
+
+def test_composites_match_reference(golden_dir):
+    """encode_pred / plot_mask (segmenation.py:71-96) as run by
+    make_golden_composite.py with OpenCV 4.13."""
+    z = np.load(os.path.join(golden_dir, 'composite.npz'))
+    for k in range(int(z['n_cases'])):
+        colors = [tuple(int(v) for v in c) for c in z[f'colors_{k}']] or None
+        mask, img = z[f'mask_{k}'], z[f'img_{k}']
+        assert np.array_equal(oracle.encode_pred(mask, colors),
+                              z[f'encode_{k}']), k
+        assert np.array_equal(oracle.plot_mask(img, mask, colors),
+                              z[f'plot_{k}']), k
+        assert np.array_equal(oracle.plot_mask(img[:, :, 0], mask, colors),
+                              z[f'plot_gray_{k}']), k
