@@ -267,7 +267,10 @@ def run_ours(args, cfg):
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
-        dist.init_process_group('nccl', device_id=dev)
+        import datetime
+        # fail in minutes, not in NCCL's default 10, if the ranks ever diverge
+        dist.init_process_group('nccl', device_id=dev,
+                                timeout=datetime.timedelta(seconds=300))
     from mlcomp_b200 import ops, scoring
 
     n_img, c = args.images or cfg['n_img'], cfg['n_cls']
