@@ -44,6 +44,8 @@ def build(verbose=False, force=False):
            '-Xcompiler', '-fPIC,-O3,-Wall', '-cudart', 'static']
     if verbose:
         cmd += ['-Xptxas', '-v']
+    # A/B builds of compile-time knobs (e.g. MLC_EXTRA_NVCC='-DMLC_ROW_BATCH=2')
+    cmd += os.environ.get('MLC_EXTRA_NVCC', '').split()
     cmd += [os.path.join(CSRC, s) for s in SOURCES]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or res.returncode:

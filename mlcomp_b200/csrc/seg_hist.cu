@@ -190,13 +190,26 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
 // by HBM.  One 1024-thread CTA per SM; the counters, the (thr[c-1], thr[c])
 // pairs and the threshold table live in the hole of the table's layout.
 constexpr int kTabThreads = 1024;
+// Row mode (MODE 0): sources whose enclosing vectors are loaded before the
+// first is used, and the CTA size.  Measured on C3 (1024 x 4 x 350x525, 4
+// flips): 1 source / 1024 threads 3.01 ms; 2 sources / 1024 threads 4.63 ms
+// (spills at the 64-register cap); 4 sources / 512 threads (128 registers)
+// 3.57 ms; 2 / 512: 3.89 ms.  The word-load version before it: 3.15 ms.
+#ifndef MLC_ROW_BATCH
+#define MLC_ROW_BATCH 1
+#endif
+constexpr int kRowBatch = MLC_ROW_BATCH;
+#ifndef MLC_ROW_THREADS
+#define MLC_ROW_THREADS 1024
+#endif
+constexpr int kTabRowThreads = MLC_ROW_THREADS;
 
 // MODE 0: any geometry (window loads); 1: flat planes, aligned tensors;
 // 2: flipped sources (no transpose) whose rows are a whole number of aligned
 // 16-byte items - the flips are index arithmetic on items, every load is one
 // 128-bit load and up to four sources are in flight together.
 template <int MODE>
-__global__ void __launch_bounds__(kTabThreads, 1)
+__global__ void __launch_bounds__(MODE == 0 ? kTabRowThreads : kTabThreads, 1)
 seg_hist_tab(const __grid_constant__ HistArgs a) {
   constexpr bool VEC = MODE == 1;
   extern __shared__ __align__(16) unsigned char tab_smem[];
@@ -386,6 +399,72 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
           ++y;
         }
       }
+    } else if (!a.flat && !(a.src.any_xf & MLC_XF_TRANSPOSE) &&
+               a.items_per_row > 0 && a.W >= 16) {
+      // Rows of any width / alignment (350 x 525 ...).  Full items of the
+      // rows whose neighbourhood stays inside the tensor: every source is
+      // read as the two aligned 16-byte vectors enclosing its window, two
+      // sources' loads in flight before the first is used (the per-source
+      // word loads of item_checked keep 20 bytes per thread in flight: ncu
+      // showed 40 % of the samples waiting on them).  Outermost rows and row
+      // tails go through the checked path.
+      const int ipr = a.items_per_row;
+      const int dy = (int)blockDim.x / ipr, dx = (int)blockDim.x - dy * ipr;
+      const int full_end = (int)min(i1, a.full_items);
+      int it = (int)i0 + (int)threadIdx.x;
+      int y = it / ipr, xi = it - y * ipr;
+      for (; it < full_end; it += blockDim.x) {
+        if (inner || (y >= 1 && y <= a.H - 2)) {
+          const int x0 = xi * 8;
+          float p[8];
+          for (int k0 = 0; k0 < S; k0 += kRowBatch) {
+            uint32_t t[kRowBatch][8];
+            uint32_t off[kRowBatch];
+#pragma unroll
+            for (int j = 0; j < kRowBatch; ++j)
+              if (k0 + j < S) {
+                const int xf = a.src.xf[k0 + j];
+                const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+                const int xs = (xf & MLC_XF_HFLIP) ? a.W - 8 - x0 : x0;
+                const uintptr_t q = reinterpret_cast<uintptr_t>(
+                    static_cast<const __half *>(a.src.ptr[k0 + j]) +
+                    plane_off + (size_t)ys * a.W + xs);
+                const uintptr_t b = q & ~(uintptr_t)15;
+                off[j] = (uint32_t)(q & 15) >> 1;
+                const uint4 lo = ldg_stream16(reinterpret_cast<const void *>(b));
+                const uint4 hi =
+                    ldg_stream16(reinterpret_cast<const void *>(b + 16));
+                t[j][0] = lo.x; t[j][1] = lo.y; t[j][2] = lo.z; t[j][3] = lo.w;
+                t[j][4] = hi.x; t[j][5] = hi.y; t[j][6] = hi.z; t[j][7] = hi.w;
+              }
+#pragma unroll
+            for (int j = 0; j < kRowBatch; ++j) {
+              if (k0 + j < S) {
+                uint32_t w[4];
+                window8_from_enclosing(
+                    t[j], off[j], (a.src.xf[k0 + j] & MLC_XF_HFLIP) != 0, w);
+                float v[8];
+                act8_table(w, tab_sa, a.act, v);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                  p[i] = (k0 + j == 0) ? v[i] : p[i] + v[i];
+              }
+            }
+          }
+          bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, 8, true), 8);
+        } else {
+          item_checked(it);
+        }
+        xi += dx;
+        y += dy;
+        if (xi >= ipr) {
+          xi -= ipr;
+          ++y;
+        }
+      }
+      for (long long jt = max(i0, a.full_items) + threadIdx.x; jt < i1;
+           jt += blockDim.x)
+        item_checked(jt);
     } else {
       for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x)
         item_checked(it);
@@ -1026,7 +1105,7 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
                              : vrows ? seg_hist_tab<2> : seg_hist_tab<0>;
       MLC_CUDA(cudaFuncSetAttribute(
           tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tab_smem));
-      tk<<<tgrid, kTabThreads, tab_smem, st>>>(a);
+      tk<<<tgrid, (vec || vrows) ? kTabThreads : kTabRowThreads, tab_smem, st>>>(a);
     } else if (act == MLC_ACT_SOFTMAX) {
       if (dtype == MLC_F16)
         seg_hist_generic<__half, false, true><<<grid, kHistThreads, smem, st>>>(a);
