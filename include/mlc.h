@@ -179,6 +179,10 @@ int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img, int n_cls,
  *   total_dev  [1] int64: int32 elements needed; if > capacity the planes
  *              that did not fit have off = -1 and the caller retries bigger.
  *   src may be uint8 masks already: dtype MLC_U8 with act NONE and thr 0.5
+ *   Planes of any size: up to ~1.6 M pixels (a column-major bit plane of at
+ *   most 200 KB) are transposed in shared memory and read once; larger ones
+ *   take a column-walking kernel that reads the plane twice (W <= 25 600;
+ *   beyond that MLC_ERR_UNSUPPORTED).
  */
 #define MLC_U8 2
 int mlc_rle_encode(const void *const *src_dev_ptrs, const int32_t *xform,

@@ -508,6 +508,109 @@ rle_kernel(const __grid_constant__ RleArgs a) {
   }
 }
 
+// ---- planes whose bit plane does not fit in shared memory -------------------
+// (more than ~1.6 M pixels.)  No transpose: a thread owns whole columns
+// (column x -> thread x mod 512, so a warp reads 32 neighbouring columns of a
+// row together), walks them twice - once to count run starts, once to emit -
+// and only the per-column start counts and latest start positions live in
+// shared memory (8 bytes per column).  The plane is read twice and the
+// activation evaluated per pixel: a fallback for correctness, not a fast path.
+constexpr int kBigThreads = 512;
+
+template <typename T, bool SM>
+__global__ void __launch_bounds__(kBigThreads)
+rle_big_kernel(const __grid_constant__ RleArgs a) {
+  extern __shared__ uint32_t bits[];  // reused: nst[W] then lst[W]
+  __shared__ int warp_tot[kBigThreads / 32];
+  __shared__ long long s_base;
+  const int H = a.H, W = a.W;
+  int *nst = reinterpret_cast<int *>(bits);  // starts in column x -> exclusive
+  int *lst = nst + W;                        // latest start <= column x
+  for (long long plane = blockIdx.x; plane < a.n_planes; plane += gridDim.x) {
+    const int c = (int)(plane % a.C);
+    const float thr = a.thr[c];
+    const size_t plane_off = (size_t)plane * H * W;
+    const PlaneCtx cx = {plane, a.n_planes, (long long)H * W, a.C};
+    auto bit = [&](int y, int x) -> bool {
+      float p[8];
+      fused_prob8<T, SM>(a.src, plane_off, cx, H, W, y, x, 1, false, a.act, p);
+      return p[0] >= thr;
+    };
+    // ---- pass 1: starts per column -----------------------------------------
+    int my_px = 0;
+    for (int x = threadIdx.x; x < W; x += kBigThreads) {
+      bool prev = x > 0 ? bit(H - 1, x - 1) : false;
+      int n = 0, last = 0;
+      for (int y = 0; y < H; ++y) {
+        const bool b = bit(y, x);
+        if (b && !prev) {
+          ++n;
+          last = x * H + y + 1;  // 1-based, column-major
+        }
+        my_px += b;
+        prev = b;
+      }
+      nst[x] = n;
+      lst[x] = last;
+    }
+    __syncthreads();
+    // ---- scans over the columns (thread = a contiguous chunk of columns) ----
+    const int per = (W + kBigThreads - 1) / kBigThreads;
+    const int c0 = min(W, (int)threadIdx.x * per), c1 = min(W, c0 + per);
+    int sum = 0, mx = 0;
+    for (int x = c0; x < c1; ++x) {
+      sum += nst[x];
+      mx = max(mx, lst[x]);
+    }
+    int tot_runs, tot_px;
+    int running = block_excl_scan(sum, warp_tot, &tot_runs);
+    (void)block_excl_scan(my_px, warp_tot, &tot_px);
+    int runmax = block_excl_max(mx, warp_tot);
+    for (int x = c0; x < c1; ++x) {
+      const int n = nst[x], m = lst[x];
+      nst[x] = running;  // starts before column x
+      lst[x] = runmax;   // start of the run open at the top of column x
+      running += n;
+      runmax = max(runmax, m);
+    }
+    const int min_area = a.min_area[c];
+    if (min_area > 0 && tot_px < min_area) tot_runs = 0;  // dice.py:13-15 rule
+    if (threadIdx.x == 0) {
+      long long base = (long long)atomicAdd(a.total, 2ull * tot_runs);
+      if (base + 2ll * tot_runs > a.capacity) base = -1;
+      s_base = base;
+      a.off[plane] = base;
+      a.cnt[plane] = tot_runs;
+      if (a.area) a.area[plane] = tot_px;
+    }
+    __syncthreads();
+    const long long base = s_base;
+    // ---- pass 2: one (start, length) pair per run, written where it ends ----
+    if (tot_runs > 0 && base >= 0) {
+      int2 *out = reinterpret_cast<int2 *>(a.runs + base);
+      for (int x = threadIdx.x; x < W; x += kBigThreads) {
+        bool prev = x > 0 ? bit(H - 1, x - 1) : false;
+        int idx = nst[x] - 1;  // index of the run open at the top, if any
+        int cur = lst[x];
+        bool b = bit(0, x);
+        for (int y = 0; y < H; ++y) {
+          const bool nb = y + 1 < H ? bit(y + 1, x)
+                                    : (x + 1 < W ? bit(0, x + 1) : false);
+          const int pos = x * H + y + 1;
+          if (b && !prev) {
+            ++idx;
+            cur = pos;
+          }
+          if (b && !nb) out[idx] = make_int2(cur, pos - cur + 1);
+          prev = b;
+          b = nb;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace mlc
 
 using namespace mlc;
@@ -575,10 +678,28 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   a.act = act;
   const size_t smem = (size_t)W * (a.Hw | 1) * 4;
   if (smem > kRleMaxSmem) {
-    set_error("plane %d x %d needs %zu bytes of shared memory for its bit "
-              "plane; this build supports up to %zu",
-              H, W, smem, kRleMaxSmem);
-    return MLC_ERR_UNSUPPORTED;
+    // the column-walking fallback: 8 bytes of shared memory per column
+    const size_t big = (size_t)W * 8;
+    if (big > kRleMaxSmem) {
+      set_error("plane %d x %d: neither its bit plane (%zu bytes) nor its "
+                "column table (%zu bytes) fits the %zu bytes of shared memory "
+                "this build uses",
+                H, W, smem, big, kRleMaxSmem);
+      return MLC_ERR_UNSUPPORTED;
+    }
+    const bool sm_ = act == MLC_ACT_SOFTMAX;
+    void (*bk)(RleArgs) =
+        dtype == MLC_F16 ? (sm_ ? rle_big_kernel<__half, true>
+                                : rle_big_kernel<__half, false>)
+        : dtype == MLC_F32 ? (sm_ ? rle_big_kernel<float, true>
+                                  : rle_big_kernel<float, false>)
+                           : rle_big_kernel<uint8_t, false>;
+    MLC_CUDA(cudaFuncSetAttribute(
+        bk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRleMaxSmem));
+    const int bgrid = (int)min(a.n_planes, 2ll * sm_count());
+    bk<<<bgrid, kBigThreads, big, st>>>(a);
+    MLC_LAUNCH_CHECK("rle_big_kernel");
+    return MLC_OK;
   }
   const bool code = dtype == MLC_F16 && n_src == 1 && a.src.any_xf == 0 &&
                     act != MLC_ACT_SOFTMAX;

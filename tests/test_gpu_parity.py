@@ -590,6 +590,39 @@ def test_rle_bounded_path_special_values_and_thresholds(ops, activation):
                 k += 1
 
 
+@pytest.mark.parametrize('dtype,tags,shape', [
+    (torch.float16, [[]], (1, 2, 2100, 900)),        # 241 KB bit plane
+    (torch.float16, [[], ['hflip']], (1, 1, 1700, 1030)),
+    (torch.float32, [['vflip']], (2, 1, 1620, 1028)),
+    (torch.float16, [[]], (1, 1, 70, 25600)),        # widest supported
+])
+def test_rle_planes_too_big_for_the_bit_plane(ops, dtype, tags, shape):
+    """Planes over ~1.6 M pixels go through rle_big_kernel (column walk)."""
+    n, c, h, w = shape
+    srcs, _ = synth_seg(n, c, h, w, seed=h, dtype=dtype, n_src=len(tags),
+                        empty=0.0)
+    seen = [forward_tta(s, t) for s, t in zip(srcs, tags)]
+    dev_src = [s.to(DEV) for s in seen]
+    thr = np.full(c, 0.5, np.float32)
+    areas = np.array([0, 10 ** 8][:c], np.int32)
+    runs, off, cnt, area = ops.rle_encode(dev_src, thr, areas, xforms=tags)
+    got = ops.rle_strings(runs, off, cnt)
+    prob = ops.seg_prob(dev_src, xforms=tags).cpu().numpy()
+    k = 0
+    for i in range(n):
+        for j in range(c):
+            want = oracle.rle_submission(prob[i, j], thr[j], int(areas[j]))
+            assert got[k] == want, (i, j)
+            assert int(area[i, j]) == int((prob[i, j] >= thr[j]).sum())
+            k += 1
+    # a column count beyond the table is refused, not mis-encoded
+    if w == 25600:
+        from mlcomp_b200._lib import MlcError
+        with pytest.raises(MlcError, match='neither its bit plane'):
+            ops.rle_encode([torch.zeros((1, 1, 70, 25608), dtype=torch.float16,
+                                        device=DEV)], thr, 0)
+
+
 def test_rle_edge_masks_and_retry(ops):
     rng = np.random.default_rng(9)
     h, w = 70, 45
