@@ -178,8 +178,9 @@ enum { kRleArith = 0, kRleCode = 1, kRleBound = 2, kRleBoundVec = 3 };
 template <bool VEC>
 __device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
                                            int W, int y0, int x0,
-                                           uint32_t fastmask, __half2 t2,
+                                           uint32_t fastmask, uint32_t t2bits,
                                            uint32_t wk[8]) {
+  const __half2 t2 = *reinterpret_cast<const __half2 *>(&t2bits);
   const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
   const int xs = rev ? W - 8 - x0 : x0;
   const int top = 32 - __clz(fastmask);  // rows beyond the last fast one
@@ -229,8 +230,60 @@ __device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
   }
 }
 
+// fp32 sources: 8 pixels are 32 bytes (two 128-bit loads when rows are
+// 16-byte multiples, else eight word loads - fp32 elements are always word
+// aligned), two rows in flight, one FSETP per pixel against the threshold
+// value x'_c.  No load reaches outside the 8-element window.
+template <bool VEC>
+__device__ __forceinline__ void bound_rows(const float *plane, int xf, int H,
+                                           int W, int y0, int x0,
+                                           uint32_t fastmask, uint32_t t_bits,
+                                           uint32_t wk[8]) {
+  const float t = __uint_as_float(t_bits);
+  const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
+  const int xs = rev ? W - 8 - x0 : x0;
+  const int top = 32 - __clz(fastmask);
+  for (int r0 = 0; r0 < top; r0 += 2) {
+    float u[2][8];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int r = r0 + q;
+      const bool on = (fastmask >> r) & 1u;
+      const int ys = vf ? H - 1 - (y0 + r) : y0 + r;
+      const float *p = plane + ((long long)ys * W + xs);
+      if (VEC) {
+        const uint4 a = on ? ldg_stream16(p) : make_uint4(0, 0, 0, 0);
+        const uint4 b = on ? ldg_stream16(p + 4) : make_uint4(0, 0, 0, 0);
+        u[q][0] = __uint_as_float(a.x); u[q][1] = __uint_as_float(a.y);
+        u[q][2] = __uint_as_float(a.z); u[q][3] = __uint_as_float(a.w);
+        u[q][4] = __uint_as_float(b.x); u[q][5] = __uint_as_float(b.y);
+        u[q][6] = __uint_as_float(b.z); u[q][7] = __uint_as_float(b.w);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          u[q][j] = on ? __uint_as_float(ldg_nc32(p + j)) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int r = r0 + q;
+      const uint32_t bit = ((fastmask >> r) & 1u) << r;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float v = rev ? u[q][7 - i] : u[q][i];
+        if (v >= t) wk[i] |= bit;
+      }
+    }
+  }
+}
+template <bool VEC>
+__device__ __forceinline__ void bound_rows(const uint8_t *, int, int, int, int,
+                                           int, uint32_t, uint32_t,
+                                           uint32_t[8]) {}  // never selected
+
 // exact fused probability of ONE pixel: the scalar twin of fused_prob8 for
 // sources without transposes
+template <typename T>
 __device__ __forceinline__ float fused_prob1(const SrcSet &s, size_t plane_off,
                                              int H, int W, int y, int x,
                                              int act) {
@@ -243,7 +296,7 @@ __device__ __forceinline__ float fused_prob1(const SrcSet &s, size_t plane_off,
         const int xf = s.xf[k0 + j];
         const int ys = (xf & MLC_XF_VFLIP) ? H - 1 - y : y;
         const int xs = (xf & MLC_XF_HFLIP) ? W - 1 - x : x;
-        v[j] = __half2float(static_cast<const __half *>(
+        v[j] = to_f32<T>(static_cast<const T *>(
             s.ptr[k0 + j])[plane_off + (size_t)ys * W + xs]);
       }
     }
@@ -280,22 +333,46 @@ rle_kernel(const __grid_constant__ RleArgs a) {
   if (CODE || BOUND) {
     if ((int)threadIdx.x < a.C) {
       const float thr = a.thr[threadIdx.x];
-      // smallest key in [key(-inf), key(+inf)] whose value passes (as S equal
-      // sources); one past +inf if none does
-      uint32_t lo = kKeyNegInf, hi = kKeyPosInf + 1;
-      while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        const uint32_t code = mid ^ ((mid & 0x8000u) ? 0x8000u : 0xFFFFu);
-        const float x =
-            __half2float(__ushort_as_half((unsigned short)code));
+      // as S equal sources: does x pass?
+      auto passes = [&](float x) {
         const float v = activate(x, a.act);
         float q[8] = {v, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         for (int k = 1; k < a.src.n; ++k) q[0] = q[0] + v;
         mean8(q, a.src.n);
-        if (q[0] >= thr) hi = mid;
-        else lo = mid + 1;
+        return q[0] >= thr;
+      };
+      if (sizeof(T) == 4) {
+        // fp32 sources: same bisection over the 32-bit order-preserving keys
+        // (the device sigmoid is non-decreasing over ALL fp32 values:
+        // tools/check_sigmoid_monotone_f32.py sweeps the 2^32 inputs).
+        // key_thr holds the BITS of the smallest passing value; a NaN
+        // pattern when nothing passes (x >= NaN is false for every x).
+        const uint32_t k_ninf = 0x007FFFFFu, k_pinf = 0xFF800000u;
+        uint32_t lo = k_ninf, hi = k_pinf + 1;  // keys of -inf, one past +inf
+        while (lo < hi) {
+          const uint32_t mid = lo + ((hi - lo) >> 1);
+          const uint32_t b = mid ^ ((mid & 0x80000000u) ? 0x80000000u
+                                                        : 0xFFFFFFFFu);
+          if (passes(__uint_as_float(b))) hi = mid;
+          else lo = mid + 1;
+        }
+        key_thr[threadIdx.x] =
+            lo > k_pinf ? 0x7FC00000u
+                        : lo ^ ((lo & 0x80000000u) ? 0x80000000u : 0xFFFFFFFFu);
+      } else {
+        // smallest key in [key(-inf), key(+inf)] whose value passes; one past
+        // +inf if none does
+        uint32_t lo = kKeyNegInf, hi = kKeyPosInf + 1;
+        while (lo < hi) {
+          const uint32_t mid = (lo + hi) >> 1;
+          const uint32_t code = mid ^ ((mid & 0x8000u) ? 0x8000u : 0xFFFFu);
+          if (passes(__half2float(__ushort_as_half((unsigned short)code))))
+            hi = mid;
+          else
+            lo = mid + 1;
+        }
+        key_thr[threadIdx.x] = lo;
       }
-      key_thr[threadIdx.x] = lo;
     }
     __syncthreads();
   }
@@ -347,10 +424,10 @@ rle_kernel(const __grid_constant__ RleArgs a) {
           }
         } else if (BOUND) {
           const uint32_t kc = key_thr[c];
-          if (kc <= kKeyPosInf) {
-            const uint32_t xc = kc ^ ((kc & 0x8000u) ? 0x8000u : 0xFFFFu);
-            const uint32_t xc2 = xc | (xc << 16);
-            const __half2 t2 = *reinterpret_cast<const __half2 *>(&xc2);
+          // fp16: key -> code, both halves of a packed pair; fp32: the bits
+          const uint32_t xc = kc ^ ((kc & 0x8000u) ? 0x8000u : 0xFFFFu);
+          const uint32_t t2 = sizeof(T) == 4 ? kc : (xc | (xc << 16));
+          if (sizeof(T) == 4 || kc <= kKeyPosInf) {
             // rows whose windows stay inside the tensor for every flip
             const uint32_t valid = rows == 32 ? ~0u : (1u << rows) - 1u;
             uint32_t fastmask = valid;
@@ -364,8 +441,7 @@ rle_kernel(const __grid_constant__ RleArgs a) {
             if (fastmask) {
               for (int k = 0; k < a.src.n; ++k) {
                 uint32_t wk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-                const __half *pl =
-                    static_cast<const __half *>(a.src.ptr[k]) + plane_off;
+                const T *pl = static_cast<const T *>(a.src.ptr[k]) + plane_off;
                 bound_rows<MODE == kRleBoundVec>(pl, a.src.xf[k], H, W, yb * 32,
                                                  x0, fastmask, t2, wk);
 #pragma unroll
@@ -397,7 +473,7 @@ rle_kernel(const __grid_constant__ RleArgs a) {
                 }
               if (i < 0) break;
               const int r = __ffs(m) - 1;
-              const bool pass = fused_prob1(a.src, plane_off, H, W,
+              const bool pass = fused_prob1<T>(a.src, plane_off, H, W,
                                             yb * 32 + r, x0 + i, a.act) >= thr;
 #pragma unroll
               for (int j = 0; j < 8; ++j)
@@ -703,14 +779,17 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   }
   const bool code = dtype == MLC_F16 && n_src == 1 && a.src.any_xf == 0 &&
                     act != MLC_ACT_SOFTMAX;
-  bool aligned = (W % 8) == 0;
+  // rows a whole number of 16-byte vectors and 16-byte aligned tensors
+  bool aligned = dtype == MLC_F16 ? (W % 8) == 0 : (W % 4) == 0;
   for (int k = 0; k < n_src; ++k)
     aligned = aligned && ((uintptr_t)src_dev_ptrs[k] % 16) == 0;
-  a.vec_ok = dtype == MLC_F16 && aligned;
+  a.vec_ok = dtype != MLC_U8 && aligned;
   const bool sm = act == MLC_ACT_SOFTMAX;
-  // several sources / flips without a transpose: bounded by packed compares
-  const bool bound = dtype == MLC_F16 && !code && !sm && W >= 8 &&
-                     !(a.src.any_xf & MLC_XF_TRANSPOSE) && !arith_only();
+  // several sources / flips without a transpose, and every fp32 job:
+  // bounded by packed compares
+  const bool bound = (dtype == MLC_F16 || dtype == MLC_F32) && !code && !sm &&
+                     W >= 8 && !(a.src.any_xf & MLC_XF_TRANSPOSE) &&
+                     !arith_only();
   // CODE: two 512-thread CTAs per SM when two bit planes (+ slack) fit, so
   // that one streams while the other scans.  BOUND: one 1024-thread CTA
   // (measured: the exact pass of a 512-thread pair costs more than the
@@ -727,8 +806,11 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
                         : rle_kernel<__half, kRleBound, false, 1024>)
                  : sm ? rle_kernel<__half, kRleArith, true, 512>
                       : rle_kernel<__half, kRleArith, false, 512>)
-      : dtype == MLC_F32 ? (sm ? rle_kernel<float, kRleArith, true, 512>
-                               : rle_kernel<float, kRleArith, false, 512>)
+      : dtype == MLC_F32
+          ? (bound ? (a.vec_ok ? rle_kernel<float, kRleBoundVec, false, 1024>
+                               : rle_kernel<float, kRleBound, false, 1024>)
+             : sm ? rle_kernel<float, kRleArith, true, 512>
+                  : rle_kernel<float, kRleArith, false, 512>)
                          : rle_kernel<uint8_t, kRleArith, false, 512>;
   MLC_CUDA(cudaFuncSetAttribute(kern,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize,

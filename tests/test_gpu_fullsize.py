@@ -165,3 +165,30 @@ def test_c1_size_confusion():
     assert r['accuracy'] == float(oracle.classify_score_final(
         oracle.classify_scores(logits, y)))
     assert r['confusion'].sum() == n and r['dropped'] == 0
+
+
+def test_device_sigmoid_is_monotone_over_all_fp32():
+    """The bounded RLE path for fp32 sources turns act(x) >= thr into
+    x >= x'_c; that needs the device sigmoid (the arithmetic every kernel
+    shares, here through mlc_seg_prob) to be non-decreasing over ALL 2^32
+    fp32 inputs.  Exhaustive sweep, NaNs excluded."""
+    from mlcomp_b200 import ops
+    chunk = 1 << 27
+    bad = 0
+    for negative in (False, True):
+        last = None
+        for b0 in range(0, 0x7F800001, chunk):
+            n = min(chunk, 0x7F800001 - b0)
+            bits = torch.arange(b0, b0 + n, device=DEV, dtype=torch.int64)
+            if negative:
+                bits = bits - (1 << 31)       # two's complement of 0x8000.. | b
+            x = bits.to(torch.int32).view(torch.float32)
+            p = ops.seg_prob([x.view(1, 1, 1, n)],
+                             activation='sigmoid').view(-1)
+            d = p[1:] - p[:-1]
+            bad += int(((d > 0) if negative else (d < 0)).sum())
+            if last is not None:
+                bad += int((p[0] > last) if negative else (p[0] < last))
+            last = p[-1].clone()
+            del bits, x, p, d
+    assert bad == 0

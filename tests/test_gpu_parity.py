@@ -552,8 +552,10 @@ def test_rle_matches_mask2rle(ops, dtype, shape, tags):
             k += 1
 
 
+@pytest.mark.parametrize('dtype', [np.float16, np.float32])
 @pytest.mark.parametrize('activation', ['sigmoid', None])
-def test_rle_bounded_path_special_values_and_thresholds(ops, activation):
+def test_rle_bounded_path_special_values_and_thresholds(ops, activation,
+                                                        dtype):
     """Multi-source fp16 planes with NaN / +-inf / +-0 sprinkled in and
     thresholds from below 0 to above 1: the packed-compare decisions plus
     the exact pass must equal (fused prob >= thr) everywhere."""
@@ -562,7 +564,7 @@ def test_rle_bounded_path_special_values_and_thresholds(ops, activation):
     tags = [[], ['hflip'], ['vflip']]
     srcs = []
     for k in range(3):
-        x = rng.normal(0, 3, (n, c, h, w)).astype(np.float16)
+        x = rng.normal(0, 3, (n, c, h, w)).astype(dtype)
         sp = rng.random((n, c, h, w))
         x[sp < 0.01] = np.nan
         x[(sp >= 0.01) & (sp < 0.02)] = np.inf
@@ -570,7 +572,8 @@ def test_rle_bounded_path_special_values_and_thresholds(ops, activation):
         x[(sp >= 0.03) & (sp < 0.04)] = -0.0
         x[(sp >= 0.04) & (sp < 0.05)] = 0.0
         if activation is None:
-            x = (1 / (1 + np.exp(-x.astype(np.float32)))).astype(np.float16)
+            with np.errstate(over='ignore'):
+                x = (1 / (1 + np.exp(-x.astype(np.float32)))).astype(dtype)
         srcs.append(torch.from_numpy(x).to(DEV))
     for thr in ([-0.5, 0.0, 0.5, 1.0], [0.25, 0.75, 1.5, 1e-3]):
         thr = np.asarray(thr, np.float32)
@@ -588,6 +591,38 @@ def test_rle_bounded_path_special_values_and_thresholds(ops, activation):
                     (i, j, thr[j])
                 assert int(area[i, j]) == int(mask.sum())
                 k += 1
+
+
+@pytest.mark.parametrize('activation', ['sigmoid', None])
+def test_rle_fp32_single_source_extremes(ops, activation):
+    """fp32 planes take the bounded path too (one FSETP per pixel against
+    the bisected threshold value): extremes of the fp32 range, thresholds at
+    and around the ends of [0, 1]."""
+    rng = np.random.default_rng(11)
+    n, c, h, w = 1, 5, 40, 72
+    x = rng.normal(0, 30, (n, c, h, w)).astype(np.float32)
+    special = np.array([np.nan, np.inf, -np.inf, 0.0, -0.0, 1e-45, -1e-45,
+                        3e38, -3e38, 88.0, -88.0, 103.9, -103.9, 16.6, -16.7,
+                        1e-8, -1e-8], np.float32)
+    idx = rng.integers(0, x.size, 600)
+    x.reshape(-1)[idx] = special[rng.integers(0, len(special), 600)]
+    if activation is None:
+        x = np.clip(x / 60 + 0.5, -1, 2).astype(np.float32)
+        x.reshape(-1)[idx[:100]] = np.nan
+    src = torch.from_numpy(x).to(DEV)
+    for thr in ([0.0, 1e-30, 0.5, 1 - 6e-8, 1.0], [-1.0, 2.5, 0.999, 1e-3,
+                                                   0.25]):
+        thr = np.asarray(thr, np.float32)
+        runs, off, cnt, area = ops.rle_encode([src], thr, 0,
+                                              activation=activation)
+        got = ops.rle_strings(runs, off, cnt)
+        prob = ops.seg_prob([src], activation=activation).cpu().numpy()
+        for j in range(c):
+            with np.errstate(invalid='ignore'):
+                mask = prob[0, j] >= thr[j]
+            assert got[j] == oracle.rle_encode(mask.astype(np.uint8)), \
+                (j, thr[j])
+            assert int(area[0, j]) == int(mask.sum())
 
 
 @pytest.mark.parametrize('dtype,tags,shape', [

@@ -37,3 +37,15 @@ print('GB hist4', px * 9 / 1e9, 'rle4', px * 8 / 1e9, 'hist1', px * 3 / 1e9, 'rl
 same = [logits.flip(*d).contiguous() if d else logits for d in ((), (3,), (2,), (2, 3))]
 print('rle_tta4_identical', round(timeit(lambda: ops.rle_encode(same, [0.5] * 4, [256] * 4, xforms=xf, capacity=cap)), 3))
 print('rle_hflip_1src', round(timeit(lambda: ops.rle_encode([same[1]], [0.5] * 4, [256] * 4, xforms=[xf[1]], capacity=cap)), 3))
+# fp32 logits (the reference's own dtype), 256 images
+n32 = 256
+s32 = [s[:n32].float() for s in srcs]
+px32 = n32 * 4 * 256 * 1600
+t = timeit(lambda: ops.seg_hist(s32, gt[:n32], thr, xforms=xf))
+print('hist_tta4_rows_fp32', round(t, 3), 'ms', round(px32 * 17 / t / 1e6 / 6550.4, 3), 'of HBM peak')
+t = timeit(lambda: ops.seg_hist(s32, gt[:n32], thr))
+print('hist_4src_flat_fp32', round(t, 3), 'ms', round(px32 * 17 / t / 1e6 / 6550.4, 3), 'of HBM peak')
+t = timeit(lambda: ops.rle_encode(s32, [0.5] * 4, [256] * 4, xforms=xf, capacity=cap))
+print('rle_tta4_fp32', round(t, 3), 'ms', round(px32 * 16 / t / 1e6 / 6550.4, 3), 'of HBM peak')
+t = timeit(lambda: ops.rle_encode([s32[0]], [0.5] * 4, [256] * 4, capacity=cap))
+print('rle_1src_fp32', round(t, 3), 'ms', round(px32 * 4 / t / 1e6 / 6550.4, 3), 'of HBM peak')
