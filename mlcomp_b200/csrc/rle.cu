@@ -184,14 +184,18 @@ __device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
   const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
   const int xs = rev ? W - 8 - x0 : x0;
   const int top = 32 - __clz(fastmask);  // rows beyond the last fast one
+  // the row pointer advances by +-W elements: all address arithmetic that
+  // does not depend on the row stays out of the loop
+  const long long step = vf ? -(long long)W : (long long)W;
+  const __half *prow = plane + ((long long)(vf ? H - 1 - y0 : y0) * W + xs);
   for (int r0 = 0; r0 < top; r0 += 4) {
     uint32_t w[4][4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int r = r0 + q;
       const bool on = (fastmask >> r) & 1u;
-      const int ys = vf ? H - 1 - (y0 + r) : y0 + r;
-      const __half *p = plane + ((long long)ys * W + xs);
+      const __half *p = prow;
+      prow += step;
       if (VEC) {
         const uint4 v = on ? ldg_stream16(p) : make_uint4(0, 0, 0, 0);
         w[q][0] = v.x; w[q][1] = v.y; w[q][2] = v.z; w[q][3] = v.w;
@@ -243,14 +247,16 @@ __device__ __forceinline__ void bound_rows(const float *plane, int xf, int H,
   const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
   const int xs = rev ? W - 8 - x0 : x0;
   const int top = 32 - __clz(fastmask);
+  const long long step = vf ? -(long long)W : (long long)W;
+  const float *prow = plane + ((long long)(vf ? H - 1 - y0 : y0) * W + xs);
   for (int r0 = 0; r0 < top; r0 += 2) {
     float u[2][8];
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
       const int r = r0 + q;
       const bool on = (fastmask >> r) & 1u;
-      const int ys = vf ? H - 1 - (y0 + r) : y0 + r;
-      const float *p = plane + ((long long)ys * W + xs);
+      const float *p = prow;
+      prow += step;
       if (VEC) {
         const uint4 a = on ? ldg_stream16(p) : make_uint4(0, 0, 0, 0);
         const uint4 b = on ? ldg_stream16(p + 4) : make_uint4(0, 0, 0, 0);
