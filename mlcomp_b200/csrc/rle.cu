@@ -68,12 +68,14 @@ template <bool RAW>
 __device__ __forceinline__ void code_rows(const __half *row0, int W, int rows,
                                           uint32_t sub, uint32_t lim_lo,
                                           uint32_t lim_hi, uint32_t word[8]) {
+  const __half *prow = row0;  // advanced by W per row: no per-row multiply
   for (int r0 = 0; r0 < rows; r0 += 4) {
     uint4 v[4];  // four rows in flight before any compare
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
-      v[q] = r0 + q < rows ? ldg_stream16(row0 + (size_t)(r0 + q) * W)
-                           : make_uint4(0, 0, 0, 0);
+    for (int q = 0; q < 4; ++q) {
+      v[q] = r0 + q < rows ? ldg_stream16(prow) : make_uint4(0, 0, 0, 0);
+      prow += W;
+    }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const uint32_t w4[4] = {v[q].x, v[q].y, v[q].z, v[q].w};
