@@ -109,6 +109,20 @@ int mlc_seg_hist(const void *const *src_dev_ptrs, const int32_t *xform,
                  int act, const uint8_t *lut_dev, uint32_t *hist_dev,
                  void *stream);
 
+/* mlc_seg_hist with a second output: the bin index cnt(p) of every pixel.
+ * No reference counterpart as a function - it is the same pass (the lines
+ * cited above), keeping what the reference would re-compute: once the search
+ * has chosen thr[k], (p >= thr[k]) is (bin > k), so the masks for
+ * mlc_rle_encode (dtype MLC_U8, act NONE, thr = k + 0.5) or for a saved
+ * prediction come from 1 byte per pixel instead of all the sources again.
+ *   bins_dev   [n_img][n_cls][H][W] uint8 (n_thr <= 255), overwritten
+ * Always served by the multi-source kernels (no lut). */
+int mlc_seg_hist_bins(const void *const *src_dev_ptrs, const int32_t *xform,
+                      int n_src, int dtype, const uint8_t *gt_dev,
+                      int64_t n_img, int n_cls, int H, int W,
+                      const float *thr_host, int n_thr, int act,
+                      uint32_t *hist_dev, uint8_t *bins_dev, void *stream);
+
 /* Same fusion, writing the fp32 probabilities [n_img][n_cls][H][W] instead
  * (what utils/torch.py:24-29 `_infer` returns after the mean). */
 int mlc_seg_prob(const void *const *src_dev_ptrs, const int32_t *xform,

@@ -32,6 +32,10 @@ SIGNATURES = {
                              c_void_p, c_int64, c_int, c_int, c_int,
                              POINTER(c_float), c_int, c_int, c_void_p,
                              c_void_p, c_void_p]),
+    'mlc_seg_hist_bins': (c_int, [POINTER(c_void_p), POINTER(c_int32), c_int,
+                                  c_int, c_void_p, c_int64, c_int, c_int, c_int,
+                                  POINTER(c_float), c_int, c_int, c_void_p,
+                                  c_void_p, c_void_p]),
     'mlc_seg_prob': (c_int, [POINTER(c_void_p), POINTER(c_int32), c_int, c_int,
                              c_int64, c_int, c_int, c_int, c_int, c_void_p,
                              c_void_p]),

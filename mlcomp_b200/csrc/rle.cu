@@ -133,6 +133,42 @@ __device__ __forceinline__ void store_columns(uint32_t *bits, int Hp, int x0,
   }
 }
 
+// BYTES (MODE 4): one untransformed uint8 source, no activation - masks, or
+// the per-pixel bin indices mlc_seg_hist_bins keeps (mask = bin >= k).  Eight
+// rows of 8 bytes in flight per lane; value >= k for four bytes at once:
+//   t = ((w & 0x7F7F7F7F) | 0x80808080) - (k & 0x7F) * 0x01010101
+// has bit 7 of a byte set iff its low 7 bits are >= those of k (no borrow
+// crosses bytes), and with the top bit of k known per class
+//   k < 128 : b >= k  <=>  top(b) |  low-part test
+//   k >= 128: b >= k  <=>  top(b) &  low-part test.
+__device__ __forceinline__ void byte_rows(const uint8_t *row0, int W, int rows,
+                                          uint32_t k, uint32_t word[8]) {
+  const uint32_t k7 = (k & 0x7Fu) * 0x01010101u;
+  const bool khi = (k & 0x80u) != 0;
+  const uint8_t *prow = row0;
+  for (int r0 = 0; r0 < rows; r0 += 8) {
+    uint2 v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      v[q] = r0 + q < rows ? ldg_stream8(prow) : make_uint2(0u, 0u);
+      prow += W;
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const uint32_t bit = r0 + q < rows ? 1u << (r0 + q) : 0u;
+      const uint32_t w2[2] = {v[q].x, v[q].y};
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t t = ((w2[h] & 0x7F7F7F7Fu) | 0x80808080u) - k7;
+        const uint32_t ge = khi ? (t & w2[h]) : (t | w2[h]);
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (ge & (0x80u << (8 * b))) word[4 * h + b] |= bit;
+      }
+    }
+  }
+}
+
 // CODE: one untransformed fp16 source.  act(x) >= thr is then a statement
 // about the 16-bit code alone, and because the activation evaluated here is
 // non-decreasing over the fp16 values (all 63 488 finite codes, asserted by
@@ -167,7 +203,8 @@ __device__ __forceinline__ int block_excl_max(int v, int *warp_tot) {
 // is.)  One packed fp16 compare per pixel pair and source decides the pixels
 // on which the variants agree; the others - the rims of the masks - are
 // collected as bits and evaluated exactly, one pixel at a time, afterwards.
-enum { kRleArith = 0, kRleCode = 1, kRleBound = 2, kRleBoundVec = 3 };
+enum { kRleArith = 0, kRleCode = 1, kRleBound = 2, kRleBoundVec = 3,
+       kRleBytes = 4 };
 
 // One source's share of a BOUND tile: bit r of wk[i] <- source pixel under
 // output pixel (y0 + r, x0 + i) >= x'_c, for the rows of `fastmask` (the
@@ -333,11 +370,22 @@ rle_kernel(const __grid_constant__ RleArgs a) {
   // in flight per SM (one CTA per SM when the bit plane is 128 KiB)
   constexpr bool CODE = MODE == kRleCode;
   constexpr bool BOUND = MODE == kRleBound || MODE == kRleBoundVec;
+  constexpr bool BYTES = MODE == kRleBytes;
   constexpr int kRleThreads = NT;
   extern __shared__ uint32_t bits[];  // [W][Hw]
   __shared__ int warp_tot[kRleThreads / 32];
   __shared__ long long s_base;
   __shared__ uint32_t key_thr[MLC_MAX_CLASSES_SEG];
+  if (BYTES) {
+    // smallest byte value that passes (float)b >= thr: 0 .. 256 (none)
+    if ((int)threadIdx.x < a.C) {
+      const float thr = a.thr[threadIdx.x];
+      key_thr[threadIdx.x] = thr <= 0.f ? 0u
+                             : thr > 255.f ? 256u
+                                           : (uint32_t)ceilf(thr);
+    }
+    __syncthreads();
+  }
   if (CODE || BOUND) {
     if ((int)threadIdx.x < a.C) {
       const float thr = a.thr[threadIdx.x];
@@ -429,6 +477,17 @@ rle_kernel(const __grid_constant__ RleArgs a) {
           if (any) {
             if (raw) code_rows<true>(row0, W, rows, sub, lim_lo, lim_hi, word);
             else code_rows<false>(row0, W, rows, sub, lim_lo, lim_hi, word);
+          }
+        } else if (BYTES) {
+          const uint32_t k = key_thr[c];
+          const uint8_t *row0 = static_cast<const uint8_t *>(a.src.ptr[0]) +
+                                plane_off + (size_t)(yb * 32) * W + x0;
+          if (k == 0) {
+            const uint32_t valid = rows == 32 ? ~0u : (1u << rows) - 1u;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) word[i] = valid;
+          } else if (k < 256) {
+            byte_rows(row0, W, rows, k, word);
           }
         } else if (BOUND) {
           const uint32_t kc = key_thr[c];
@@ -798,11 +857,15 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   const bool bound = (dtype == MLC_F16 || dtype == MLC_F32) && !code && !sm &&
                      W >= 8 && !(a.src.any_xf & MLC_XF_TRANSPOSE) &&
                      !arith_only();
+  // uint8 masks / bin planes with whole 8-byte row segments: packed compares
+  const bool bytes = dtype == MLC_U8 && n_src == 1 && a.src.any_xf == 0 &&
+                     act == MLC_ACT_NONE && (W % 8) == 0 &&
+                     ((uintptr_t)src_dev_ptrs[0] % 8) == 0 && !arith_only();
   // CODE: two 512-thread CTAs per SM when two bit planes (+ slack) fit, so
   // that one streams while the other scans.  BOUND: one 1024-thread CTA
   // (measured: the exact pass of a 512-thread pair costs more than the
   // overlap gains - 2.60 vs 2.36 ms on 512 Severstal 4-flip images).
-  const bool wide = bound || (code && smem > 100 * 1024);
+  const bool wide = bound || ((code || bytes) && smem > 100 * 1024);
   const int nt = wide ? 1024 : 512;
   void (*kern)(RleArgs) =
       dtype == MLC_F16
@@ -819,7 +882,9 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
                                : rle_kernel<float, kRleBound, false, 1024>)
              : sm ? rle_kernel<float, kRleArith, true, 512>
                   : rle_kernel<float, kRleArith, false, 512>)
-                         : rle_kernel<uint8_t, kRleArith, false, 512>;
+      : bytes ? (wide ? rle_kernel<uint8_t, kRleBytes, false, 1024>
+                      : rle_kernel<uint8_t, kRleBytes, false, 512>)
+              : rle_kernel<uint8_t, kRleArith, false, 512>;
   MLC_CUDA(cudaFuncSetAttribute(kern,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)kRleMaxSmem));

@@ -23,6 +23,7 @@ struct HistArgs {
   const uint8_t *gt;
   uint32_t *hist;
   const uint8_t *lut;
+  uint8_t *bins;  // optional [plane][H][W] bin index of every pixel (or null)
   long long n_planes;
   long long plane_px;  // H*W
   int n_cls;
@@ -60,6 +61,26 @@ __device__ __forceinline__ void flush_bins(uint32_t *cnt, int nbins,
     }
   }
   __syncthreads();
+}
+
+// Optional second output of the multi-source kernels: the bin index
+// cnt(p) of every pixel as one byte (B <= 255), so that a later pass - RLE at
+// a threshold the search has yet to choose - reads 1 byte per pixel instead of
+// all the sources again: (p >= thr[k])  <=>  (bin > k).
+__device__ __forceinline__ void store_bins8(uint8_t *dst, const int c[8],
+                                            int nv) {
+  if (nv == 8 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0) {
+    uint2 v;
+    v.x = (uint32_t)c[0] | ((uint32_t)c[1] << 8) | ((uint32_t)c[2] << 16) |
+          ((uint32_t)c[3] << 24);
+    v.y = (uint32_t)c[4] | ((uint32_t)c[5] << 8) | ((uint32_t)c[6] << 16) |
+          ((uint32_t)c[7] << 24);
+    *reinterpret_cast<uint2 *>(dst) = v;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i < nv) dst[i] = (uint8_t)c[i];
+  }
 }
 
 // ---- generic kernel: any number of sources, flips, f16/f32 ---------------
@@ -104,7 +125,8 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
     const long long i1 = min(n_items, i0 + a.items_per_unit);
 
     // bins of one item's eight probabilities -> the warp-lane counters
-    auto bin8 = [&](const float (&p)[8], const uint2 g, const int nv) {
+    auto bin8 = [&](const float (&p)[8], const uint2 g, const int nv,
+                    const size_t px_off) {
       int c[8];
       bool ok = nv == 8;
 #pragma unroll
@@ -120,16 +142,19 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
           red_shared_add(cnt_sa + ((c[i] << 7) | lane4),
                          gb ? 0x10000u : 1u);
         }
+        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, 8);
       } else {  // partial item, guess off by one, NaN / +inf, odd table
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           if (i < nv) {
             const int cc = count_ge(p[i], thr, B, scale, bias);
+            c[i] = cc;
             const uint32_t gb =
                 ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
             red_shared_add(cnt_sa + ((cc << 7) | lane4), gb ? 0x10000u : 1u);
           }
         }
+        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, nv);
       }
     };
     // one item through the bounds-checked loads (any mode, any alignment)
@@ -152,7 +177,8 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
       const PlaneCtx cx = {plane, a.n_planes, a.plane_px, a.n_cls};
       fused_prob8<T, SM>(a.src, plane_off, cx, a.H, a.W, y, x0, nv, inner,
                          a.act, p);
-      bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner), nv);
+      bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner), nv,
+           (size_t)y * a.W + x0);
     };
 
     if (VEC && !SM) {
@@ -167,7 +193,7 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
         float p[8];
         fused_flat8<T>(a.src, plane_off + x0, a.act, p);
         mean8(p, a.src.n);
-        bin8(p, ldg_stream8(gtp + x0), 8);
+        bin8(p, ldg_stream8(gtp + x0), 8, (size_t)x0);
       }
       if (threadIdx.x == 0 && f0 && i0 == 0) item_checked(0);
       if (threadIdx.x == 32 && f1 >= f0 && f1 < n_items && f1 >= i0 &&
@@ -244,7 +270,8 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
     const long long i0 = (long long)sub * a.items_per_unit;
     const long long i1 = min(n_items, i0 + a.items_per_unit);
 
-    auto bin8 = [&](float (&p)[8], const uint2 g, const int nv) {
+    auto bin8 = [&](float (&p)[8], const uint2 g, const int nv,
+                    const size_t px_off) {
       mean8(p, S);
       int c[8];
       bool ok = nv == 8;
@@ -261,16 +288,19 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
           red_shared_add(cnt_sa + ((c[i] << 7) | lane4),
                          gb ? 0x10000u : 1u);
         }
+        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, 8);
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           if (i < nv) {
             const int cc = count_ge(p[i], thr, B, scale, bias);
+            c[i] = cc;
             const uint32_t gb =
                 ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
             red_shared_add(cnt_sa + ((cc << 7) | lane4), gb ? 0x10000u : 1u);
           }
         }
+        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, nv);
       }
     };
     // one item through the window / bounds-checked loads (rows, flips, edges)
@@ -315,7 +345,8 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) p[i] = k == 0 ? v[i] : p[i] + v[i];
       }
-      bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner), nv);
+      bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, nv, inner), nv,
+           (size_t)y * a.W + x0);
     };
 
     if (VEC) {
@@ -347,7 +378,7 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
             }
           }
         }
-        bin8(p, ldg_stream8(gtp + x0), 8);
+        bin8(p, ldg_stream8(gtp + x0), 8, (size_t)x0);
       }
       if (threadIdx.x == 0 && f0 && i0 == 0) item_checked(0);
       if (threadIdx.x == 32 && f1 >= f0 && f1 < n_items && f1 >= i0 &&
@@ -391,7 +422,7 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
             }
           }
         }
-        bin8(p, ldg_stream8(gtp + (size_t)it * 8), 8);
+        bin8(p, ldg_stream8(gtp + (size_t)it * 8), 8, (size_t)it * 8);
         xi += dx;
         y += dy;
         if (xi >= ipr) {
@@ -451,7 +482,8 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
               }
             }
           }
-          bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, 8, true), 8);
+          bin8(p, fetch8_bytes(gtp, a.H, a.W, y, x0, 8, true), 8,
+               (size_t)y * a.W + x0);
         } else {
           item_checked(it);
         }
@@ -978,12 +1010,12 @@ extern "C" int mlc_seg_lut_build(const float *thr_host, int n_thr, int act,
   return MLC_OK;
 }
 
-extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
-                            const int32_t *xform, int n_src, int dtype,
-                            const uint8_t *gt_dev, int64_t n_img, int n_cls,
-                            int H, int W, const float *thr_host, int n_thr,
-                            int act, const uint8_t *lut_dev,
-                            uint32_t *hist_dev, void *stream) {
+static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
+                         int n_src, int dtype, const uint8_t *gt_dev,
+                         int64_t n_img, int n_cls, int H, int W,
+                         const float *thr_host, int n_thr, int act,
+                         const uint8_t *lut_dev, uint32_t *hist_dev,
+                         uint8_t *bins_dev, void *stream) {
   if (int rc = check_thr(thr_host, n_thr)) return rc;
   MLC_REQUIRE(dtype == MLC_F16 || dtype == MLC_F32,
               "dtype %d is not MLC_F16/MLC_F32", dtype);
@@ -1006,6 +1038,7 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   a.gt = gt_dev;
   a.hist = hist_dev;
   a.lut = lut_dev;
+  a.bins = bins_dev;
   a.n_planes = (long long)n_img * n_cls;
   a.plane_px = (long long)H * W;
   a.n_cls = n_cls;
@@ -1022,7 +1055,10 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
   a.bias = 1.0f - thr_host[0] * a.scale;
 
   const int sms = sm_count();
-  const bool table = lut_dev && act != MLC_ACT_SOFTMAX && n_src == 1 &&
+  // (the per-code table kernels do not write bins: one source is cheap to
+  // read again)
+  const bool table = lut_dev && !bins_dev && act != MLC_ACT_SOFTMAX &&
+                     n_src == 1 &&
                      dtype == MLC_F16 && a.flat &&
                      (a.plane_px % 8) == 0 &&
                      ((uintptr_t)src_dev_ptrs[0] % 16) == 0 &&
@@ -1121,6 +1157,30 @@ extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
     MLC_LAUNCH_CHECK("seg_hist_generic");
   }
   return MLC_OK;
+}
+
+extern "C" int mlc_seg_hist(const void *const *src_dev_ptrs,
+                            const int32_t *xform, int n_src, int dtype,
+                            const uint8_t *gt_dev, int64_t n_img, int n_cls,
+                            int H, int W, const float *thr_host, int n_thr,
+                            int act, const uint8_t *lut_dev,
+                            uint32_t *hist_dev, void *stream) {
+  return seg_hist_impl(src_dev_ptrs, xform, n_src, dtype, gt_dev, n_img, n_cls,
+                       H, W, thr_host, n_thr, act, lut_dev, hist_dev, nullptr,
+                       stream);
+}
+
+extern "C" int mlc_seg_hist_bins(const void *const *src_dev_ptrs,
+                                 const int32_t *xform, int n_src, int dtype,
+                                 const uint8_t *gt_dev, int64_t n_img,
+                                 int n_cls, int H, int W,
+                                 const float *thr_host, int n_thr, int act,
+                                 uint32_t *hist_dev, uint8_t *bins_dev,
+                                 void *stream) {
+  MLC_REQUIRE(bins_dev, "bins_dev is null");
+  return seg_hist_impl(src_dev_ptrs, xform, n_src, dtype, gt_dev, n_img, n_cls,
+                       H, W, thr_host, n_thr, act, nullptr, hist_dev, bins_dev,
+                       stream);
 }
 
 extern "C" int mlc_seg_prob(const void *const *src_dev_ptrs,

@@ -19,6 +19,7 @@ __all__ = ['activation_code', 'compose_tta', 'confusion', 'seg_lut',
            'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
            'threshold_grid', 'counts_from_hist', 'rle_strings',
            'rle_strings_host', 'rle_decode', 'rle_parse', 'mask_composite',
+           'rle_from_bins',
            'mask_outline']
 
 
@@ -173,10 +174,14 @@ def seg_lut(thr, activation='sigmoid', device=None):
 
 
 def seg_hist(sources, gt, thr, xforms=None, activation='sigmoid', lut=None,
-             out=None):
+             out=None, bins=False):
     """Fused TTA/ensemble mean + activation + label-conditioned histogram of
     cnt(p) = #{k: p >= thr[k]} (mlc_seg_hist).  Returns int32
-    [n_img, n_cls, 2, B+1] (counts are < 2**31)."""
+    [n_img, n_cls, 2, B+1] (counts are < 2**31).
+
+    ``bins=True`` (mlc_seg_hist_bins) also returns the bin index of every
+    pixel, uint8 [n_img, n_cls, H, W]: ``bins > k`` is the mask at thr[k]
+    (``rle_from_bins``), 1 byte per pixel instead of the sources again."""
     lib = _lib.load()
     sources, ptrs, xf, n, c, h, w = _sources(sources, xforms)
     gt = _need_cuda(gt, 'gt', (torch.uint8,))
@@ -194,12 +199,31 @@ def seg_hist(sources, gt, thr, xforms=None, activation='sigmoid', lut=None,
         _need_cuda(lut, 'lut', (torch.uint8,))
         if lut.numel() != _lib.MLC_LUT_BYTES:
             raise ValueError('lut must come from seg_lut()')
+    if bins:
+        if len(thr) > 255:
+            raise ValueError('bins need n_thr <= 255')
+        bins_out = torch.empty((n, c, h, w), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.mlc_seg_hist_bins(
+                ptrs, xf, len(sources), _dtype_code(sources[0]), _ptr(gt), n,
+                c, h, w, thr_p, len(thr), activation_code(activation),
+                _ptr(out), _ptr(bins_out), _stream()))
+        return out, bins_out
     with torch.cuda.device(dev):
         check(lib.mlc_seg_hist(ptrs, xf, len(sources), _dtype_code(sources[0]),
                                _ptr(gt), n, c, h, w, thr_p, len(thr),
                                activation_code(activation), _ptr(lut),
                                _ptr(out), _stream()))
     return out
+
+
+def rle_from_bins(bins, k_per_class, min_area_per_class=0, capacity=None):
+    """Run-length pairs of the masks (bins > k_c) = (prob >= thr[k_c]) from
+    the per-pixel bin indices ``seg_hist(..., bins=True)`` kept (same return
+    values as ``rle_encode``)."""
+    k = np.asarray(k_per_class, dtype=np.float32) + np.float32(0.5)
+    return rle_encode([bins], k, min_area_per_class, activation=None,
+                      capacity=capacity)
 
 
 def seg_prob(sources, xforms=None, activation='sigmoid'):

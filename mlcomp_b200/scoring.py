@@ -99,15 +99,22 @@ class SegSearch:
         self.n_img = 0
 
     # -- device-resident chunk ------------------------------------------------
-    def add(self, sources, gt, xforms=None):
+    def add(self, sources, gt, xforms=None, keep_bins=False):
         """Score one chunk already in HBM; returns its histograms
-        [n, C, 2, B+1] (int32) for per-image reporting."""
+        [n, C, 2, B+1] (int32) for per-image reporting - with
+        ``keep_bins`` the pair (histograms, per-pixel bin indices uint8
+        [n, C, H, W]) for ``ops.rle_from_bins`` at the point the search picks."""
         if self.record_events:
             ev = (torch.cuda.Event(enable_timing=True),
                   torch.cuda.Event(enable_timing=True))
             ev[0].record()
-        hist = ops.seg_hist(sources, gt, self.thr, xforms=xforms,
-                            activation=self.activation, lut=self.lut)
+        bins = None
+        if keep_bins:
+            hist, bins = ops.seg_hist(sources, gt, self.thr, xforms=xforms,
+                                      activation=self.activation, bins=True)
+        else:
+            hist = ops.seg_hist(sources, gt, self.thr, xforms=xforms,
+                                activation=self.activation, lut=self.lut)
         if self.record_events:
             ev[1].record()
             self.kernel_events.append(ev)
@@ -120,7 +127,7 @@ class SegSearch:
             self.dice_sum += dsum
             self.micro += micro
         self.n_img += hist.shape[0]
-        return hist
+        return (hist, bins) if keep_bins else hist
 
     # -- host-resident chunks: copies overlapped with compute -----------------
     def add_host(self, sources, gt, xforms=None, chunk=64):

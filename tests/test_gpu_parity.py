@@ -759,3 +759,80 @@ def test_composite_and_outline_match_oracle(ops, shape):
                                                            sat))
     with pytest.raises(IndexError):
         ops.mask_composite(dm, colors[:c - 1] if c > 1 else [])
+
+
+# ------------------------------------------------------- per-pixel bin output
+@pytest.mark.parametrize('dtype', [torch.float16, torch.float32])
+@pytest.mark.parametrize('shape,tags', [
+    ((2, 2, 16, 24), [[]]),                                   # flat, aligned
+    ((2, 3, 35, 53), [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]),
+    ((2, 2, 32, 64), [[], ['hflip'], ['vflip']]),             # aligned rows
+    ((1, 2, 21, 37), [[], []]),                               # flat, odd size
+    ((1, 1, 24, 40), [['transpose']]),
+])
+def test_seg_hist_bins_are_the_pixel_bin_indices(ops, dtype, shape, tags):
+    n, c, h, w = shape
+    srcs, gt = synth_seg(n, c, h, w, seed=h + w, dtype=dtype, n_src=len(tags))
+    if tags == [['transpose']]:
+        seen = [forward_tta(s, t) for s, t in zip(srcs, tags)]
+    else:
+        seen = [forward_tta(s, t) for s, t in zip(srcs, tags)]
+    dev_src = [s.to(DEV) for s in seen]
+    thr = oracle.threshold_grid(100)
+    hist, bins = ops.seg_hist(dev_src, gt.to(DEV), thr, xforms=tags, bins=True)
+    assert torch.equal(hist, ops.seg_hist(dev_src, gt.to(DEV), thr,
+                                          xforms=tags))
+    prob = ops.seg_prob(dev_src, xforms=tags).cpu().numpy()
+    want = np.searchsorted(thr, prob, side='right').astype(np.uint8)
+    assert np.array_equal(bins.cpu().numpy(), want)
+    # masks at chosen grid points: from the bins == from the sources
+    ks = [10, 50, 90][:c] + [50] * max(0, c - 3)
+    a = ops.rle_from_bins(bins, ks, 5)
+    b = ops.rle_encode(dev_src, [thr[k] for k in ks], 5, xforms=tags)
+    assert ops.rle_strings(*a[:3]) == ops.rle_strings(*b[:3])
+    assert torch.equal(a[3], b[3])
+
+
+def test_seg_hist_bins_unaligned_views_and_nan(ops):
+    """Planes that start at odd element offsets (slices of a larger tensor)
+    and NaN pixels (bin 0)."""
+    rng = np.random.default_rng(8)
+    n, c, h, w = 3, 2, 9, 13
+    big = torch.from_numpy(rng.normal(0, 2, (n + 1, c, h, w))
+                           .astype(np.float16)).to(DEV)
+    src = big.view(-1)[3:3 + n * c * h * w].view(n, c, h, w)
+    src.view(-1)[::17] = float('nan')
+    gt = torch.from_numpy((rng.random((n, c, h, w)) < 0.3)
+                          .astype(np.uint8)).to(DEV)
+    thr = oracle.threshold_grid(100)
+    assert not src.is_contiguous() or src.data_ptr() % 16 != 0
+    hist, bins = ops.seg_hist([src, src], gt, thr, bins=True)
+    prob = ops.seg_prob([src, src]).cpu().numpy()
+    with np.errstate(invalid='ignore'):
+        want = np.where(np.isnan(prob), 0,
+                        np.searchsorted(thr, np.nan_to_num(prob), side='right'))
+    assert np.array_equal(bins.cpu().numpy(), want.astype(np.uint8))
+
+
+def test_rle_uint8_planes_any_byte_threshold(ops):
+    """uint8 sources (masks, bin planes) through the packed byte compare:
+    every kind of threshold, values over the whole byte range."""
+    rng = np.random.default_rng(21)
+    n, c, h, w = 2, 6, 45, 64
+    x = rng.integers(0, 256, (n, c, h, w)).astype(np.uint8)
+    x[0, 0] = 0
+    x[1, 1] = 255
+    src = torch.from_numpy(x).to(DEV)
+    for thr in ([0.5, 1.0, 127.5, 128.0, 254.5, 255.0],
+                [0.0, -3.0, 255.5, 300.0, 63.2, 200.0]):
+        thr = np.asarray(thr, np.float32)
+        runs, off, cnt, area = ops.rle_encode([src], thr, 0, activation=None)
+        got = ops.rle_strings(runs, off, cnt)
+        k = 0
+        for i in range(n):
+            for j in range(c):
+                mask = x[i, j].astype(np.float32) >= thr[j]
+                assert got[k] == oracle.rle_encode(mask.astype(np.uint8)), \
+                    (i, j, thr[j])
+                assert int(area[i, j]) == int(mask.sum())
+                k += 1

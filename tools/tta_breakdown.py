@@ -49,3 +49,9 @@ t = timeit(lambda: ops.rle_encode(s32, [0.5] * 4, [256] * 4, xforms=xf, capacity
 print('rle_tta4_fp32', round(t, 3), 'ms', round(px32 * 16 / t / 1e6 / 6550.4, 3), 'of HBM peak')
 t = timeit(lambda: ops.rle_encode([s32[0]], [0.5] * 4, [256] * 4, capacity=cap))
 print('rle_1src_fp32', round(t, 3), 'ms', round(px32 * 4 / t / 1e6 / 6550.4, 3), 'of HBM peak')
+# per-pixel bins: cost of writing them in pass 1, and RLE from them
+t = timeit(lambda: ops.seg_hist(srcs, gt, thr, xforms=xf, bins=True))
+print('hist_tta4_rows_with_bins', round(t, 3), 'ms')
+_, bins = ops.seg_hist(srcs, gt, thr, xforms=xf, bins=True)
+t = timeit(lambda: ops.rle_from_bins(bins, [50] * 4, [256] * 4, capacity=cap))
+print('rle_from_bins', round(t, 3), 'ms')
