@@ -769,6 +769,9 @@ def test_composite_and_outline_match_oracle(ops, shape):
     ((2, 2, 32, 64), [[], ['hflip'], ['vflip']]),             # aligned rows
     ((1, 2, 21, 37), [[], []]),                               # flat, odd size
     ((1, 1, 24, 40), [['transpose']]),
+    ((1, 1, 256, 320), [[], []]),           # plane split into several units
+    ((1, 1, 256, 320), [[], ['hflip']]),
+    ((1, 1, 250, 323), [[], ['vflip']]),
 ])
 def test_seg_hist_bins_are_the_pixel_bin_indices(ops, dtype, shape, tags):
     n, c, h, w = shape
