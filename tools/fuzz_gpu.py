@@ -80,6 +80,21 @@ def main():
                     assert np.array_equal(
                         hh[i, j], oracle.bin_counts(gt[i, j], p[i, j], thr)), \
                         ('hist', i, j)
+            if b <= 255:
+                h2, bins = ops.seg_hist(dev_src, torch.from_numpy(gt).to(DEV),
+                                        thr, xforms=tags, activation=act,
+                                        bins=True)
+                assert torch.equal(h2, hist), ('hist with bins',)
+                with np.errstate(invalid='ignore'):
+                    wb = np.where(np.isnan(p), 0, np.searchsorted(
+                        thr, np.nan_to_num(p), side='right'))
+                assert np.array_equal(bins.cpu().numpy(), wb), ('bins',)
+                kk = rng.integers(0, b, c)
+                ra = ops.rle_from_bins(bins, kk, 3)
+                rb = ops.rle_encode(dev_src, thr[kk], 3, xforms=tags,
+                                    activation=act)
+                assert ops.rle_strings(*ra[:3]) == ops.rle_strings(*rb[:3]), \
+                    ('rle from bins',)
             t_c = rng.random(c).astype(np.float32)
             a_c = rng.integers(0, 40, c).astype(np.int32)
             runs, off, cnt, area = ops.rle_encode(dev_src, t_c, a_c,
