@@ -64,7 +64,15 @@ def ulp_diff(a, b):
                                        (3000, 64, torch.float32),
                                        (2000, 100, torch.float32),
                                        (500, 1000, torch.float16),
-                                       (1, 1, torch.float32)])
+                                       (1, 1, torch.float32),
+                                       (3001, 65, torch.float32),
+                                       (2500, 255, torch.float16),
+                                       (1000, 256, torch.float16),
+                                       (777, 7, torch.float16),
+                                       (33, 200, torch.float32),
+                                       (999, 257, torch.float16),
+                                       (400, 1001, torch.float16),
+                                       (100001, 4, torch.float16)])
 def test_confusion_bit_exact(ops, n, c, dtype):
     rng = np.random.default_rng(n + c)
     y = rng.integers(0, c, n)
@@ -108,6 +116,32 @@ def test_confusion_nan_and_foreign_labels(ops):
     assert np.array_equal(am.cpu().numpy(), logits.argmax(axis=1))
     assert np.array_equal(cm.cpu().numpy(), oracle.confusion_numpy(y, logits))
     assert int(stats[1]) == 3
+
+
+@pytest.mark.parametrize('c', [5, 64, 100, 300])
+@pytest.mark.parametrize('dtype', [torch.float16, torch.float32])
+def test_confusion_unaligned_rows_nan_ties(ops, c, dtype):
+    """preds that do not start on a 16-byte boundary (a view into a larger
+    buffer), NaN / inf rows and ties, for every kernel variant."""
+    rng = np.random.default_rng(c)
+    n = 1500
+    logits = rng.normal(0, 1, (n, c)).astype(np.float32)
+    logits[3, c // 2] = np.nan
+    logits[4, 1] = logits[4, c - 1] = np.nan
+    logits[5, :] = np.inf
+    logits[6, :] = -np.inf
+    logits[7:200, 0] = logits[7:200, c - 1] = 9.0          # ties -> index 0
+    y = rng.integers(0, c, n)
+    p = torch.from_numpy(logits).to(dtype)
+    buf = torch.zeros(n * c + 3, dtype=dtype, device=DEV)
+    view = buf[3:].view(n, c)
+    view.copy_(p)
+    assert view.data_ptr() % 16 != 0
+    ref_in = p.float().numpy()
+    cm, stats, am = ops.confusion(view, torch.from_numpy(y).to(DEV),
+                                  want_argmax=True)
+    assert np.array_equal(am.cpu().numpy(), ref_in.argmax(axis=1))
+    assert np.array_equal(cm.cpu().numpy(), oracle.confusion_numpy(y, ref_in))
 
 
 # ------------------------------------------------------------- probabilities
