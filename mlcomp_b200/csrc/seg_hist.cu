@@ -92,9 +92,13 @@ __device__ __forceinline__ void store_bins8(uint8_t *dst, const int c[8],
 // table and costs one LDS.64 on a near-uniform one.
 // VEC: flat mode with 16-byte-aligned tensors - every full item after the
 // first of a plane is loaded with fused_flat8.
-template <typename T, bool VEC, bool SM>
+// MODE 0: any geometry; 1 (VEC): flat aligned planes; 2: flipped rows of
+// whole aligned items (fused_rows8) - the fp32 / no-activation twin of
+// seg_hist_tab<2>.
+template <typename T, int MODE, bool SM>
 __global__ void __launch_bounds__(kHistThreads, 2)
 seg_hist_generic(const __grid_constant__ HistArgs a) {
+  constexpr bool VEC = MODE == 1;
   extern __shared__ uint32_t smem[];
   const int B = a.B, nbins = B + 1;
   const float scale = a.scale, bias = a.bias;
@@ -199,6 +203,23 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
       if (threadIdx.x == 32 && f1 >= f0 && f1 < n_items && f1 >= i0 &&
           f1 < i1)
         item_checked(f1);
+    } else if (MODE == 2 && !SM) {
+      const int ipr = a.items_per_row;  // W / 8, every item full
+      const int dy = (int)blockDim.x / ipr, dx = (int)blockDim.x - dy * ipr;
+      int it = (int)i0 + (int)threadIdx.x;
+      int y = it / ipr, xi = it - y * ipr;
+      for (; it < (int)i1; it += blockDim.x) {
+        float p[8];
+        fused_rows8<T>(a.src, plane_off, a.H, ipr, y, xi, a.act, p);
+        mean8(p, a.src.n);
+        bin8(p, ldg_stream8(gtp + (size_t)it * 8), 8, (size_t)it * 8);
+        xi += dx;
+        y += dy;
+        if (xi >= ipr) {
+          xi -= ipr;
+          ++y;
+        }
+      }
     } else {
       for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x)
         item_checked(it);
@@ -1121,6 +1142,12 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
     bool vec = a.flat && ((uintptr_t)gt_dev % 16) == 0;
     for (int i = 0; i < n_src; ++i)
       vec = vec && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
+    // flipped rows of whole aligned items (e.g. 256 x 1600 TTA)
+    bool vrows = !a.flat && !(a.src.any_xf & MLC_XF_TRANSPOSE) &&
+                 (W % 8) == 0 && ((uintptr_t)gt_dev % 8) == 0 &&
+                 a.items_per_plane < (1ll << 31) - kTabThreads;
+    for (int i = 0; i < n_src; ++i)
+      vrows = vrows && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
     if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID && hist_variant() != 4) {
       // activation table in shared memory: one 1024-thread CTA per SM
       const size_t tab_smem = kActTabBytes;
@@ -1131,28 +1158,25 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
       // kernel is LSU-bound, not balance-bound (grids of 2x / 4x / one CTA
       // per unit measured within 1 %)
       const int tgrid = (int)min(n_units, (long long)sms);
-      // flipped rows of whole aligned items (e.g. 256 x 1600 TTA)
-      bool vrows = !a.flat && !(a.src.any_xf & MLC_XF_TRANSPOSE) &&
-                   (W % 8) == 0 && ((uintptr_t)gt_dev % 8) == 0 &&
-                   a.items_per_plane < (1ll << 31) - kTabThreads;
-      for (int i = 0; i < n_src; ++i)
-        vrows = vrows && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
       void (*tk)(HistArgs) = vec ? seg_hist_tab<1>
                              : vrows ? seg_hist_tab<2> : seg_hist_tab<0>;
       MLC_CUDA(cudaFuncSetAttribute(
           tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tab_smem));
       tk<<<tgrid, (vec || vrows) ? kTabThreads : kTabRowThreads, tab_smem, st>>>(a);
-    } else if (act == MLC_ACT_SOFTMAX) {
-      if (dtype == MLC_F16)
-        seg_hist_generic<__half, false, true><<<grid, kHistThreads, smem, st>>>(a);
-      else
-        seg_hist_generic<float, false, true><<<grid, kHistThreads, smem, st>>>(a);
-    } else if (dtype == MLC_F16) {
-      if (vec) seg_hist_generic<__half, true, false><<<grid, kHistThreads, smem, st>>>(a);
-      else seg_hist_generic<__half, false, false><<<grid, kHistThreads, smem, st>>>(a);
     } else {
-      if (vec) seg_hist_generic<float, true, false><<<grid, kHistThreads, smem, st>>>(a);
-      else seg_hist_generic<float, false, false><<<grid, kHistThreads, smem, st>>>(a);
+      const bool sm = act == MLC_ACT_SOFTMAX;
+      void (*gk)(HistArgs);
+      if (dtype == MLC_F16)
+        gk = sm ? seg_hist_generic<__half, 0, true>
+             : vec ? seg_hist_generic<__half, 1, false>
+             : vrows ? seg_hist_generic<__half, 2, false>
+                     : seg_hist_generic<__half, 0, false>;
+      else
+        gk = sm ? seg_hist_generic<float, 0, true>
+             : vec ? seg_hist_generic<float, 1, false>
+             : vrows ? seg_hist_generic<float, 2, false>
+                     : seg_hist_generic<float, 0, false>;
+      gk<<<grid, kHistThreads, smem, st>>>(a);
     }
     MLC_LAUNCH_CHECK("seg_hist_generic");
   }
