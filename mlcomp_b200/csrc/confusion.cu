@@ -137,18 +137,27 @@ confusion_wide(const __grid_constant__ ConfArgs a) {
     int bi = 0x7fffffff;  // "no candidate yet"
     if (sizeof(T) == 2 && (a.C & 1) == 0 &&
         (reinterpret_cast<uintptr_t>(preds) & 3) == 0) {
-      // fp16 rows of even length start on a word: two classes per load
+      // fp16 rows of even length start on a word: two classes per load, eight
+      // loads per lane issued before the first compare
       const uint32_t *row2 = reinterpret_cast<const uint32_t *>(row);
-#pragma unroll 4
-      for (int c2 = lane; c2 < (a.C >> 1); c2 += 32) {
-        const uint32_t w = ldg_nc32(row2 + c2);
-        const float2 f =
-            __half22float2(*reinterpret_cast<const __half2 *>(&w));
-        const int c = 2 * c2;
-        if (bi == 0x7fffffff || beats(f.x, c, bv, bi)) { bv = f.x; bi = c; }
-        if (beats(f.y, c + 1, bv, bi)) { bv = f.y; bi = c + 1; }
+      const int C2 = a.C >> 1;
+      for (int c0 = lane; c0 < C2; c0 += 256) {
+        uint32_t w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          w[u] = c0 + 32 * u < C2 ? ldg_nc32(row2 + c0 + 32 * u) : 0u;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = 2 * (c0 + 32 * u);
+          if (c < a.C) {
+            const float2 f =
+                __half22float2(*reinterpret_cast<const __half2 *>(&w[u]));
+            if (bi == 0x7fffffff || beats(f.x, c, bv, bi)) { bv = f.x; bi = c; }
+            if (beats(f.y, c + 1, bv, bi)) { bv = f.y; bi = c + 1; }
+          }
+        }
       }
-    } else {
+    } else {  // (batching eight loads here measured slower: 1.22 vs 1.03 ms)
 #pragma unroll 4
       for (int c = lane; c < a.C; c += 32) {
         const float v = to_f32<T>(row[c]);
