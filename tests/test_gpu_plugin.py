@@ -321,3 +321,26 @@ def test_infer_keeps_logits_on_device(tmp_path):
     gen = infer(DS(False), path, batch_size=4, batch_mode=True, num_workers=0)
     counts = [b['count'] for b in gen]
     assert counts == [4, 3]
+
+
+def test_add_host_with_run_length_ground_truth():
+    """SegSearch.add_host(gt_runs=...): same scores as with dense planes."""
+    from mlcomp_b200 import ops, scoring
+    rng = np.random.default_rng(9)
+    n, c, h, w = 11, 3, 40, 56
+    gt = (rng.random((n, c, h, w)) < 0.2).astype(np.uint8)
+    gt[2] = 0
+    logits = torch.from_numpy((6 * (gt - 0.5) + rng.normal(0, 2, gt.shape))
+                              .astype(np.float16))
+    g = torch.from_numpy(gt)
+    a = scoring.SegSearch(c, min_areas=(0, 50))
+    a.add_host([logits], g, chunk=4)
+    want = a.result()
+    runs = tuple(t.cpu() for t in
+                 ops.rle_encode([g.to(DEV)], 0.5, 0, activation=None)[:3])
+    b = scoring.SegSearch(c, min_areas=(0, 50))
+    b.add_host([logits], None, chunk=4, gt_runs=runs)
+    got = b.result()
+    assert np.array_equal(got['score'], want['score'])
+    assert np.array_equal(got['micro_T'], want['micro_T'])
+    assert got['n_img'] == n
