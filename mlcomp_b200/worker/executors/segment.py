@@ -75,11 +75,18 @@ class _SegInputs:
 class ValidSegment(_SegInputs, Valid):
     def __init__(self, logits=None, tta=None, targets=None, imgs=None,
                  bins=100, min_areas=(0,), activation='sigmoid',
-                 report_threshold=0.5, colors=None, **kwargs):
+                 report_threshold=0.5, colors=None, targets_rle=None,
+                 **kwargs):
         kwargs.setdefault('layout', 'img_segment')
         super().__init__(**kwargs)
         self._init_inputs(logits, tta, activation)
         self.targets = _open(targets)
+        # ground truth in its at-rest form: a csv with an ``EncodedPixels``
+        # column (one row per image x class, in that order; what
+        # contrib/transform/rle.py:16-31 ``rle2mask`` is fed from) or the list
+        # of strings itself - parsed once, decoded per part on the device
+        self.targets_rle = targets_rle
+        self._gt_runs = None
         self.imgs = imgs
         self.thr = ops.threshold_grid(int(bins))
         self.min_areas = min_areas
@@ -107,12 +114,32 @@ class ValidSegment(_SegInputs, Valid):
             self.search = scoring.SegSearch(n_cls, self.thr, self.min_areas,
                                             activation=act)
         lo, hi = self.part
-        gt = _to_device(self.targets[lo:hi], torch.uint8)
+        gt = self._targets(lo, hi, tensors[0], tags[0])
         hist = self.search.add(tensors, gt, tags)
         per_plane = ops.plane_dice(hist, [self.report_k] * n_cls, [0] * n_cls)
         res = per_plane.mean(dim=1).cpu().numpy()
         self.scores.extend(res.tolist())
         return res
+
+    def _targets(self, lo, hi, like, tags0):
+        """uint8 planes [hi-lo, C, H, W] of the part on the device."""
+        if self.targets_rle is None:
+            return _to_device(self.targets[lo:hi], torch.uint8)
+        c = like.shape[1]
+        h, w = like.shape[2:]
+        if 'transpose' in tags0:
+            h, w = w, h
+        if self._gt_runs is None:
+            rows = self.targets_rle
+            if isinstance(rows, str):
+                import pandas as pd
+                rows = pd.read_csv(rows, keep_default_na=False)[
+                    'EncodedPixels'].tolist()
+            runs, off, cnt = ops.rle_parse([str(r) for r in rows])
+            self._gt_runs = (runs, off.reshape(-1), cnt.reshape(-1))
+        runs, off, cnt = self._gt_runs
+        return ops.rle_decode(runs, off[lo * c:hi * c], cnt[lo * c:hi * c],
+                              h, w).view(hi - lo, c, h, w)
 
     def score_final(self):
         out = self.search.result()
@@ -130,7 +157,8 @@ class ValidSegment(_SegInputs, Valid):
         mask = (prob >= float(self.thr[self.report_k])).to(torch.uint8)
         self.builder.process_pred(
             imgs=self.imgs[lo:lo + k], preds={'pred': mask.cpu().numpy()},
-            targets=np.asarray(self.targets[lo:lo + k]),
+            targets=self._targets(lo, lo + k, tensors[0],
+                                  tags[0]).cpu().numpy(),
             scores={'dice': scores})
 
     def plot_final(self, score):

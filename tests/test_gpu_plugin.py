@@ -344,3 +344,40 @@ def test_add_host_with_run_length_ground_truth():
     assert np.array_equal(got['score'], want['score'])
     assert np.array_equal(got['micro_T'], want['micro_T'])
     assert got['n_img'] == n
+
+
+def test_valid_segment_with_rle_targets(tmp_path, monkeypatch):
+    """``targets_rle`` (csv of EncodedPixels, the competitions' at-rest form)
+    gives the same search result as dense ``targets``."""
+    import pandas as pd
+    from mlcomp_b200.worker.executors import ValidSegment
+    monkeypatch.chdir(tmp_path)
+    rng = np.random.default_rng(17)
+    n, c, h, w = 9, 2, 24, 40
+    gt = (rng.random((n, c, h, w)) < 0.25).astype(np.uint8)
+    gt[1] = 0
+    logits = (6 * (gt - 0.5) + rng.normal(0, 2, gt.shape)).astype(np.float16)
+    rows = [{'ImageId': f'{i}_{j + 1}',
+             'EncodedPixels': oracle.rle_encode(gt[i, j])}
+            for i in range(n) for j in range(c)]
+    pd.DataFrame(rows).to_csv('train.csv', index=False)
+    from mlcomp_b200.worker import store
+
+    def run(ex):
+        sess = store.MemorySession()
+        dag = sess.add(store.Dag(name='d', img_size=0))
+        task = sess.add(store.Task(name='v', dag=dag.id))
+        ex.session = sess
+        return ex(task=task, task_provider=sess, dag=dag)
+
+    dense = ValidSegment(logits=[logits], targets=gt, part_size=4,
+                         min_areas=[0, 20], plot_count=2,
+                         imgs=np.zeros((n, h, w, 3), np.uint8), name='seg')
+    want = run(dense)
+    rle = ValidSegment(logits=[logits], targets_rle='train.csv', part_size=4,
+                       min_areas=[0, 20], plot_count=2,
+                       imgs=np.zeros((n, h, w, 3), np.uint8), name='seg')
+    got = run(rle)
+    assert got == want
+    assert np.array_equal(rle.search.result()['score'],
+                          dense.search.result()['score'])
