@@ -888,7 +888,13 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   MLC_CUDA(cudaFuncSetAttribute(kern,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)kRleMaxSmem));
-  const int per_sm = (int)max((size_t)1, min((size_t)4, (220 * 1024) / (smem + 1024)));
+  // persistent grid = exactly the CTAs that are resident at once (registers,
+  // threads and shared memory all count): a larger grid would run its last
+  // CTAs as a second, half-empty wave
+  int per_sm = 1;
+  MLC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt,
+                                                         smem));
+  per_sm = max(1, per_sm);
   const int grid = (int)min(a.n_planes, (long long)per_sm * sm_count());
   kern<<<grid, nt, smem, st>>>(a);
   MLC_LAUNCH_CHECK("rle_kernel");
