@@ -95,7 +95,10 @@ __device__ __forceinline__ void store_bins8(uint8_t *dst, const int c[8],
 // MODE 0: any geometry; 1 (VEC): flat aligned planes; 2: flipped rows of
 // whole aligned items (fused_rows8) - the fp32 / no-activation twin of
 // seg_hist_tab<2>.
-template <typename T, int MODE, bool SM>
+// BINS: also write the per-pixel bin index (a separate instantiation: the
+// plain one pays nothing for it - measured 6-10 % on the table kernel when
+// it was a run-time test).
+template <typename T, int MODE, bool SM, bool BINS>
 __global__ void __launch_bounds__(kHistThreads, 2)
 seg_hist_generic(const __grid_constant__ HistArgs a) {
   constexpr bool VEC = MODE == 1;
@@ -146,7 +149,7 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
           red_shared_add(cnt_sa + ((c[i] << 7) | lane4),
                          gb ? 0x10000u : 1u);
         }
-        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, 8);
+        if (BINS) store_bins8(a.bins + plane_off + px_off, c, 8);
       } else {  // partial item, guess off by one, NaN / +inf, odd table
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -158,7 +161,7 @@ seg_hist_generic(const __grid_constant__ HistArgs a) {
             red_shared_add(cnt_sa + ((cc << 7) | lane4), gb ? 0x10000u : 1u);
           }
         }
-        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, nv);
+        if (BINS) store_bins8(a.bins + plane_off + px_off, c, nv);
       }
     };
     // one item through the bounds-checked loads (any mode, any alignment)
@@ -255,7 +258,7 @@ constexpr int kTabRowThreads = MLC_ROW_THREADS;
 // 2: flipped sources (no transpose) whose rows are a whole number of aligned
 // 16-byte items - the flips are index arithmetic on items, every load is one
 // 128-bit load and up to four sources are in flight together.
-template <int MODE>
+template <int MODE, bool BINS>
 __global__ void __launch_bounds__(MODE == 0 ? kTabRowThreads : kTabThreads, 1)
 seg_hist_tab(const __grid_constant__ HistArgs a) {
   constexpr bool VEC = MODE == 1;
@@ -309,7 +312,7 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
           red_shared_add(cnt_sa + ((c[i] << 7) | lane4),
                          gb ? 0x10000u : 1u);
         }
-        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, 8);
+        if (BINS) store_bins8(a.bins + plane_off + px_off, c, 8);
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -321,7 +324,7 @@ seg_hist_tab(const __grid_constant__ HistArgs a) {
             red_shared_add(cnt_sa + ((cc << 7) | lane4), gb ? 0x10000u : 1u);
           }
         }
-        if (a.bins) store_bins8(a.bins + plane_off + px_off, c, nv);
+        if (BINS) store_bins8(a.bins + plane_off + px_off, c, nv);
       }
     };
     // one item through the window / bounds-checked loads (rows, flips, edges)
@@ -1158,24 +1161,28 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
       // kernel is LSU-bound, not balance-bound (grids of 2x / 4x / one CTA
       // per unit measured within 1 %)
       const int tgrid = (int)min(n_units, (long long)sms);
-      void (*tk)(HistArgs) = vec ? seg_hist_tab<1>
-                             : vrows ? seg_hist_tab<2> : seg_hist_tab<0>;
+      void (*tk)(HistArgs) =
+          bins_dev ? (vec ? seg_hist_tab<1, true>
+                      : vrows ? seg_hist_tab<2, true> : seg_hist_tab<0, true>)
+                   : (vec ? seg_hist_tab<1, false>
+                      : vrows ? seg_hist_tab<2, false>
+                              : seg_hist_tab<0, false>);
       MLC_CUDA(cudaFuncSetAttribute(
           tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tab_smem));
       tk<<<tgrid, (vec || vrows) ? kTabThreads : kTabRowThreads, tab_smem, st>>>(a);
     } else {
       const bool sm = act == MLC_ACT_SOFTMAX;
       void (*gk)(HistArgs);
+#define MLC_GK(T, B)                                              \
+  (sm ? seg_hist_generic<T, 0, true, B>                           \
+   : vec ? seg_hist_generic<T, 1, false, B>                       \
+   : vrows ? seg_hist_generic<T, 2, false, B>                     \
+           : seg_hist_generic<T, 0, false, B>)
       if (dtype == MLC_F16)
-        gk = sm ? seg_hist_generic<__half, 0, true>
-             : vec ? seg_hist_generic<__half, 1, false>
-             : vrows ? seg_hist_generic<__half, 2, false>
-                     : seg_hist_generic<__half, 0, false>;
+        gk = bins_dev ? MLC_GK(__half, true) : MLC_GK(__half, false);
       else
-        gk = sm ? seg_hist_generic<float, 0, true>
-             : vec ? seg_hist_generic<float, 1, false>
-             : vrows ? seg_hist_generic<float, 2, false>
-                     : seg_hist_generic<float, 0, false>;
+        gk = bins_dev ? MLC_GK(float, true) : MLC_GK(float, false);
+#undef MLC_GK
       gk<<<grid, kHistThreads, smem, st>>>(a);
     }
     MLC_LAUNCH_CHECK("seg_hist_generic");
