@@ -967,6 +967,35 @@ struct ProbArgs {
   long long items_per_plane;
 };
 
+// Aligned layouts (planes a whole number of 8-element items, 16-byte aligned
+// tensors): one 128-bit load per source and item, two 128-bit stores.
+// ROWS: flipped sources, rows a whole number of items (fused_rows8);
+// otherwise no transforms at all - the tensor is one flat array.
+template <typename T, bool ROWS>
+__global__ void __launch_bounds__(256)
+seg_prob_vec_kernel(const __grid_constant__ ProbArgs a) {
+  const long long ipp = a.plane_px >> 3;  // items per plane
+  const long long total = a.n_planes * ipp;
+  const int ipr = a.W >> 3;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+       g < total; g += (long long)gridDim.x * blockDim.x) {
+    float p[8];
+    if (ROWS) {
+      const long long plane = g / ipp;
+      const int it = (int)(g - plane * ipp);
+      const int y = it / ipr;
+      fused_rows8<T>(a.src, (size_t)plane * a.plane_px, a.H, ipr, y,
+                     it - y * ipr, a.act, p);
+    } else {
+      fused_flat8<T>(a.src, (size_t)g * 8, a.act, p);
+    }
+    mean8(p, a.src.n);
+    float4 *o = reinterpret_cast<float4 *>(a.prob + (size_t)g * 8);
+    o[0] = make_float4(p[0], p[1], p[2], p[3]);
+    o[1] = make_float4(p[4], p[5], p[6], p[7]);
+  }
+}
+
 template <typename T, bool SM>
 __global__ void __launch_bounds__(256)
 seg_prob_kernel(const __grid_constant__ ProbArgs a) {
@@ -1244,7 +1273,22 @@ extern "C" int mlc_seg_prob(const void *const *src_dev_ptrs,
   const long long total = a.n_planes * a.items_per_plane;
   const int grid = (int)min((total + 255) / 256, 32ll * sm_count());
   cudaStream_t st = (cudaStream_t)stream;
-  if (act == MLC_ACT_SOFTMAX) {
+  bool aligned = ((long long)H * W) % 8 == 0 && ((uintptr_t)prob_dev % 16) == 0;
+  for (int k = 0; k < n_src; ++k)
+    aligned = aligned && ((uintptr_t)src_dev_ptrs[k] % 16) == 0;
+  const bool flat = aligned && a.src.any_xf == 0;
+  const bool rows = aligned && !flat && (W % 8) == 0 &&
+                    !(a.src.any_xf & MLC_XF_TRANSPOSE);
+  if (act != MLC_ACT_SOFTMAX && (flat || rows)) {
+    const long long items = a.n_planes * (a.plane_px / 8);
+    const int vgrid = (int)min((items + 255) / 256, 32ll * sm_count());
+    void (*vk)(ProbArgs) =
+        dtype == MLC_F16 ? (rows ? seg_prob_vec_kernel<__half, true>
+                                 : seg_prob_vec_kernel<__half, false>)
+                         : (rows ? seg_prob_vec_kernel<float, true>
+                                 : seg_prob_vec_kernel<float, false>);
+    vk<<<vgrid, 256, 0, st>>>(a);
+  } else if (act == MLC_ACT_SOFTMAX) {
     if (dtype == MLC_F16) seg_prob_kernel<__half, true><<<grid, 256, 0, st>>>(a);
     else seg_prob_kernel<float, true><<<grid, 256, 0, st>>>(a);
   } else {
