@@ -71,20 +71,32 @@ rle_decode_kernel(const __grid_constant__ DecArgs a) {
       }
     }
     __syncthreads();
-    // row-major bytes, 4 pixels per thread per step (W % 4 tail handled)
+    // row-major bytes: a thread takes 4 columns x 32 rows - four column
+    // words, then one 4-byte store per row (a warp's stores of a row are 128
+    // contiguous bytes); ~3 instructions per pixel
     const int w4 = (W + 3) >> 2;
-    for (long long i = threadIdx.x; i < (long long)H * w4; i += kDecThreads) {
-      const int y = (int)(i / w4), x0 = (int)(i - (long long)y * w4) * 4;
-      uint32_t v = 0;
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (x0 + k < W)
-          v |= ((bits[(x0 + k) * Hp + (y >> 5)] >> (y & 31)) & 1u) << (8 * k);
-      uint8_t *o = out + (long long)y * W + x0;
-      if (x0 + 4 <= W && ((reinterpret_cast<uintptr_t>(o) & 3) == 0)) {
-        *reinterpret_cast<uint32_t *>(o) = v;
-      } else {
-        for (int k = 0; k < 4 && x0 + k < W; ++k) o[k] = (uint8_t)(v >> (8 * k));
+    const int Hw = a.Hw;
+    for (int i = threadIdx.x; i < Hw * w4; i += kDecThreads) {
+      const int yb = i / w4, x0 = (i - yb * w4) * 4;
+      uint32_t c0 = bits[x0 * Hp + yb];
+      uint32_t c1 = x0 + 1 < W ? bits[(x0 + 1) * Hp + yb] : 0u;
+      uint32_t c2 = x0 + 2 < W ? bits[(x0 + 2) * Hp + yb] : 0u;
+      uint32_t c3 = x0 + 3 < W ? bits[(x0 + 3) * Hp + yb] : 0u;
+      const int rows = min(32, H - yb * 32);
+      uint8_t *o = out + (long long)(yb * 32) * W + x0;
+      const bool vec = x0 + 4 <= W && (W & 3) == 0 &&
+                       (reinterpret_cast<uintptr_t>(o) & 3) == 0;
+      for (int r = 0; r < rows; ++r) {
+        const uint32_t v = (c0 & 1u) | ((c1 & 1u) << 8) | ((c2 & 1u) << 16) |
+                           ((c3 & 1u) << 24);
+        c0 >>= 1; c1 >>= 1; c2 >>= 1; c3 >>= 1;
+        if (vec) {
+          *reinterpret_cast<uint32_t *>(o) = v;
+        } else {
+          for (int k = 0; k < 4 && x0 + k < W; ++k)
+            o[k] = (uint8_t)(v >> (8 * k));
+        }
+        o += W;
       }
     }
     __syncthreads();
