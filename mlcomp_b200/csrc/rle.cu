@@ -64,13 +64,19 @@ constexpr uint32_t kKeyNegInf = 0x03FFu, kKeyPosInf = 0xFC00u;
 
 // 8 columns x `rows` rows of one fp16 plane -> 8 column words (bit r = row r
 // passes).  RAW: compare the raw codes, else their order-preserving keys.
-template <bool RAW>
-__device__ __forceinline__ void code_rows(const __half *row0, int W, int rows,
-                                          uint32_t sub, uint32_t lim_lo,
-                                          uint32_t lim_hi, uint32_t word[8]) {
-  const __half *prow = row0;  // advanced by W per row: no per-row multiply
+// Same rows through one packed fp16 compare per pixel pair (HSET2.GE against
+// the threshold VALUE x'_c, the code of key_c): act(x) >= thr  <=>  x >= x'_c
+// for the non-decreasing activation, NaN compares false, -0 and +0 share
+// their activation so no bisection ever separates them.  5 instructions per
+// pair (an integer range test on order-preserving keys needed 9: 0.535 ->
+// 0.487 ms on 512 Severstal images, C4 0.99 -> 0.95 ms).
+__device__ __forceinline__ void code_rows_hset(const __half *row0, int W,
+                                               int rows, uint32_t t2bits,
+                                               uint32_t word[8]) {
+  const __half2 t2 = *reinterpret_cast<const __half2 *>(&t2bits);
+  const __half *prow = row0;
   for (int r0 = 0; r0 < rows; r0 += 4) {
-    uint4 v[4];  // four rows in flight before any compare
+    uint4 v[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       v[q] = r0 + q < rows ? ldg_stream16(prow) : make_uint4(0, 0, 0, 0);
@@ -82,18 +88,15 @@ __device__ __forceinline__ void code_rows(const __half *row0, int W, int rows,
       const uint32_t bit = r0 + q < rows ? 1u << (r0 + q) : 0u;
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
-        uint32_t k2 = w4[h];
-        if (!RAW) {
-          // per half: negative -> flip all bits, else flip the sign bit
-          const uint32_t m = prmt32(k2, 0u, 0xBB99u);
-          k2 ^= m | 0x80008000u;
-        }
-        if ((k2 << 16) - sub <= lim_lo) word[2 * h] |= bit;
-        if (k2 - sub <= lim_hi) word[2 * h + 1] |= bit;
+        const uint32_t m =
+            __hge2_mask(*reinterpret_cast<const __half2 *>(&w4[h]), t2);
+        word[2 * h] |= prmt32(m, 0u, 0x0000u) & bit;
+        word[2 * h + 1] |= prmt32(m, 0u, 0x2222u) & bit;
       }
     }
   }
 }
+
 
 // Conflict-free store of a lane's 8 column words: with an odd column pitch
 // the bank of (x, yb) is (x * Hp + yb) % 32, and lane l writing column
@@ -456,27 +459,14 @@ rle_kernel(const __grid_constant__ RleArgs a) {
       if (nv > 0) {
         const int rows = min(32, H - yb * 32);
         if (CODE && nv == 8 && (W & 7) == 0 && a.vec_ok) {
-          // rows are 16-byte aligned: one 128-bit load per row.  A pixel
-          // passes iff key(code) lies in [key_c, key(+inf)] (NaN keys fall
-          // outside); both halves of a packed pair are tested in place:
-          //   high half: (k2 - (kc << 16))       <= (span << 16 | 0xFFFF)
-          //   low half : ((k2 << 16) - (kc << 16)) <= (span << 16)
-          // When the class threshold is a non-negative logit the passing
-          // codes [code_c, 0x7C00] are already one unsigned range of the RAW
-          // code and the key transform is skipped (flip == 0).
+          // rows are 16-byte aligned: one 128-bit load per row, one packed
+          // compare per pixel pair against x'_c (the value of key_c)
           const uint32_t kc = key_thr[c];
-          const bool any = kc <= kKeyPosInf;
-          const bool raw = kc >= 0x8000u;           // x_c >= +0
-          const uint32_t lo_c = raw ? kc ^ 0x8000u : kc;
-          const uint32_t hi_c = raw ? 0x7C00u : kKeyPosInf;
-          const uint32_t sub = lo_c << 16;
-          const uint32_t lim_lo = (hi_c - lo_c) << 16;
-          const uint32_t lim_hi = lim_lo | 0xFFFFu;
-          const __half *row0 = static_cast<const __half *>(a.src.ptr[0]) +
-                               plane_off + (size_t)(yb * 32) * W + x0;
-          if (any) {
-            if (raw) code_rows<true>(row0, W, rows, sub, lim_lo, lim_hi, word);
-            else code_rows<false>(row0, W, rows, sub, lim_lo, lim_hi, word);
+          if (kc <= kKeyPosInf) {
+            const uint32_t xc = kc ^ ((kc & 0x8000u) ? 0x8000u : 0xFFFFu);
+            const __half *row0 = static_cast<const __half *>(a.src.ptr[0]) +
+                                 plane_off + (size_t)(yb * 32) * W + x0;
+            code_rows_hset(row0, W, rows, xc | (xc << 16), word);
           }
         } else if (BYTES) {
           const uint32_t k = key_thr[c];
