@@ -28,9 +28,11 @@ def main():
     bad = 0
     for case in range(n_cases):
         n, c = int(rng.integers(1, 4)), int(rng.integers(1, 5))
-        h, w = int(rng.integers(1, 70)), int(rng.integers(1, 130))
+        big = os.environ.get('FUZZ_BIG') == '1'   # several bands / x-chunks
+        h = int(rng.integers(1, 300 if big else 70))
+        w = int(rng.integers(1, 700 if big else 130))
         if rng.random() < 0.3:
-            w = int(rng.integers(1, 9)) * 8
+            w = int(rng.integers(1, 80 if big else 9)) * 8
         n_src = int(rng.integers(1, 6))
         dtype = torch.float16 if rng.random() < 0.7 else torch.float32
         act = ['sigmoid', None, 'softmax'][int(rng.integers(0, 3))]
