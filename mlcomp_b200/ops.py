@@ -327,7 +327,7 @@ def rle_encode(sources, thr_per_class, min_area_per_class=0, xforms=None,
     off = torch.empty((n, c), dtype=torch.int64, device=dev)
     cnt = torch.empty((n, c), dtype=torch.int32, device=dev)
     area = torch.empty((n, c), dtype=torch.int32, device=dev)
-    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    total = torch.empty(1, dtype=torch.int64, device=dev)  # cleared by the call
     if capacity is None:
         # 1 run pair per 64 px is generous for real masks; retried if not
         capacity = max(1024, n * c * h * w // 32)
@@ -356,7 +356,7 @@ def rle_strings(runs, off, cnt):
     planes = off.numel()
     str_off = torch.empty(planes, dtype=torch.int64, device=dev)
     str_len = torch.empty(planes, dtype=torch.int32, device=dev)
-    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    total = torch.empty(1, dtype=torch.int64, device=dev)  # cleared by the call
     capacity = max(64, 8 * int(runs.numel()))
     while True:
         chars = torch.empty(capacity, dtype=torch.uint8, device=dev)
