@@ -885,12 +885,16 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   MLC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt,
                                                          smem));
   per_sm = max(1, per_sm);
-  // The light 512-thread kernels run one CTA per plane and leave the
-  // balancing to the hardware scheduler (measured: Severstal single source
-  // 0.474 -> 0.463 ms, bin planes 0.487 -> 0.451 ms); the 1024-thread ones
-  // (BOUND with its per-class bisection over S sources, 135 KB bit planes)
-  // do better as a persistent grid (C4 0.955 vs 0.98 ms).
-  const bool per_plane = !wide && (code || bytes);
+  // One CTA per plane, balanced by the hardware scheduler, for the light
+  // 512-thread kernels (Severstal single source 0.474 -> 0.463 ms, bin planes
+  // 0.487 -> 0.451 ms) and for BOUND, whose planes differ in cost with their
+  // rims (60 % empty planes, disagreement along the rims: 1.69 -> 1.61 ms;
+  // heavy disagreement 4.75 -> 3.28 ms; uniform synthetic planes pay 2 % for
+  // the per-CTA bisection).  The single-source kernel on 135 KB bit planes
+  // stays a persistent grid (C4 0.955 vs 0.98 ms).
+  const char *e_grid = getenv("MLC_RLE_GRID");  // A/B: 1 / 0 force either
+  const bool per_plane =
+      e_grid ? e_grid[0] == '1' : (bound || (!wide && (code || bytes)));
   const int grid = per_plane
                        ? (int)min(a.n_planes, (long long)1 << 22)
                        : (int)min(a.n_planes, (long long)per_sm * sm_count());
