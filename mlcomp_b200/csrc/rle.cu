@@ -217,25 +217,21 @@ enum { kRleArith = 0, kRleCode = 1, kRleBound = 2, kRleBoundVec = 3,
 // 2-byte alignment.  The 8-element window of an hflipped or partial item may
 // reach up to 8 elements into the neighbouring row: the caller keeps the
 // outermost rows of the tensor out of `fastmask`.
-template <bool VEC>
-__device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
-                                           int W, int y0, int x0,
-                                           uint32_t fastmask, uint32_t t2bits,
-                                           uint32_t wk[8]) {
-  const __half2 t2 = *reinterpret_cast<const __half2 *>(&t2bits);
-  const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
-  const int xs = rev ? W - 8 - x0 : x0;
-  const int top = 32 - __clz(fastmask);  // rows beyond the last fast one
-  // the row pointer advances by +-W elements: all address arithmetic that
-  // does not depend on the row stays out of the loop
-  const long long step = vf ? -(long long)W : (long long)W;
-  const __half *prow = plane + ((long long)(vf ? H - 1 - y0 : y0) * W + xs);
+// FULL: every row of the tile is compared (fastmask all ones): no per-row
+// tests.  REV: the source is h-flipped - the pairs are compared in source
+// order and the results land in the mirrored columns (pair j holds pixels
+// 7-2j and 6-2j), so the data is never permuted.
+template <bool VEC, bool FULL, bool REV>
+__device__ __forceinline__ void bound_rows_t(const __half *prow, long long step,
+                                             uint32_t fastmask, __half2 t2,
+                                             uint32_t wk[8]) {
+  const int top = FULL ? 32 : 32 - __clz(fastmask);
   for (int r0 = 0; r0 < top; r0 += 4) {
     uint32_t w[4][4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int r = r0 + q;
-      const bool on = (fastmask >> r) & 1u;
+      const bool on = FULL || ((fastmask >> r) & 1u);
       const __half *p = prow;
       prow += step;
       if (VEC) {
@@ -256,30 +252,37 @@ __device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int r = r0 + q;
-      const uint32_t bit = ((fastmask >> r) & 1u) << r;
-      uint32_t u[4] = {w[q][0], w[q][1], w[q][2], w[q][3]};
-      if (rev) {
-        const uint32_t r0_ = prmt32(u[3], 0u, 0x1032u),
-                       r1_ = prmt32(u[2], 0u, 0x1032u),
-                       r2_ = prmt32(u[1], 0u, 0x1032u),
-                       r3_ = prmt32(u[0], 0u, 0x1032u);
-        u[0] = r0_; u[1] = r1_; u[2] = r2_; u[3] = r3_;
-      }
+      const uint32_t bit = FULL ? 1u << r : ((fastmask >> r) & 1u) << r;
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
         const uint32_t m =
-            __hge2_mask(*reinterpret_cast<const __half2 *>(&u[h]), t2);
-        wk[2 * h] |= prmt32(m, 0u, 0x0000u) & bit;
-        wk[2 * h + 1] |= prmt32(m, 0u, 0x2222u) & bit;
+            __hge2_mask(*reinterpret_cast<const __half2 *>(&w[q][h]), t2);
+        wk[REV ? 7 - 2 * h : 2 * h] |= prmt32(m, 0u, 0x0000u) & bit;
+        wk[REV ? 6 - 2 * h : 2 * h + 1] |= prmt32(m, 0u, 0x2222u) & bit;
       }
     }
   }
 }
-
-// fp32 sources: 8 pixels are 32 bytes (two 128-bit loads when rows are
-// 16-byte multiples, else eight word loads - fp32 elements are always word
-// aligned), two rows in flight, one FSETP per pixel against the threshold
-// value x'_c.  No load reaches outside the 8-element window.
+template <bool VEC>
+__device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
+                                           int W, int y0, int x0,
+                                           uint32_t fastmask, uint32_t t2bits,
+                                           uint32_t wk[8]) {
+  const __half2 t2 = *reinterpret_cast<const __half2 *>(&t2bits);
+  const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
+  const int xs = rev ? W - 8 - x0 : x0;
+  // the row pointer advances by +-W elements: all address arithmetic that
+  // does not depend on the row stays out of the loop
+  const long long step = vf ? -(long long)W : (long long)W;
+  const __half *prow = plane + ((long long)(vf ? H - 1 - y0 : y0) * W + xs);
+  if (fastmask == 0xFFFFFFFFu) {
+    if (rev) bound_rows_t<VEC, true, true>(prow, step, fastmask, t2, wk);
+    else bound_rows_t<VEC, true, false>(prow, step, fastmask, t2, wk);
+  } else {
+    if (rev) bound_rows_t<VEC, false, true>(prow, step, fastmask, t2, wk);
+    else bound_rows_t<VEC, false, false>(prow, step, fastmask, t2, wk);
+  }
+}
 template <bool VEC>
 __device__ __forceinline__ void bound_rows(const float *plane, int xf, int H,
                                            int W, int y0, int x0,
