@@ -283,23 +283,17 @@ __device__ __forceinline__ void bound_rows(const __half *plane, int xf, int H,
     else bound_rows_t<VEC, false, false>(prow, step, fastmask, t2, wk);
   }
 }
-template <bool VEC>
-__device__ __forceinline__ void bound_rows(const float *plane, int xf, int H,
-                                           int W, int y0, int x0,
-                                           uint32_t fastmask, uint32_t t_bits,
-                                           uint32_t wk[8]) {
-  const float t = __uint_as_float(t_bits);
-  const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
-  const int xs = rev ? W - 8 - x0 : x0;
-  const int top = 32 - __clz(fastmask);
-  const long long step = vf ? -(long long)W : (long long)W;
-  const float *prow = plane + ((long long)(vf ? H - 1 - y0 : y0) * W + xs);
+template <bool VEC, bool FULL, bool REV>
+__device__ __forceinline__ void bound_rows_t(const float *prow, long long step,
+                                             uint32_t fastmask, float t,
+                                             uint32_t wk[8]) {
+  const int top = FULL ? 32 : 32 - __clz(fastmask);
   for (int r0 = 0; r0 < top; r0 += 2) {
     float u[2][8];
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
       const int r = r0 + q;
-      const bool on = (fastmask >> r) & 1u;
+      const bool on = FULL || ((fastmask >> r) & 1u);
       const float *p = prow;
       prow += step;
       if (VEC) {
@@ -318,13 +312,29 @@ __device__ __forceinline__ void bound_rows(const float *plane, int xf, int H,
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
       const int r = r0 + q;
-      const uint32_t bit = ((fastmask >> r) & 1u) << r;
+      const uint32_t bit = FULL ? 1u << r : ((fastmask >> r) & 1u) << r;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float v = rev ? u[q][7 - i] : u[q][i];
-        if (v >= t) wk[i] |= bit;
-      }
+      for (int i = 0; i < 8; ++i)
+        if (u[q][REV ? 7 - i : i] >= t) wk[i] |= bit;
     }
+  }
+}
+template <bool VEC>
+__device__ __forceinline__ void bound_rows(const float *plane, int xf, int H,
+                                           int W, int y0, int x0,
+                                           uint32_t fastmask, uint32_t t_bits,
+                                           uint32_t wk[8]) {
+  const float t = __uint_as_float(t_bits);
+  const bool rev = (xf & MLC_XF_HFLIP) != 0, vf = (xf & MLC_XF_VFLIP) != 0;
+  const int xs = rev ? W - 8 - x0 : x0;
+  const long long step = vf ? -(long long)W : (long long)W;
+  const float *prow = plane + ((long long)(vf ? H - 1 - y0 : y0) * W + xs);
+  if (fastmask == 0xFFFFFFFFu) {
+    if (rev) bound_rows_t<VEC, true, true>(prow, step, fastmask, t, wk);
+    else bound_rows_t<VEC, true, false>(prow, step, fastmask, t, wk);
+  } else {
+    if (rev) bound_rows_t<VEC, false, true>(prow, step, fastmask, t, wk);
+    else bound_rows_t<VEC, false, false>(prow, step, fastmask, t, wk);
   }
 }
 template <bool VEC>
