@@ -70,22 +70,21 @@ constexpr uint32_t kKeyNegInf = 0x03FFu, kKeyPosInf = 0xFC00u;
 // their activation so no bisection ever separates them.  5 instructions per
 // pair (an integer range test on order-preserving keys needed 9: 0.535 ->
 // 0.487 ms on 512 Severstal images, C4 0.99 -> 0.95 ms).
-__device__ __forceinline__ void code_rows_hset(const __half *row0, int W,
-                                               int rows, uint32_t t2bits,
-                                               uint32_t word[8]) {
-  const __half2 t2 = *reinterpret_cast<const __half2 *>(&t2bits);
-  const __half *prow = row0;
-  for (int r0 = 0; r0 < rows; r0 += 4) {
+template <bool FULL>  // FULL: all 32 rows of the band exist - no row tests
+__device__ __forceinline__ void code_rows_t(const __half *prow, int W, int rows,
+                                            __half2 t2, uint32_t word[8]) {
+  for (int r0 = 0; r0 < (FULL ? 32 : rows); r0 += 4) {
     uint4 v[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      v[q] = r0 + q < rows ? ldg_stream16(prow) : make_uint4(0, 0, 0, 0);
+      v[q] = (FULL || r0 + q < rows) ? ldg_stream16(prow)
+                                     : make_uint4(0, 0, 0, 0);
       prow += W;
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const uint32_t w4[4] = {v[q].x, v[q].y, v[q].z, v[q].w};
-      const uint32_t bit = r0 + q < rows ? 1u << (r0 + q) : 0u;
+      const uint32_t bit = (FULL || r0 + q < rows) ? 1u << (r0 + q) : 0u;
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
         const uint32_t m =
@@ -95,6 +94,13 @@ __device__ __forceinline__ void code_rows_hset(const __half *row0, int W,
       }
     }
   }
+}
+__device__ __forceinline__ void code_rows_hset(const __half *row0, int W,
+                                               int rows, uint32_t t2bits,
+                                               uint32_t word[8]) {
+  const __half2 t2 = *reinterpret_cast<const __half2 *>(&t2bits);
+  if (rows == 32) code_rows_t<true>(row0, W, rows, t2, word);
+  else code_rows_t<false>(row0, W, rows, t2, word);
 }
 
 
