@@ -150,31 +150,42 @@ __device__ __forceinline__ void store_columns(uint32_t *bits, int Hp, int x0,
 // crosses bytes), and with the top bit of k known per class
 //   k < 128 : b >= k  <=>  top(b) |  low-part test
 //   k >= 128: b >= k  <=>  top(b) &  low-part test.
-__device__ __forceinline__ void byte_rows(const uint8_t *row0, int W, int rows,
-                                          uint32_t k, uint32_t word[8]) {
-  const uint32_t k7 = (k & 0x7Fu) * 0x01010101u;
-  const bool khi = (k & 0x80u) != 0;
-  const uint8_t *prow = row0;
-  for (int r0 = 0; r0 < rows; r0 += 8) {
+template <bool FULL, bool KHI>  // FULL: 32 rows; KHI: the top bit of k
+__device__ __forceinline__ void byte_rows_t(const uint8_t *prow, int W,
+                                            int rows, uint32_t k7,
+                                            uint32_t word[8]) {
+  for (int r0 = 0; r0 < (FULL ? 32 : rows); r0 += 8) {
     uint2 v[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      v[q] = r0 + q < rows ? ldg_stream8(prow) : make_uint2(0u, 0u);
+      v[q] = (FULL || r0 + q < rows) ? ldg_stream8(prow) : make_uint2(0u, 0u);
       prow += W;
     }
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      const uint32_t bit = r0 + q < rows ? 1u << (r0 + q) : 0u;
+      const uint32_t bit = (FULL || r0 + q < rows) ? 1u << (r0 + q) : 0u;
       const uint32_t w2[2] = {v[q].x, v[q].y};
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const uint32_t t = ((w2[h] & 0x7F7F7F7Fu) | 0x80808080u) - k7;
-        const uint32_t ge = khi ? (t & w2[h]) : (t | w2[h]);
+        const uint32_t ge = KHI ? (t & w2[h]) : (t | w2[h]);
 #pragma unroll
         for (int b = 0; b < 4; ++b)
           if (ge & (0x80u << (8 * b))) word[4 * h + b] |= bit;
       }
     }
+  }
+}
+__device__ __forceinline__ void byte_rows(const uint8_t *row0, int W, int rows,
+                                          uint32_t k, uint32_t word[8]) {
+  const uint32_t k7 = (k & 0x7Fu) * 0x01010101u;
+  const bool khi = (k & 0x80u) != 0, full = rows == 32;
+  if (full) {
+    if (khi) byte_rows_t<true, true>(row0, W, rows, k7, word);
+    else byte_rows_t<true, false>(row0, W, rows, k7, word);
+  } else {
+    if (khi) byte_rows_t<false, true>(row0, W, rows, k7, word);
+    else byte_rows_t<false, false>(row0, W, rows, k7, word);
   }
 }
 
