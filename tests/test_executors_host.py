@@ -188,3 +188,28 @@ def test_rle2mask_host_decoder_matches_golden(golden_dir):
         m = z['mask'][off:off + h * w].reshape(h, w)
         off += h * w
         assert np.array_equal(rle2mask(r['rle'], (w, h)), m)
+
+
+def test_palette_wraps_like_numpy_and_saturates_like_opencv():
+    """Host side of mask_composite / mask_outline: encode_pred multiplies in
+    uint8 (modulo 256), cv2 colour scalars saturate; a palette shorter than
+    the class count fails like ``colors[i]`` does in the reference."""
+    from mlcomp_b200.ops import _palette
+    wrap, _ = _palette([(300, -1, 255), (0, 256, 511)], 2, wrap=True)
+    assert wrap.tolist() == [[44, 255, 255], [0, 0, 255]]
+    sat, _ = _palette([(300, -1, 255), (0, 256, 511)], 2, wrap=False)
+    assert sat.tolist() == [[255, 0, 255], [0, 255, 255]]
+    assert _palette(None, 3, wrap=True) == (None, None)
+    with pytest.raises(IndexError):
+        _palette([(1, 2, 3)], 2, wrap=True)
+
+
+def test_shard_ranges_cover_the_set_once():
+    from mlcomp_b200.scoring import shard_range
+    for n in (0, 1, 7, 6666, 30000):
+        for world in (1, 2, 3, 8):
+            spans = [shard_range(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
