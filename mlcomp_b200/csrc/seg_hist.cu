@@ -971,6 +971,210 @@ struct ProbArgs {
 // tensors): one 128-bit load per source and item, two 128-bit stores.
 // ROWS: flipped sources, rows a whole number of items (fused_rows8);
 // otherwise no transforms at all - the tensor is one flat array.
+// ---- logit-domain kernel: ONE untransformed source, any element type -------
+// With one source no mean is taken, and the activation is non-decreasing over
+// its whole input type (identity trivially; the device sigmoid over ALL fp32
+// values: exhaustive sweep in tests/test_gpu_fullsize.py), so
+//   cnt(act(x)) = #{k : act(x) >= thr[k]} = #{k : x >= x'_k},
+// x'_k = the smallest input with act(x'_k) >= thr[k], found per CTA by a
+// 32-step bisection over the order-preserving keys with the kernels' own
+// activate() (NaN if no input passes).  No activation is evaluated per pixel.
+// Binning x against the x'_k: a table of kXCells cells over the span of the
+// finite x'_k (affine map, clamped; cell 0 lies below them all), each cell
+// holding (number of x'_k in lower cells, the one x'_k inside it or NaN); a
+// cell that holds two or more is an escape.  One LDS.64 and one compare per
+// pixel give the exact count; NaN pixels compare false everywhere -> 0.
+constexpr int kXCells = 2048;
+struct XSmem {
+  float2 cell[kXCells];                  // (count below as int bits, x' inside)
+  uint32_t cnt[(MLC_MAX_THR + 1) * 32];  // [bin][lane]
+  float xthr[MLC_MAX_THR + 1];
+  float map[2];                          // scale, bias of the cell index
+};
+constexpr int kXEscape = 0x7FFF;
+
+__device__ __forceinline__ int x_cell(float x, float scale, float bias) {
+  // monotone in x; NaN -> 0, +-inf -> the clamped ends
+  return max(0, min(__float2int_rd(fmaf(x, scale, bias)), kXCells - 1));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256, 3)
+seg_hist_logit(const __grid_constant__ HistArgs a) {
+  extern __shared__ __align__(16) unsigned char xraw[];
+  XSmem &sm = *reinterpret_cast<XSmem *>(xraw);
+  const int B = a.B, nbins = B + 1;
+  // ---- per-CTA set-up ------------------------------------------------------
+  for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) sm.cnt[i] = 0;
+  if ((int)threadIdx.x < B) {
+    const float thr = a.thr.v[threadIdx.x];
+    const uint32_t k_ninf = 0x007FFFFFu, k_pinf = 0xFF800000u;
+    uint32_t lo = k_ninf, hi = k_pinf + 1;  // keys of -inf, one past +inf
+    while (lo < hi) {
+      const uint32_t mid = lo + ((hi - lo) >> 1);
+      const uint32_t b = mid ^ ((mid & 0x80000000u) ? 0x80000000u : 0xFFFFFFFFu);
+      if (activate(__uint_as_float(b), a.act) >= thr) hi = mid;
+      else lo = mid + 1;
+    }
+    sm.xthr[threadIdx.x] =
+        lo > k_pinf ? __uint_as_float(0x7FC00000u)
+                    : __uint_as_float(lo ^ ((lo & 0x80000000u) ? 0x80000000u
+                                                               : 0xFFFFFFFFu));
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float x_lo = 0.f, x_hi = 0.f;
+    bool any = false;
+    for (int k = 0; k < B; ++k) {
+      const float t = sm.xthr[k];
+      if (t == t && fabsf(t) <= 3.0e38f) {  // finite (ascending with k)
+        if (!any) x_lo = t;
+        x_hi = t;
+        any = true;
+      }
+    }
+    // cells 1 .. kXCells-2 span [x_lo, x_hi]; cell 0 is everything below
+    const float span = x_hi - x_lo;
+    // any finite positive scale keeps x -> cell monotone (0 or inf would
+    // turn +-inf / 0 into NaN products); exactness never depends on it
+    const float scale =
+        (any && span > 0.f && span < 3.0e38f)
+            ? fminf(fmaxf((float)(kXCells - 3) / span, 1e-30f), 1e30f)
+            : 1e-30f;
+    sm.map[0] = scale;
+    sm.map[1] = 1.5f - x_lo * scale;  // x_lo lands mid-cell 1, x_hi in the last but one
+  }
+  __syncthreads();
+  const float scale = sm.map[0], bias = sm.map[1];
+  // cell table: every threshold drops itself into its cell, then a block scan
+  // over the cells turns the per-cell counts into "thresholds in lower cells"
+  for (int i = threadIdx.x; i < kXCells; i += blockDim.x)
+    sm.cell[i] = make_float2(__int_as_float(0), __uint_as_float(0x7FC00000u));
+  __syncthreads();
+  if ((int)threadIdx.x < B) {
+    const float t = sm.xthr[threadIdx.x];
+    if (t == t) {
+      const int ck = x_cell(t, scale, bias);
+      atomicAdd(reinterpret_cast<int *>(&sm.cell[ck].x), 1);
+      sm.cell[ck].y = t;  // only read when it is the cell's single threshold
+    }
+  }
+  __syncthreads();
+  {
+    constexpr int PER = kXCells / 256;  // cells per thread, blockDim.x == 256
+    const int c0 = threadIdx.x * PER;
+    int n[PER], sum = 0;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      n[j] = __float_as_int(sm.cell[c0 + j].x);
+      sum += n[j];
+    }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((threadIdx.x & 31) >= o) inc += v;
+    }
+    __shared__ int wtot[8];
+    if ((threadIdx.x & 31) == 31) wtot[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    int before = inc - sum;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) before += wtot[w];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      sm.cell[c0 + j].x = __int_as_float(n[j] > 1 ? kXEscape : before);
+      before += n[j];
+    }
+  }
+  __syncthreads();
+  const uint32_t lane4 = (threadIdx.x & 31) * 4;
+  const uint32_t cnt_sa = (uint32_t)__cvta_generic_to_shared(sm.cnt);
+  const uint32_t cell_sa = (uint32_t)__cvta_generic_to_shared(sm.cell);
+  const long long n_units = a.n_planes * a.units_per_plane;
+  const T *src = static_cast<const T *>(a.src.ptr[0]);
+  auto exact = [&](float x) {  // escape cells, head / tail pixels
+    int c = 0;
+    while (c < B && x >= sm.xthr[c]) ++c;
+    return c;
+  };
+  auto add = [&](int c, uint32_t gb) {
+    red_shared_add(cnt_sa + ((c << 7) | lane4), gb ? 0x10000u : 1u);
+  };
+
+  for (long long unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+    const long long plane = unit / a.units_per_plane;
+    const int sub = (int)(unit - plane * a.units_per_plane);
+    const size_t plane_off = (size_t)plane * a.plane_px;
+    const T *lg = src + plane_off;
+    const uint8_t *gtp = a.gt + plane_off;
+    // 8-pixel items aligned to 8 elements of the TENSOR (16 / 32-byte loads);
+    // up to 7 head and 7 tail pixels of the plane go one by one
+    const int shift = (int)(plane_off & 7);
+    const int head = shift ? 8 - shift : 0;          // pixels before item 0
+    const long long n_it = (a.plane_px - min((long long)head, a.plane_px)) >> 3;
+    const long long per = (n_it + a.units_per_plane - 1) / a.units_per_plane;
+    const long long i0 = sub * per, i1 = min(n_it, i0 + per);
+    constexpr int UN = sizeof(T) == 4 ? 2 : 4;  // items in flight per thread
+    for (long long base = i0; base < i1; base += (long long)UN * blockDim.x) {
+      uint4 q[UN][sizeof(T) == 4 ? 2 : 1];
+      uint2 g[UN];
+#pragma unroll
+      for (int u = 0; u < UN; ++u) {
+        const long long it = base + (long long)u * blockDim.x + threadIdx.x;
+        if (it < i1) {
+          const long long e0 = head + it * 8;
+          q[u][0] = ldg_stream16(lg + e0);
+          if (sizeof(T) == 4) q[u][sizeof(T) == 4 ? 1 : 0] = ldg_stream16(lg + e0 + 4);
+          g[u] = ldg_stream8(gtp + e0);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UN; ++u) {
+        const long long it = base + (long long)u * blockDim.x + threadIdx.x;
+        if (it >= i1) break;
+        float x[8];
+        if (sizeof(T) == 4) {
+          const uint4 q0 = q[u][0], q1 = q[u][sizeof(T) == 4 ? 1 : 0];
+          x[0] = __uint_as_float(q0.x); x[1] = __uint_as_float(q0.y);
+          x[2] = __uint_as_float(q0.z); x[3] = __uint_as_float(q0.w);
+          x[4] = __uint_as_float(q1.x); x[5] = __uint_as_float(q1.y);
+          x[6] = __uint_as_float(q1.z); x[7] = __uint_as_float(q1.w);
+        } else {
+          const uint32_t w[4] = {q[u][0].x, q[u][0].y, q[u][0].z, q[u][0].w};
+          unpack8(w, x);
+        }
+        int c[8];
+        bool esc = false;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float2 e = lds_f2(cell_sa + x_cell(x[i], scale, bias) * 8);
+          const int below = __float_as_int(e.x);
+          esc |= below == kXEscape;
+          c[i] = below + (x[i] >= e.y ? 1 : 0);
+        }
+        if (esc) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) c[i] = exact(x[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          add(c[i], ((i < 4 ? g[u].x : g[u].y) >> (8 * (i & 3))) & 0xFFu);
+      }
+    }
+    if (sub == 0) {  // head and tail pixels of the plane
+      const long long tail0 = head + n_it * 8;
+      if (threadIdx.x < 16) {  // at most 7 + 7 pixels
+        const long long e = (long long)threadIdx.x < head
+                                ? threadIdx.x
+                                : tail0 + (threadIdx.x - head);
+        if (e < a.plane_px) add(exact(to_f32<T>(lg[e])), gtp[e]);
+      }
+    }
+    uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
+    flush_bins(sm.cnt, nbins, out, a.units_per_plane > 1);
+  }
+}
+
 template <typename T, bool ROWS>
 __global__ void __launch_bounds__(256)
 seg_prob_vec_kernel(const __grid_constant__ ProbArgs a) {
@@ -1139,7 +1343,20 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
   if (units > 1) MLC_CUDA(cudaMemsetAsync(hist_dev, 0, hist_bytes, st));
   const long long n_units = a.n_planes * units;
 
-  if (table && hist_variant() == 3 && (a.plane_px % 16) == 0) {
+  // one untransformed source without the per-code table (fp32 logits, fp16
+  // without activation or without a lut): binned in the logit domain
+  const bool logit = !table && !bins_dev && n_src == 1 && a.flat &&
+                     act != MLC_ACT_SOFTMAX && hist_variant() != 5 &&
+                     ((uintptr_t)src_dev_ptrs[0] % 16) == 0 &&
+                     ((uintptr_t)gt_dev % 8) == 0;
+  if (logit) {
+    void (*lk)(HistArgs) = dtype == MLC_F16 ? seg_hist_logit<__half>
+                                            : seg_hist_logit<float>;
+    MLC_CUDA(cudaFuncSetAttribute(
+        lk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(XSmem)));
+    lk<<<(int)min(n_units, (long long)1 << 22), 256, sizeof(XSmem), st>>>(a);
+    MLC_LAUNCH_CHECK("seg_hist_logit");
+  } else if (table && hist_variant() == 3 && (a.plane_px % 16) == 0) {
     // unit boundaries on whole 512-item chunks (already guaranteed: the
     // table path rounds items_per_unit to a multiple of 2048)
     MLC_CUDA(cudaFuncSetAttribute(seg_hist_cell_tma,
