@@ -95,7 +95,7 @@ def c3(n=1024):
     thr = ops.threshold_grid(100)
     out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
     ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, xforms=tags, out=out))
-    report('C3 cloud 4-flip TTA %dx4x350x525 fp16: seg_hist_generic' % n, ms,
+    report('C3 cloud 4-flip TTA %dx4x350x525 fp16: seg_hist_tab<0>' % n, ms,
            n * c * (h * w * (4 * 2 + 1) + 808), n * c)
 
 
@@ -105,7 +105,7 @@ def c5(n=512):
     thr = ops.threshold_grid(100)
     out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
     ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, out=out))
-    report('C5 ensemble 5 models %dx4x256x1600 fp16: seg_hist_generic' % n,
+    report('C5 ensemble 5 models %dx4x256x1600 fp16: seg_hist_tab<1>' % n,
            ms, n * c * (h * w * (5 * 2 + 1) + 808), n * c)
 
 
@@ -115,11 +115,11 @@ def c2g(n=1024):
     thr = ops.threshold_grid(100)
     out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
     ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, out=out))
-    report('C2 without table (seg_hist_generic, 1 source) %d img' % n, ms,
+    report('C2 fp16 without the per-code table (seg_hist_logit) %d img' % n, ms,
            n * c * (h * w * 3 + 808), n * c)
     x32 = [srcs[0].float()]
     ms = timeit(lambda: ops.seg_hist(x32, gt, thr, out=out))
-    report('C2 fp32 logits (seg_hist_generic) %d img' % n, ms,
+    report('C2 fp32 logits (seg_hist_logit) %d img' % n, ms,
            n * c * (h * w * 5 + 808), n * c)
 
 
