@@ -873,3 +873,36 @@ def test_rle_uint8_planes_any_byte_threshold(ops):
                     (i, j, thr[j])
                 assert int(area[i, j]) == int(mask.sum())
                 k += 1
+
+
+@pytest.mark.parametrize('dtype,activation', [(torch.float32, 'sigmoid'),
+                                              (torch.float32, None),
+                                              (torch.float16, None),
+                                              (torch.float16, 'sigmoid')])
+def test_logit_domain_kernel_on_split_planes_and_odd_offsets(ops, dtype,
+                                                             activation):
+    """seg_hist_logit (one source, no per-code table): planes large enough to
+    be split into units, a tensor whose planes start at odd element offsets
+    (head / tail pixels), special values, non-uniform thresholds."""
+    rng = np.random.default_rng(12)
+    n, c, h, w = 2, 3, 251, 333
+    x = rng.normal(0, 4, (n, c, h, w)).astype(np.float32)
+    x.reshape(-1)[::1001] = np.nan
+    x.reshape(-1)[5::1777] = np.inf
+    x.reshape(-1)[7::1999] = -np.inf
+    if activation is None:
+        x = np.clip(x / 8 + 0.5, -0.5, 1.5).astype(np.float32)
+    src = torch.from_numpy(x).to(dtype).to(DEV)
+    gt = torch.from_numpy((rng.random((n, c, h, w)) < 0.3)
+                          .astype(np.uint8)).to(DEV)
+    for thr in (oracle.threshold_grid(100),
+                np.array([0.0, 0.2, 0.2, 0.5, 0.999, 1.0, 1.7], np.float32),
+                np.array([0.5], np.float32)):
+        hist = ops.seg_hist([src], gt, thr, activation=activation)
+        prob = ops.seg_prob([src], activation=activation).cpu().numpy()
+        g = gt.cpu().numpy()
+        for i in range(n):
+            for j in range(c):
+                assert np.array_equal(hist[i, j].cpu().numpy(),
+                                      oracle.bin_counts(g[i, j], prob[i, j],
+                                                        thr)), (i, j, len(thr))
