@@ -182,6 +182,14 @@ int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img, int n_cls,
                    int n_thr, const int32_t *k_host, const int32_t *min_area_host,
                    int empty_one, double eps, double *dice_dev, void *stream);
 
+/* Mask area of every plane at one threshold index per class: area[p] =
+ * P(k_c) = sum_{j > k_c} (hist[p][0][j] + hist[p][1][j]) - `outputs.sum()` of
+ * contrib/metrics/dice.py:11 for thr[k_c], before the min-area rule.
+ *   area_dev [n_img*n_cls] int32 */
+int mlc_plane_area(const uint32_t *hist_dev, int64_t n_img, int n_cls,
+                   int n_thr, const int32_t *k_host, int32_t *area_dev,
+                   void *stream);
+
 /* ---- run-length encoding ------------------------------------------------
  * Replaces (prob >= t) + min-area reject + mask2rle
  * (contrib/transform/rle.py:4-13): column-major, 1-based (start, length).
@@ -205,6 +213,25 @@ int mlc_rle_encode(const void *const *src_dev_ptrs, const int32_t *xform,
                    int32_t *runs_dev, int64_t capacity, int64_t *off_dev,
                    int32_t *cnt_dev, int32_t *area_dev, int64_t *total_dev,
                    void *stream);
+
+/* mlc_rle_encode for masks whose AREA is already known - the usual case after
+ * a threshold search: with thr = thr_grid[k], the area of plane p's mask is
+ * P(k) of its histogram (mlc_plane_area).  Same reference lines as
+ * mlc_rle_encode; the min-area rule (contrib/metrics/dice.py:13-15) and the
+ * empty string of an empty mask (contrib/transform/rle.py:4-13) are decided
+ * from the known area, so planes that end up without runs are not read at
+ * all (most planes of a Severstal-like set).
+ *   known_area_dev [planes] int32: the exact pixel count of (prob >= thr_c)
+ *              for every plane; a wrong value gives a wrong result
+ * Everything else as for mlc_rle_encode (skipped planes get cnt = 0, off = 0,
+ * area = the known area). */
+int mlc_rle_encode_known(const void *const *src_dev_ptrs, const int32_t *xform,
+                         int n_src, int dtype, int64_t n_img, int n_cls, int H,
+                         int W, const float *thr_host,
+                         const int32_t *min_area_host, int act,
+                         const int32_t *known_area_dev, int32_t *runs_dev,
+                         int64_t capacity, int64_t *off_dev, int32_t *cnt_dev,
+                         int32_t *area_dev, int64_t *total_dev, void *stream);
 
 /* Text of the run-length strings, replacing the ' '.join(str(x) for x in
  * runs) of contrib/transform/rle.py:13 (and what

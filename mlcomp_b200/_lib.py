@@ -55,6 +55,13 @@ SIGNATURES = {
                                POINTER(c_float), POINTER(c_int32), c_int,
                                c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p]),
+    'mlc_rle_encode_known': (c_int, [POINTER(c_void_p), POINTER(c_int32), c_int,
+                                     c_int, c_int64, c_int, c_int, c_int,
+                                     POINTER(c_float), POINTER(c_int32), c_int,
+                                     c_void_p, c_void_p, c_int64, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p]),
+    'mlc_plane_area': (c_int, [c_void_p, c_int64, c_int, c_int,
+                               POINTER(c_int32), c_void_p, c_void_p]),
     'mlc_rle_format': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
                                c_int64, c_void_p, c_void_p, c_void_p,
                                c_void_p]),
@@ -76,24 +83,43 @@ class MlcError(RuntimeError):
 
 
 def lib_path():
-    return _build.LIB
+    """The library to load: MLC_LIB (a variant built by
+    ``python -m mlcomp_b200.build --bounds-check`` etc.) or the default."""
+    return os.environ.get('MLC_LIB') or _build.LIB
 
 
 def load():
-    """Load (building first if the sources are newer and nvcc exists)."""
+    """Load the library; the default one is (re)built first when nvcc is
+    available and a source is newer than it.  Without nvcc an existing
+    library is used as it is (with a warning if it is older than the
+    sources); a missing one is an ImportError - there is no CPU fallback."""
     global _lib
     if _lib is not None:
         return _lib
     path = lib_path()
-    if not os.path.exists(path):
+    if path == _build.LIB:
         try:
-            _build.build()
-        except Exception as e:
-            raise ImportError(
-                f'{path} is missing and could not be built ({e}); '
-                'mlcomp_b200 has no CPU fallback - run '
-                '`python -m mlcomp_b200.build` where nvcc is available'
-            ) from e
+            have_nvcc = bool(_build.nvcc_path())
+        except RuntimeError:
+            have_nvcc = False
+        if have_nvcc:
+            try:
+                _build.build()      # returns at once when nothing is stale
+            except Exception as e:
+                if not os.path.exists(path):
+                    raise ImportError(
+                        f'{path} is missing and could not be built ({e}); '
+                        'mlcomp_b200 has no CPU fallback - run '
+                        '`python -m mlcomp_b200.build` where nvcc is available'
+                    ) from e
+                raise
+        elif os.path.exists(path) and _build.needs_build():
+            import warnings
+            warnings.warn(f'{path} is older than its sources and nvcc is not '
+                          'available to rebuild it')
+    if not os.path.exists(path):
+        raise ImportError(f'{path} is missing; mlcomp_b200 has no CPU '
+                          'fallback - run `python -m mlcomp_b200.build`')
     lib = ctypes.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)      # AttributeError if a symbol is missing

@@ -137,15 +137,21 @@ __global__ void dice_reduce_kernel(const double *partial, double *out,
   out[i] = s;
 }
 
+// Image chunks per class.  A function of the SHAPE alone, on purpose: the
+// workspace size (mlc_dice_search_workspace) must not depend on which device
+// is current, and the chunk count fixes the fp64 summation order, so results
+// are bit-identical on any sm_100 part.  4 x 148 CTAs fill a B200; a part
+// with another SM count only runs a slightly different number of waves.
 static int chunks_for(int64_t n_img, int n_cls) {
-  long long per_cls = (4ll * 148 + n_cls - 1) / n_cls;  // shape-only, no device query
+  long long per_cls = (4ll * 148 + n_cls - 1) / n_cls;
   if (per_cls < 1) per_cls = 1;
   return (int)(n_img < per_cls ? (n_img < 1 ? 1 : n_img) : per_cls);
 }
 
 struct PlaneArgs {
   const uint32_t *hist;
-  double *dice;
+  double *dice;        // or null
+  int32_t *area_out;   // or null: P(k), the mask area before the min-area rule
   long long n_planes;
   int C, B;
   int empty_one;
@@ -178,8 +184,11 @@ plane_dice_kernel(const __grid_constant__ PlaneArgs a) {
     p += __shfl_xor_sync(0xffffffffu, p, o);
     i += __shfl_xor_sync(0xffffffffu, i, o);
   }
-  if (lane == 0)
-    a.dice[warp] = dice_point(t, p, i, a.area[c], a.empty_one, a.eps);
+  if (lane == 0) {
+    if (a.dice)
+      a.dice[warp] = dice_point(t, p, i, a.area[c], a.empty_one, a.eps);
+    if (a.area_out) a.area_out[warp] = (int32_t)p;
+  }
 }
 
 }  // namespace mlc
@@ -262,6 +271,7 @@ extern "C" int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img,
   PlaneArgs a;
   a.hist = hist_dev;
   a.dice = dice_dev;
+  a.area_out = nullptr;
   a.n_planes = (long long)n_img * n_cls;
   a.C = n_cls;
   a.B = n_thr;
@@ -274,6 +284,38 @@ extern "C" int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img,
     MLC_REQUIRE(min_area_host[c] >= 0, "min_area of class %d is negative", c);
     a.k[c] = k_host[c];
     a.area[c] = min_area_host[c];
+  }
+  const long long blocks = (a.n_planes + 7) / 8;
+  plane_dice_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  MLC_LAUNCH_CHECK("plane_dice_kernel");
+  return MLC_OK;
+}
+
+extern "C" int mlc_plane_area(const uint32_t *hist_dev, int64_t n_img,
+                              int n_cls, int n_thr, const int32_t *k_host,
+                              int32_t *area_dev, void *stream) {
+  MLC_REQUIRE(hist_dev && area_dev && k_host, "hist/area/k pointer is null");
+  MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && n_cls <= MLC_MAX_CLASSES_SEG,
+              "bad n_img=%lld / n_cls=%d (max %d classes)", (long long)n_img,
+              n_cls, MLC_MAX_CLASSES_SEG);
+  MLC_REQUIRE(n_thr >= 1 && n_thr <= MLC_MAX_THR, "n_thr=%d outside [1, %d]",
+              n_thr, MLC_MAX_THR);
+  if (n_img == 0) return MLC_OK;
+  PlaneArgs a;
+  a.hist = hist_dev;
+  a.dice = nullptr;
+  a.area_out = area_dev;
+  a.n_planes = (long long)n_img * n_cls;
+  a.C = n_cls;
+  a.B = n_thr;
+  a.empty_one = 0;
+  a.eps = 0.0;
+  for (int c = 0; c < n_cls; ++c) {
+    MLC_REQUIRE(k_host[c] >= 0 && k_host[c] < n_thr,
+                "threshold index %d of class %d outside [0, %d)", k_host[c], c,
+                n_thr);
+    a.k[c] = k_host[c];
+    a.area[c] = 0;
   }
   const long long blocks = (a.n_planes + 7) / 8;
   plane_dice_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a);
@@ -306,6 +348,8 @@ static __device__ __align__(256) double g_dice_partials[kStaticPartialDoubles];
 // Device address of g_dice_partials on the CURRENT device, or nullptr with
 // *err set.  First use on a device performs the symbol look-up.
 static double *static_partials(cudaError_t *err) {
+  // written without a lock: two threads racing on a device's first call both
+  // look the symbol up and store the same address (idempotent)
   static double *cache[64] = {nullptr};
   int dev = 0;
   *err = cudaGetDevice(&dev);

@@ -25,6 +25,7 @@ struct RleArgs {
   long long *off;
   int32_t *cnt;
   int32_t *area;
+  const int32_t *known_area;  // or null: the planes' mask areas, known already
   unsigned long long *total;
   long long n_planes;
   int C, H, W, Hw;
@@ -479,6 +480,19 @@ rle_kernel(const __grid_constant__ RleArgs a) {
     const float thr = a.thr[c];
     const size_t plane_off = (size_t)plane * H * W;
     const bool inner = plane > 0 && plane + 1 < a.n_planes;
+    if (a.known_area) {
+      // the caller knows this mask's area (from the histograms): an empty or
+      // rejected mask (dice.py:13-15) has no runs - nothing to read
+      const int ka = a.known_area[plane];
+      if (ka == 0 || (a.min_area[c] > 0 && ka < a.min_area[c])) {
+        if (threadIdx.x == 0) {
+          a.off[plane] = 0;
+          a.cnt[plane] = 0;
+          if (a.area) a.area[plane] = ka;
+        }
+        continue;
+      }
+    }
 
     // ---- phase 1: column-major bit plane ---------------------------------
     for (int tile = warp; tile < n_tiles; tile += n_warps) {
@@ -694,6 +708,17 @@ rle_big_kernel(const __grid_constant__ RleArgs a) {
     const float thr = a.thr[c];
     const size_t plane_off = (size_t)plane * H * W;
     const PlaneCtx cx = {plane, a.n_planes, (long long)H * W, a.C};
+    if (a.known_area) {
+      const int ka = a.known_area[plane];
+      if (ka == 0 || (a.min_area[c] > 0 && ka < a.min_area[c])) {
+        if (threadIdx.x == 0) {
+          a.off[plane] = 0;
+          a.cnt[plane] = 0;
+          if (a.area) a.area[plane] = ka;
+        }
+        continue;
+      }
+    }
     auto bit = [&](int y, int x) -> bool {
       float p[8];
       fused_prob8<T, SM>(a.src, plane_off, cx, H, W, y, x, 1, false, a.act, p);
@@ -778,25 +803,31 @@ rle_big_kernel(const __grid_constant__ RleArgs a) {
 
 using namespace mlc;
 
-// MLC_RLE_ARITH=1 keeps multi-source planes on the all-arithmetic path (A/B
-// measurements; results are identical).
+// Developer builds (-DMLC_DEV_KNOBS) only: MLC_RLE_ARITH=1 keeps multi-source
+// planes on the all-arithmetic path, MLC_RLE_GRID=1/0 forces one CTA per plane
+// / a persistent grid (A/B measurements; results are identical).  The shipped
+// library reads no environment.
 static bool arith_only() {
+#ifdef MLC_DEV_KNOBS
   static const bool v = [] {
     const char *e = getenv("MLC_RLE_ARITH");
     return e && e[0] == '1';
   }();
   return v;
+#else
+  return false;
+#endif
 }
 
-extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
-                              const int32_t *xform, int n_src, int dtype,
-                              int64_t n_img, int n_cls, int H, int W,
-                              const float *thr_host,
-                              const int32_t *min_area_host, int act,
-                              int32_t *runs_dev, int64_t capacity,
-                              int64_t *off_dev, int32_t *cnt_dev,
-                              int32_t *area_dev, int64_t *total_dev,
-                              void *stream) {
+static int rle_encode_impl(const void *const *src_dev_ptrs,
+                           const int32_t *xform, int n_src, int dtype,
+                           int64_t n_img, int n_cls, int H, int W,
+                           const float *thr_host,
+                           const int32_t *min_area_host, int act,
+                           int32_t *runs_dev, int64_t capacity,
+                           int64_t *off_dev, int32_t *cnt_dev,
+                           int32_t *area_dev, int64_t *total_dev,
+                           const int32_t *known_area_dev, void *stream) {
   MLC_REQUIRE(dtype == MLC_F16 || dtype == MLC_F32 || dtype == MLC_U8,
               "dtype %d is not MLC_F16/MLC_F32/MLC_U8", dtype);
   MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID ||
@@ -832,6 +863,7 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   a.off = reinterpret_cast<long long *>(off_dev);
   a.cnt = cnt_dev;
   a.area = area_dev;
+  a.known_area = known_area_dev;
   a.total = reinterpret_cast<unsigned long long *>(total_dev);
   a.n_planes = (long long)n_img * n_cls;
   a.C = n_cls;
@@ -922,13 +954,47 @@ extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
   // heavy disagreement 4.75 -> 3.28 ms; uniform synthetic planes pay 2 % for
   // the per-CTA bisection).  The single-source kernel on 135 KB bit planes
   // stays a persistent grid (C4 0.955 vs 0.98 ms).
-  const char *e_grid = getenv("MLC_RLE_GRID");  // A/B: 1 / 0 force either
-  const bool per_plane =
-      e_grid ? e_grid[0] == '1' : (bound || (!wide && (code || bytes)));
+  // (with known areas most planes end at once: let the scheduler balance)
+  bool per_plane = bound || (!wide && (code || bytes)) || known_area_dev;
+#ifdef MLC_DEV_KNOBS
+  if (const char *e_grid = getenv("MLC_RLE_GRID")) per_plane = e_grid[0] == '1';
+#endif
   const int grid = per_plane
                        ? (int)min(a.n_planes, (long long)1 << 22)
                        : (int)min(a.n_planes, (long long)per_sm * sm_count());
   kern<<<grid, nt, smem, st>>>(a);
   MLC_LAUNCH_CHECK("rle_kernel");
   return MLC_OK;
+}
+
+extern "C" int mlc_rle_encode(const void *const *src_dev_ptrs,
+                              const int32_t *xform, int n_src, int dtype,
+                              int64_t n_img, int n_cls, int H, int W,
+                              const float *thr_host,
+                              const int32_t *min_area_host, int act,
+                              int32_t *runs_dev, int64_t capacity,
+                              int64_t *off_dev, int32_t *cnt_dev,
+                              int32_t *area_dev, int64_t *total_dev,
+                              void *stream) {
+  return rle_encode_impl(src_dev_ptrs, xform, n_src, dtype, n_img, n_cls, H, W,
+                         thr_host, min_area_host, act, runs_dev, capacity,
+                         off_dev, cnt_dev, area_dev, total_dev, nullptr,
+                         stream);
+}
+
+extern "C" int mlc_rle_encode_known(const void *const *src_dev_ptrs,
+                                    const int32_t *xform, int n_src, int dtype,
+                                    int64_t n_img, int n_cls, int H, int W,
+                                    const float *thr_host,
+                                    const int32_t *min_area_host, int act,
+                                    const int32_t *known_area_dev,
+                                    int32_t *runs_dev, int64_t capacity,
+                                    int64_t *off_dev, int32_t *cnt_dev,
+                                    int32_t *area_dev, int64_t *total_dev,
+                                    void *stream) {
+  MLC_REQUIRE(known_area_dev, "known_area_dev is null");
+  return rle_encode_impl(src_dev_ptrs, xform, n_src, dtype, n_img, n_cls, H, W,
+                         thr_host, min_area_host, act, runs_dev, capacity,
+                         off_dev, cnt_dev, area_dev, total_dev, known_area_dev,
+                         stream);
 }

@@ -8,80 +8,11 @@
 // lands in the same few bins).  Each word packs two 16-bit counters, low =
 // pixels with gt 0, high = pixels with gt 1; a CTA flushes to global memory
 // before a lane column can reach 65 535.
-#include "mlc_common.cuh"
+#include "seg_hist.cuh"
 
 #include <cstdlib>
 
 namespace mlc {
-
-constexpr int kHistThreads = 512;
-constexpr int kMaxUnitPx = 1 << 20;  // 32 lanes x 32 768 px < 65 536 per half
-
-struct HistArgs {
-  SrcSet src;
-  ThrTable thr;
-  const uint8_t *gt;
-  uint32_t *hist;
-  const uint8_t *lut;
-  uint8_t *bins;  // optional [plane][H][W] bin index of every pixel (or null)
-  long long n_planes;
-  long long plane_px;  // H*W
-  int n_cls;
-  int H, W;            // geometry used for fetches (flat mode: 1, H*W)
-  int B;
-  int act;
-  int units_per_plane;
-  long long items_per_unit;  // items of 8 px
-  long long items_per_plane;
-  long long full_items;  // row mode: H * (W / 8)
-  int items_per_row;     // row mode: W / 8 full items per row
-  int flat;
-  float scale, bias;
-};
-
-__device__ __forceinline__ void flush_bins(uint32_t *cnt, int nbins,
-                                           uint32_t *out, bool atomic) {
-  __syncthreads();
-  for (int j = threadIdx.x; j < nbins; j += blockDim.x) {
-    uint32_t lo = 0, hi = 0;
-#pragma unroll 8
-    for (int i = 0; i < 32; ++i) {
-      const int col = (j + i) & 31;  // rotate: conflict-free column walk
-      const uint32_t w = cnt[j * 32 + col];
-      cnt[j * 32 + col] = 0;
-      lo += w & 0xffffu;
-      hi += w >> 16;
-    }
-    if (atomic) {
-      if (lo) atomicAdd(out + j, lo);
-      if (hi) atomicAdd(out + nbins + j, hi);
-    } else {
-      out[j] = lo;
-      out[nbins + j] = hi;
-    }
-  }
-  __syncthreads();
-}
-
-// Optional second output of the multi-source kernels: the bin index
-// cnt(p) of every pixel as one byte (B <= 255), so that a later pass - RLE at
-// a threshold the search has yet to choose - reads 1 byte per pixel instead of
-// all the sources again: (p >= thr[k])  <=>  (bin > k).
-__device__ __forceinline__ void store_bins8(uint8_t *dst, const int c[8],
-                                            int nv) {
-  if (nv == 8 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0) {
-    uint2 v;
-    v.x = (uint32_t)c[0] | ((uint32_t)c[1] << 8) | ((uint32_t)c[2] << 16) |
-          ((uint32_t)c[3] << 24);
-    v.y = (uint32_t)c[4] | ((uint32_t)c[5] << 8) | ((uint32_t)c[6] << 16) |
-          ((uint32_t)c[7] << 24);
-    *reinterpret_cast<uint2 *>(dst) = v;
-  } else {
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-      if (i < nv) dst[i] = (uint8_t)c[i];
-  }
-}
 
 // ---- generic kernel: any number of sources, flips, f16/f32 ---------------
 // Binning: cnt(p) = #{k : p >= thr[k]}.  A linear first guess c is checked
@@ -547,6 +478,7 @@ __global__ void lut_build(ThrTable t, int B, int act, uint8_t *lut) {
 
 constexpr int kLutUnroll = 4;
 
+#ifdef MLC_DEV_KNOBS
 __global__ void __launch_bounds__(kHistThreads, 2)
 seg_hist_lut(const __grid_constant__ HistArgs a) {
   extern __shared__ uint32_t smem[];
@@ -607,6 +539,8 @@ seg_hist_lut(const __grid_constant__ HistArgs a) {
     flush_bins(cnt, nbins, out, a.units_per_plane > 1);
   }
 }
+
+#endif  // MLC_DEV_KNOBS
 
 // ---- cell-table kernel: the same job with conflict-free look-ups ----------
 // ncu on seg_hist_lut (profiles/README.md): the LSU data pipe is 95 % busy
@@ -777,6 +711,7 @@ seg_hist_cell(const __grid_constant__ HistArgs a) {
   }
 }
 
+#ifdef MLC_DEV_KNOBS
 // ---- cell-table kernel fed by bulk async copies (TMA, 1-D) ---------------
 // Same arithmetic as seg_hist_cell.  A producer warp streams the plane into a
 // ring of shared-memory stages with cp.async.bulk (UBLKCP) signalled through
@@ -953,6 +888,8 @@ seg_hist_cell_tma(const __grid_constant__ HistArgs a) {
     asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers) : "memory");
   }
 }
+
+#endif  // MLC_DEV_KNOBS
 
 // ---- fused probabilities only --------------------------------------------
 struct ProbArgs {
@@ -1222,17 +1159,20 @@ seg_prob_kernel(const __grid_constant__ ProbArgs a) {
   }
 }
 
-// Developer switch for A/B runs of the single-fp16-source path:
-// MLC_HIST_VARIANT=1 byte-table kernel (seg_hist_lut), =3 cell table fed by
-// bulk async copies (seg_hist_cell_tma; measured 7 % slower on C2 than the
-// default: per-chunk mbarrier traffic outweighs the freed registers),
-// default: cell-table kernel with register-staged 128-bit loads
-// (seg_hist_cell).  =4: multi-source fp16 jobs evaluate the sigmoid instead
-// of reading it from the shared-memory activation table (seg_hist_generic
-// where seg_hist_tab would run).
+// Developer builds (-DMLC_DEV_KNOBS, `python -m mlcomp_b200.build
+// --dev-knobs`) keep the retired schedules of the single-source kernel and an
+// environment switch for A/B runs; the shipped library reads no environment.
+//   MLC_HIST_VARIANT=1 byte-table kernel (seg_hist_lut), =3 cell table fed by
+//   bulk async copies (seg_hist_cell_tma), =4 multi-source fp16 jobs evaluate
+//   the sigmoid (seg_hist_generic), =5 no logit-domain kernel, =6 no guarded
+//   estimate (seg_hist_tab serves the multi-source fp16 jobs)
 static int hist_variant() {
+#ifdef MLC_DEV_KNOBS
   const char *e = getenv("MLC_HIST_VARIANT");
   return e ? atoi(e) : 0;
+#else
+  return 0;
+#endif
 }
 
 static int check_thr(const float *thr, int n_thr) {
@@ -1357,12 +1297,15 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
     // persistent, 6 CTAs per SM (two waves of the 3 resident ones): the
     // per-CTA bisection makes one CTA per unit 4 % slower here
     // (fp32 C2 1.79 vs 1.73 ms); MLC_LOGIT_GRID overrides, 0 = per unit
-    const char *e_lg = getenv("MLC_LOGIT_GRID");
-    const int lgs = e_lg ? atoi(e_lg) : 6;
+    int lgs = 6;
+#ifdef MLC_DEV_KNOBS
+    if (const char *e_lg = getenv("MLC_LOGIT_GRID")) lgs = atoi(e_lg);
+#endif
     const long long lgrid = lgs > 0 ? min(n_units, (long long)lgs * sms)
                                     : min(n_units, (long long)1 << 22);
     lk<<<(int)lgrid, 256, sizeof(XSmem), st>>>(a);
     MLC_LAUNCH_CHECK("seg_hist_logit");
+#ifdef MLC_DEV_KNOBS
   } else if (table && hist_variant() == 3 && (a.plane_px % 16) == 0) {
     // unit boundaries on whole 512-item chunks (already guaranteed: the
     // table path rounds items_per_unit to a multiple of 2048)
@@ -1372,7 +1315,8 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
     const int grid = (int)min(n_units, 2ll * sms);
     seg_hist_cell_tma<<<grid, kTmaThreads, sizeof(TmaStages) + 128, st>>>(a);
     MLC_LAUNCH_CHECK("seg_hist_cell_tma");
-  } else if (table && hist_variant() != 1) {
+#endif
+  } else if (table && hist_variant() != 1) {  // always, unless a dev knob
     // One CTA per unit, not a persistent grid: measured on C2 (26 664
     // planes), 4 resident CTAs per SM looping over a static share of the
     // planes reach 86 % of the measured HBM peak, the same CTAs handed out by
@@ -1382,6 +1326,7 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
     seg_hist_cell<256, 4, 4>
         <<<(int)min(n_units, (long long)1 << 22), 256, 0, st>>>(a);
     MLC_LAUNCH_CHECK("seg_hist_cell");
+#ifdef MLC_DEV_KNOBS
   } else if (table) {
     const size_t smem = 65536 + (size_t)(n_thr + 1) * 32 * 4;
     // per-device attribute, cheap: set on every call rather than cache
@@ -1391,6 +1336,7 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
     const int grid = (int)min(n_units, 2ll * sms);
     seg_hist_lut<<<grid, kHistThreads, smem, st>>>(a);
     MLC_LAUNCH_CHECK("seg_hist_lut");
+#endif
   } else {
     const size_t smem = (size_t)(n_thr + 1) * (32 * 4 + 8) + (size_t)n_thr * 4;
     // one CTA per unit (see seg_hist_cell above)
@@ -1404,6 +1350,17 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
                  a.items_per_plane < (1ll << 31) - kTabThreads;
     for (int i = 0; i < n_src; ++i)
       vrows = vrows && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
+    if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID && (vec || vrows) &&
+        (a.plane_px % 8) == 0 && hist_variant() != 4 && hist_variant() != 6) {
+      // guarded estimate (seg_hist_guarded.cu); declines irregular grids
+      const long long ipp = a.items_per_plane, ipu = a.items_per_unit;
+      a.items_per_plane = a.plane_px / 8;
+      a.items_per_unit = (a.items_per_plane + units - 1) / units;
+      int rc = MLC_OK;
+      if (seg_hist_guarded_launch(a, !vec, st, &rc)) return rc;
+      a.items_per_plane = ipp;
+      a.items_per_unit = ipu;
+    }
     if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID && hist_variant() != 4) {
       // activation table in shared memory: one 1024-thread CTA per SM
       const size_t tab_smem = kActTabBytes;

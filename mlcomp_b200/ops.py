@@ -19,7 +19,7 @@ __all__ = ['activation_code', 'compose_tta', 'confusion', 'seg_lut',
            'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
            'threshold_grid', 'counts_from_hist', 'rle_strings',
            'rle_strings_host', 'rle_decode', 'rle_parse', 'mask_composite',
-           'rle_from_bins',
+           'rle_from_bins', 'plane_area',
            'mask_outline']
 
 
@@ -217,13 +217,16 @@ def seg_hist(sources, gt, thr, xforms=None, activation='sigmoid', lut=None,
     return out
 
 
-def rle_from_bins(bins, k_per_class, min_area_per_class=0, capacity=None):
+def rle_from_bins(bins, k_per_class, min_area_per_class=0, capacity=None,
+                  hist=None):
     """Run-length pairs of the masks (bins > k_c) = (prob >= thr[k_c]) from
     the per-pixel bin indices ``seg_hist(..., bins=True)`` kept (same return
-    values as ``rle_encode``)."""
+    values as ``rle_encode``).  ``hist``: the histograms of the same pass -
+    planes whose mask is empty or below the min-area are then not read."""
     k = np.asarray(k_per_class, dtype=np.float32) + np.float32(0.5)
+    known = plane_area(hist, k_per_class) if hist is not None else None
     return rle_encode([bins], k, min_area_per_class, activation=None,
-                      capacity=capacity)
+                      capacity=capacity, known_area=known)
 
 
 def seg_prob(sources, xforms=None, activation='sigmoid'):
@@ -297,6 +300,21 @@ def plane_dice(hist, k_per_class, min_area_per_class, empty_one=True,
     return out
 
 
+def plane_area(hist, k_per_class):
+    """Mask area of every plane at thr[k_c] (mlc_plane_area): int32 [n, C]."""
+    lib = _lib.load()
+    hist = _need_cuda(hist, 'hist', (torch.int32,))
+    n, c, _, nb = hist.shape
+    k = np.ascontiguousarray(np.broadcast_to(
+        np.asarray(k_per_class, dtype=np.int32), (c,)))
+    out = torch.empty((n, c), dtype=torch.int32, device=hist.device)
+    with torch.cuda.device(hist.device):
+        check(lib.mlc_plane_area(_ptr(hist), n, c, nb - 1,
+                                 k.ctypes.data_as(ctypes.POINTER(c_int32)),
+                                 _ptr(out), _stream()))
+    return out
+
+
 def counts_from_hist(hist):
     """Host-side view helper for tests/reports: (T [n,c], P [n,c,B],
     I [n,c,B]) int64 from a histogram tensor, via torch integer ops on the
@@ -310,13 +328,17 @@ def counts_from_hist(hist):
 
 # -------------------------------------------------------------------- rle
 def rle_encode(sources, thr_per_class, min_area_per_class=0, xforms=None,
-               activation='sigmoid', capacity=None):
+               activation='sigmoid', capacity=None, known_area=None):
     """(prob >= thr_c) + min-area reject + column-major run-length pairs
     (mlc_rle_encode).  Returns device tensors
     (runs int32 [total], off int64 [n,c], cnt int32 [n,c], area int32 [n,c]);
     plane p owns runs[off[p] : off[p] + 2*cnt[p]] as (start, length) pairs.
     Synchronises once to learn the total size (and retries if the first
-    guess of the capacity was too small)."""
+    guess of the capacity was too small).
+
+    ``known_area`` (int32 [n, c] on the device, e.g. ``plane_area(hist, k)``
+    when thr_c = thr_grid[k_c]): the exact mask areas; planes that end up
+    without runs are then not read at all (mlc_rle_encode_known)."""
     lib = _lib.load()
     sources, ptrs, xf, n, c, h, w = _sources(sources, xforms, allow_u8=True)
     dev = sources[0].device
@@ -328,18 +350,31 @@ def rle_encode(sources, thr_per_class, min_area_per_class=0, xforms=None,
     cnt = torch.empty((n, c), dtype=torch.int32, device=dev)
     area = torch.empty((n, c), dtype=torch.int32, device=dev)
     total = torch.empty(1, dtype=torch.int64, device=dev)  # cleared by the call
+    if known_area is not None:
+        known_area = _need_cuda(known_area, 'known_area', (torch.int32,))
+        if known_area.numel() != n * c:
+            raise ValueError('known_area must be [n_img, n_cls]')
     if capacity is None:
         # 1 run pair per 64 px is generous for real masks; retried if not
         capacity = max(1024, n * c * h * w // 32)
     while True:
         runs = torch.empty(capacity, dtype=torch.int32, device=dev)
         with torch.cuda.device(dev):
-            check(lib.mlc_rle_encode(
-                ptrs, xf, len(sources), _dtype_code(sources[0]), n, c, h, w,
-                thr.ctypes.data_as(ctypes.POINTER(c_float)),
-                ar.ctypes.data_as(ctypes.POINTER(c_int32)),
-                activation_code(activation), _ptr(runs), capacity, _ptr(off),
-                _ptr(cnt), _ptr(area), _ptr(total), _stream()))
+            if known_area is None:
+                check(lib.mlc_rle_encode(
+                    ptrs, xf, len(sources), _dtype_code(sources[0]), n, c, h,
+                    w, thr.ctypes.data_as(ctypes.POINTER(c_float)),
+                    ar.ctypes.data_as(ctypes.POINTER(c_int32)),
+                    activation_code(activation), _ptr(runs), capacity,
+                    _ptr(off), _ptr(cnt), _ptr(area), _ptr(total), _stream()))
+            else:
+                check(lib.mlc_rle_encode_known(
+                    ptrs, xf, len(sources), _dtype_code(sources[0]), n, c, h,
+                    w, thr.ctypes.data_as(ctypes.POINTER(c_float)),
+                    ar.ctypes.data_as(ctypes.POINTER(c_int32)),
+                    activation_code(activation), _ptr(known_area),
+                    _ptr(runs), capacity, _ptr(off), _ptr(cnt), _ptr(area),
+                    _ptr(total), _stream()))
         need = int(total.item())
         if need <= capacity:
             return runs[:need], off, cnt, area
