@@ -3,16 +3,28 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-Workload (BASELINE.json configs[1], "C2"): Severstal-shaped validation set,
-6,666 images x 4 classes x 256x1600 fp16 logits + uint8 one-hot ground truth
-PER GPU (weak scaling), 100-threshold x 5-min-area dice search.  One "step" is
-one full pass: fused sigmoid + label-conditioned threshold histogram over all
-planes, histogram scan -> dice for the whole grid, (N>1: NCCL all-reduce of
-the integer counts + all-gather of the fp64 partial sums), D2H of the score
-table and the host-side arg-max.  A "mask" is one (image, class) plane.
+Workload (BASELINE.json `metric` / north_star target, on configs[1]'s shapes):
+Severstal-shaped validation set, 6,666 images x 4 classes x 256x1600, every
+image predicted under 4 flip variants (id, h, v, hv; fp16 logits, stored as the
+model emitted them, i.e. flipped) + uint8 one-hot ground truth, PER GPU (weak
+scaling).  One "step" is the whole pipeline over all planes:
 
-One JSON line on stdout (rank 0).  `--impl reference` times the CPU oracle
-port of the reference's own functions (oracle/) on all host cores instead.
+  1. fused un-flip + sigmoid + mean + label-conditioned threshold histogram
+     of every plane, all 100 thresholds in one read (also keeps every pixel's
+     bin index, 1 B/px)                                    [seg_hist_guarded]
+  2. histogram scan -> dice for the 100 x 5 (threshold x min-area) grid, summed
+     over images; N>1: one all-gather of the packed partials      [dice_search]
+  3. D2H of the score table, arg-max per class on the host
+  4. mask area of every plane at the chosen threshold          [plane_area]
+  5. RLE of every mask at the chosen (threshold, min-area); planes whose mask
+     is empty / rejected are known from 4 and not read            [rle_kernel]
+  6. D2H of the run count
+
+A "mask" is one (image, class) plane.  One JSON line on stdout (rank 0).
+`--impl reference` times the reference's CPU path (oracle/_ref = the
+reference's own dice.py / rle.py / tensors.py when present, else the oracle
+port) on all host cores.  The former headline (C2: one source, no RLE) stays
+as the side key `c2_single_source`.
 """
 import argparse
 import json
@@ -27,20 +39,26 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-C2 = dict(n_img=6666, n_cls=4, H=256, W=1600, bins=100,
-          min_areas=(0, 256, 512, 1024, 2048), empty=0.86)
+CFG = dict(n_img=6666, n_cls=4, H=256, W=1600, bins=100,
+           min_areas=(0, 256, 512, 1024, 2048), empty=0.86)
+TAGS = [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]
+FLIP_DIMS = [(), (3,), (2,), (2, 3)]
 METRIC = 'validated_masks_per_sec'
 UNIT = 'masks/s'
+SIGMOID_NOTE = ('bit-equal to torch CUDA sigmoid (the reference\'s device '
+                'path, utils/torch.py:15,24-25); CPU oracle (torch CPU '
+                'sigmoid) differs by <= 4 ulp per source')
 
 
-def workload_name(cfg):
-    return ('C2 severstal-valid: %d img x %d cls x %dx%d fp16 logits + u8 gt '
-            'per GPU, %d thresholds x %d min-areas' %
-            (cfg['n_img'], cfg['n_cls'], cfg['H'], cfg['W'], cfg['bins'],
-             len(cfg['min_areas'])))
+def workload_name(cfg, n_img=None):
+    return ('north_star pipeline on C2 shapes: 4-flip TTA (id,h,v,hv) + 100 '
+            'thr x %d min-area dice search + RLE of every mask at the chosen '
+            'point; %d img x %d cls x %dx%d fp16 x 4 variants + u8 gt per GPU'
+            % (len(cfg['min_areas']), n_img or cfg['n_img'], cfg['n_cls'],
+               cfg['H'], cfg['W']))
 
 
-def algorithmic_bytes_per_plane(cfg, n_src=1, elem=2):
+def hist_bytes_per_plane(cfg, n_src, elem=2):
     """logits once + 1 B/px ground truth + histogram out."""
     px = cfg['H'] * cfg['W']
     return n_src * px * elem + px + 2 * (cfg['bins'] + 1) * 4
@@ -48,13 +66,15 @@ def algorithmic_bytes_per_plane(cfg, n_src=1, elem=2):
 
 # ---------------------------------------------------------------------------
 # synthetic data: mostly-empty planes, a few ellipses,
-# logits = +-4 around the mask + N(0, 1.5), stored fp16
+# logits = +-4 around the mask + N(0, 1.5); TTA variant = the shared logits +
+# its own N(0, 0.5) per pixel, stored flipped (what the model emitted)
 # ---------------------------------------------------------------------------
-def synth(cfg, n_img, seed, device, chunk=64):
+def synth_tta(cfg, n_img, seed, device, chunk=32, n_var=4):
     import torch
     c, h, w = cfg['n_cls'], cfg['H'], cfg['W']
     g = torch.Generator(device=device).manual_seed(seed)
-    logits = torch.empty((n_img, c, h, w), dtype=torch.float16, device=device)
+    srcs = [torch.empty((n_img, c, h, w), dtype=torch.float16, device=device)
+            for _ in range(n_var)]
     gt = torch.empty((n_img, c, h, w), dtype=torch.uint8, device=device)
     yy = torch.arange(h, device=device, dtype=torch.float32)[None, :, None]
     xx = torch.arange(w, device=device, dtype=torch.float32)[None, None, :]
@@ -73,44 +93,89 @@ def synth(cfg, n_img, seed, device, chunk=64):
             mask |= (((yy - cy[:, None, None]) / ry[:, None, None]) ** 2 +
                      ((xx - cx[:, None, None]) / rx[:, None, None]) ** 2) <= 1
         mask &= ~empty[:, None, None]
-        noise = torch.randn((p, h, w), generator=g, device=device,
-                            dtype=torch.float32) * 1.5
-        lg = (mask.float() * 8 - 4) + noise
-        logits[lo:hi] = lg.to(torch.float16).view(hi - lo, c, h, w)
+        lg = torch.randn((p, h, w), generator=g, device=device,
+                         dtype=torch.float32) * 1.5
+        lg += mask.float() * 8 - 4
+        lg = lg.view(hi - lo, c, h, w)
+        for k in range(n_var):
+            v = lg + 0.5 * torch.randn(lg.shape, generator=g, device=device,
+                                       dtype=torch.float32)
+            dims = FLIP_DIMS[k % 4]
+            srcs[k][lo:hi] = (v.flip(*dims) if dims else v).to(torch.float16)
+            del v
         gt[lo:hi] = mask.to(torch.uint8).view(hi - lo, c, h, w)
-        del mask, noise, lg
-    return logits, gt
+        del mask, lg
+    return srcs, gt
 
 
 # ---------------------------------------------------------------------------
-# CPU leg: the oracle port of the reference's own loop, one plane per task
+# CPU leg: what the reference's Valid + Infer executors did per plane
 # ---------------------------------------------------------------------------
+_REF = None
+
+
 def _cpu_init():
     import torch
     torch.set_num_threads(1)        # worker/tasks.py:122-126 sets OMP/MKL = 1
+    global _REF
+    from oracle import make_ref
+    _REF = make_ref.load()
 
 
 def _cpu_plane(args):
-    """sigmoid (utils/torch.py:15) + dice_numpy at every (t, a) of the grid
-    (contrib/metrics/dice.py:4-23) for one plane - what the reference's
-    Valid executor did per plane."""
+    """One plane: sigmoid per variant (utils/torch.py:15), TtaWrap.inverse
+    (contrib/transform/tta.py:20-31 via flip, contrib/torch/tensors.py:4-8),
+    mean, dice_numpy at every (t, a) of the grid
+    (contrib/metrics/dice.py:4-23), mask2rle at one (t, a)
+    (contrib/transform/rle.py:4-13).  The three leaf functions are the
+    reference's own files when oracle/_ref exists."""
     import torch
     import oracle
-    logit, gt, bins, areas = args
-    prob = oracle.activate(torch.from_numpy(logit), 'sigmoid').numpy()
+    planes, gt, tags, bins, areas, t_rle, a_rle = args
+    ref = _REF
+    acc = None
+    for x, tg in zip(planes, tags):
+        p = torch.sigmoid(torch.from_numpy(x).float()[None, None])
+        if ref is not None:
+            for t in tg:
+                p = ref.flip(p, 3 if t == 'hflip' else 2)
+        else:
+            p = oracle.tta_inverse(p, tg)
+        p = p.numpy()[0, 0]
+        acc = p.copy() if acc is None else acc + p
+    prob = acc / np.float32(len(planes))
     thr = oracle.threshold_grid(bins)
-    table = oracle.dice_grid_slow(gt[None, None].astype(np.float32),
-                                  prob[None, None], thr, areas)
-    return table[0, 0]
+    g = gt.astype(np.float32)
+    table = np.zeros((len(thr), len(areas)))
+    dice = ref.dice_numpy if ref is not None else oracle.plane_dice
+    for k, t in enumerate(thr):
+        for m, a in enumerate(areas):
+            table[k, m] = dice(g, prob, threshold=np.float32(t),
+                               min_area=int(a))
+    mask = (prob >= np.float32(t_rle)).astype(np.uint8)
+    if a_rle and mask.sum() < a_rle:
+        mask[:] = 0
+    rle = ref.mask2rle(mask) if ref is not None else oracle.rle_encode(mask)
+    return table, rle, prob
 
 
-def cpu_rate(pool, cores, planes_logit, planes_gt, cfg):
-    tasks = [(planes_logit[i], planes_gt[i], cfg['bins'],
-              list(cfg['min_areas'])) for i in range(len(planes_logit))]
+def cpu_run(pool, srcs_np, gt_np, tags, cfg, t_c, a_c):
+    """srcs_np: list of [planes, H, W] fp16 (stored flipped), gt_np
+    [planes, H, W]; class of plane i = i % n_cls."""
+    c = cfg['n_cls']
+    tasks = [([s[i] for s in srcs_np], gt_np[i], tags, cfg['bins'],
+              list(cfg['min_areas']), t_c[i % c], a_c[i % c])
+             for i in range(len(gt_np))]
     t0 = time.perf_counter()
     out = pool.map(_cpu_plane, tasks, chunksize=1)
     dt = time.perf_counter() - t0
-    return len(tasks) / dt, dt, np.stack(out)
+    return (len(tasks) / dt, dt, np.stack([o[0] for o in out]),
+            [o[1] for o in out], np.stack([o[2] for o in out]))
+
+
+def cpu_kind():
+    from oracle import make_ref
+    return 'reference' if make_ref.load() is not None else 'port'
 
 
 def cpu_model():
@@ -207,9 +272,9 @@ def measured_peak():
         return 6650.0, 'fallback'
 
 
-def committed_traffic(key):
+def committed(name, key):
     try:
-        d = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))
+        d = json.load(open(os.path.join(ROOT, 'profiles', name)))
         return d.get(key)
     except Exception:
         return None
@@ -217,43 +282,146 @@ def committed_traffic(key):
 
 # ---------------------------------------------------------------------------
 def run_reference(args, cfg):
-    """The reference's CPU implementation of the path (oracle port), all host
-    cores, each step a bounded sample of the workload."""
+    """The reference's CPU implementation of the path, all host cores, each
+    step a bounded sample of the workload."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    import torch
     pool, cores = make_pool()
     n_planes = max(16, cores)
     n_img = (n_planes + cfg['n_cls'] - 1) // cfg['n_cls']
-    logits, gt = synth(cfg, n_img, 2000, 'cpu', chunk=8)
-    lg = logits.numpy().reshape(-1, cfg['H'], cfg['W'])[:n_planes]
-    g = gt.numpy().reshape(-1, cfg['H'], cfg['W'])[:n_planes]
+    srcs, gt = synth_tta(cfg, n_img, 2000, 'cpu', chunk=4)
+    h, w = cfg['H'], cfg['W']
+    s_np = [s.numpy().reshape(-1, h, w)[:n_planes] for s in srcs]
+    g_np = gt.numpy().reshape(-1, h, w)[:n_planes]
+    t_c, a_c = [0.5] * cfg['n_cls'], [1024] * cfg['n_cls']
     for _ in range(args.warmup):
-        cpu_rate(pool, cores, lg, g, cfg)
+        cpu_run(pool, s_np, g_np, TAGS, cfg, t_c, a_c)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        cpu_rate(pool, cores, lg, g, cfg)
+        cpu_run(pool, s_np, g_np, TAGS, cfg, t_c, a_c)
     dt = time.perf_counter() - t0
     pool.close()
     value = n_planes * args.steps / dt
-    sample = ('%d planes per step (%d images) of the C2 workload, one plane '
-              'per task over %d processes' % (n_planes, n_img, cores))
+    kind = cpu_kind()
+    sample = ('%d planes per step (%d images) of the workload, one plane per '
+              'task over %d processes; %s' %
+              (n_planes, n_img, cores,
+               'dice_numpy / mask2rle / flip are the reference\'s own files '
+               '(oracle/_ref), sigmoid + mean restated' if kind == 'reference'
+               else 'oracle port'))
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT,
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True,
-        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16',
         'data': 'synthetic',
         'config': {'workload': workload_name(cfg), 'sample': sample},
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores,
-                         'kind': 'port', 'sample': sample},
+                         'kind': kind, 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0,
                 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }))
 
 
+# ---------------------------------------------------------------------------
+# parity of this very run against the CPU path
+# ---------------------------------------------------------------------------
+def parity_check(ops, cfg, srcs, gt, tags, thr, hist, bins, best, rle_out,
+                 cpu_table, cpu_rle, cpu_prob, n_planes):
+    """Compare the first ``n_planes`` planes of the step's outputs with the
+    CPU path's.  Integer outputs must agree exactly, except where a pixel's
+    CPU and GPU probabilities fall on different sides of a threshold (the two
+    sigmoids differ by <= 4 ulp): those pixels are found and listed, and
+    every disagreeing (plane, threshold, area) dice cell / RLE string must be
+    explained by one of them."""
+    import torch
+    c, h, w = cfg['n_cls'], cfg['H'], cfg['W']
+    n_img = n_planes // c
+    areas = list(cfg['min_areas'])
+    nb = len(thr) + 1
+    sub = [s[:n_img] for s in srcs]
+    # (1) the device's exact probabilities: bins and histograms must be THEIR
+    #     binning, bit for bit
+    p_gpu = ops.seg_prob(sub, xforms=tags).cpu().numpy().reshape(-1, h, w)
+    b_gpu = bins[:n_img].cpu().numpy().reshape(-1, h * w).astype(np.int64)
+    h_gpu = hist[:n_img].cpu().numpy().reshape(-1, 2, nb).astype(np.int64)
+    g_np = gt[:n_img].cpu().numpy().reshape(-1, h * w)
+    exact = True
+    strad = []
+    n_strad = 0
+    plane_strad = {}
+    for i in range(n_planes):
+        cg = np.searchsorted(thr, p_gpu[i].ravel(), side='right')
+        exact &= bool(np.array_equal(cg, b_gpu[i]))
+        want = np.bincount((g_np[i] != 0) * nb + cg,
+                           minlength=2 * nb).reshape(2, nb)
+        exact &= bool(np.array_equal(want, h_gpu[i]))
+        cc = np.searchsorted(thr, cpu_prob[i].ravel(), side='right')
+        bad = np.nonzero(cg != cc)[0]
+        if len(bad):
+            n_strad += len(bad)
+            plane_strad[i] = [(int(min(cg[j], cc[j])), int(max(cg[j], cc[j])))
+                              for j in bad]
+            for j in bad[:4]:
+                if len(strad) < 16:
+                    strad.append({'plane': i, 'y': int(j // w),
+                                  'x': int(j % w),
+                                  'p_gpu': float(p_gpu[i].ravel()[j]),
+                                  'p_cpu': float(cpu_prob[i].ravel()[j])})
+
+    def explained(i, k):
+        # a straddler of plane i moves between bins lo < hi: it changes the
+        # mask at threshold k when lo <= k < hi
+        return any(lo <= k < hi for lo, hi in plane_strad.get(i, ()))
+    # (2) dice at every (threshold, area) cell of those planes
+    t_, p_, i_ = ops.counts_from_hist(hist[:n_img])
+    t_ = t_.cpu().numpy().reshape(-1)
+    p_ = p_.cpu().numpy().reshape(n_planes, -1)
+    i_ = i_.cpu().numpy().reshape(n_planes, -1)
+    import oracle
+    cells = bad_cells = unexplained = 0
+    for i in range(n_planes):
+        for m, a in enumerate(areas):
+            got = oracle.dice_from_counts(t_[i], p_[i], i_[i], int(a))
+            ref = cpu_table[i, :, m]
+            diff = np.abs(got - ref) > 1e-5 * np.maximum(np.abs(ref), 1e-12)
+            cells += len(ref)
+            for k in np.nonzero(diff)[0]:
+                bad_cells += 1
+                unexplained += 0 if explained(i, int(k)) else 1
+    # (3) RLE strings at the chosen point
+    runs, off, cnt = rle_out
+    got = ops.rle_strings_host(runs, off.reshape(-1)[:n_planes],
+                               cnt.reshape(-1)[:n_planes])
+    rle_bad = rle_unexplained = 0
+    for i in range(n_planes):
+        if got[i] != cpu_rle[i]:
+            rle_bad += 1
+            rle_unexplained += 0 if explained(
+                i, best[i % c]['threshold_index']) else 1
+        # against the device's own probabilities: always exact
+        exact &= got[i] == oracle.rle_submission(
+            p_gpu[i], best[i % c]['threshold'], best[i % c]['min_area'])
+    ok = exact and unexplained == 0 and rle_unexplained == 0
+    return ok, {
+        'subset_planes': n_planes,
+        'subset_pixels': n_planes * h * w,
+        'exact_vs_device_probabilities': bool(exact),
+        'straddling_pixels': n_strad,
+        'straddlers_listed': strad,
+        'dice_cells_checked': cells,
+        'dice_cells_differing': bad_cells,
+        'unexplained_cells': unexplained,
+        'rle_strings_checked': n_planes,
+        'rle_strings_differing': rle_bad,
+        'unexplained_rle_strings': rle_unexplained,
+        'sigmoid': SIGMOID_NOTE,
+    }
+
+
+# ---------------------------------------------------------------------------
 def run_ours(args, cfg):
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
@@ -274,43 +442,71 @@ def run_ours(args, cfg):
     from mlcomp_b200 import ops, scoring
 
     n_img, c = args.images or cfg['n_img'], cfg['n_cls']
+    h, w = cfg['H'], cfg['W']
     planes = n_img * c
-    logits, gt = synth(cfg, n_img, 1000 * 2 + rank, dev)
+    px = h * w
+    srcs, gt = synth_tta(cfg, n_img, 1000 * 2 + rank, dev)
     thr = ops.threshold_grid(cfg['bins'])
     search = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev,
                                record_events=True)
+    cap = max(1 << 20, planes * px // 64)
 
     def step():
         search.reset()
-        search.add(logits, gt)
-        return search.result()
+        hist, bins = search.add(srcs, gt, xforms=TAGS, keep_bins=True)
+        res = search.result()
+        k_c = [b['threshold_index'] for b in res['best']]
+        a_c = [b['min_area'] for b in res['best']]
+        rle = ops.rle_from_bins(bins, k_c, a_c, capacity=cap, hist=hist)
+        return res, hist, bins, rle
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- parity of this very run against the oracle, on a subset -----------
-    import oracle
-    sub = min(n_img, 16)    # first 64 planes of the shard
-    res = step()
-    hist = ops.seg_hist([logits[:sub]], gt[:sub], thr, lut=search.lut)
-    h = hist.cpu().numpy().astype(np.int64)
-    lg_h = logits[:sub].cpu()
-    gt_h = gt[:sub].cpu().numpy()
-    prob_cpu = oracle.fuse_probs([lg_h], [[]], 'sigmoid')
-    moved = 0
-    for i in range(sub):
-        for j in range(c):
-            want = oracle.bin_counts(gt_h[i, j], prob_cpu[i, j], thr)
-            moved += int(np.abs(h[i, j] - want).sum()) // 2
-    validated = moved <= 2 + sub * c * cfg['H'] * cfg['W'] // 20000
-    per = ops.plane_dice(hist, [50] * c, [0] * c).cpu().numpy()
-    for i in range(min(sub, 2)):
-        for j in range(c):
-            ref = float(oracle.plane_dice(gt_h[i, j].astype(np.float32),
-                                          prob_cpu[i, j], np.float32(thr[50])))
-            validated &= abs(per[i, j] - ref) <= 1e-5 * max(abs(ref), 1e-12)
+    res, hist, bins, rle = step()
+    best = res['best']
+    n_runs = int(rle[0].numel() // 2)
+    n_nonempty = int((rle[2] > 0).sum().item())
+
+    # ---- CPU path on the first planes of the shard + parity (rank 0) -------
+    validated = True
+    parity = cpu = None
+    if rank == 0 and pool is not None:
+        n_cpu = max(64, 4 * cores) // c * c
+        k_img = min(n_img, n_cpu // c)
+        n_cpu = k_img * c
+        s_np = [s[:k_img].cpu().numpy().reshape(-1, h, w) for s in srcs]
+        g_np = gt[:k_img].cpu().numpy().reshape(-1, h, w)
+        rate, dt, table, cpu_rle, cpu_prob = cpu_run(
+            pool, s_np, g_np, TAGS, cfg,
+            [b['threshold'] for b in best], [b['min_area'] for b in best])
+        pool.close()
+        _cpu_init()
+        t0 = time.perf_counter()
+        _cpu_plane(([s[0] for s in s_np], g_np[0], TAGS, cfg['bins'],
+                    list(cfg['min_areas']), best[0]['threshold'],
+                    best[0]['min_area']))
+        single = 1.0 / (time.perf_counter() - t0)
+        kind = cpu_kind()
+        cpu = {'value': rate, 'unit': UNIT, 'cores': cores, 'kind': kind,
+               'single_core_value': single, 'cpu_model': cpu_model(),
+               'sample': '%d planes (%d images) of this run\'s data: 4 x '
+                         'sigmoid + un-flip + mean, dice_numpy at %d x %d '
+                         'points, mask2rle at the chosen point; one plane per '
+                         'task over %d processes, %.1f s wall; %s' %
+                         (n_cpu, k_img, cfg['bins'], len(cfg['min_areas']),
+                          cores, dt,
+                          'leaf functions = the reference\'s own files '
+                          '(oracle/_ref)' if kind == 'reference'
+                          else 'oracle port')}
+        ok, parity = parity_check(ops, cfg, srcs, gt, TAGS, thr, hist, bins,
+                                  best, rle[:3], table, cpu_rle, cpu_prob,
+                                  n_cpu)
+        validated &= ok
+        del s_np, g_np, table, cpu_prob
+    del hist, bins, rle
 
     # ---- warm-up + timed region ---------------------------------------------
     for _ in range(max(args.warmup, 3)):
@@ -321,12 +517,11 @@ def run_ours(args, cfg):
     if sampler:
         sampler.start()
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-    # no-ops unless run under `ncu --profile-from-start off`: the profiler
-    # then sees exactly the timed region
+    # no-ops unless run under `ncu --profile-from-start off`
     torch.cuda.profiler.start()
     e0.record()
     for _ in range(args.steps):
-        res = step()
+        out = step()
     e1.record()
     barrier()
     torch.cuda.profiler.stop()
@@ -339,292 +534,206 @@ def run_ours(args, cfg):
     value = planes * world * args.steps / (ms * 1e-3)
     kern_ms = [a.elapsed_time(b) for a, b in search.kernel_events]
     kern_avg = float(np.mean(kern_ms))
+    same_best = [b['threshold_index'] for b in out[0]['best']] == \
+        [b['threshold_index'] for b in best]
+    validated &= same_best
+    del out
 
-    # ---- end to end: pinned host buffers in, scores out ---------------------
-    e_img = min(n_img, args.e2e_images)
-    h_logits = torch.empty((e_img,) + tuple(logits.shape[1:]),
-                           dtype=torch.float16, pin_memory=True)
-    h_gt = torch.empty((e_img,) + tuple(gt.shape[1:]), dtype=torch.uint8,
-                       pin_memory=True)
-    h_logits.copy_(logits[:e_img])
-    h_gt.copy_(gt[:e_img])
-    torch.cuda.synchronize()
-    e2e_search = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev)
+    side = {}
+    # ---- side: the pass without bins, RLE re-reading the sources -----------
+    if not args.no_side:
+        def step_reread():
+            search.reset()
+            hist = search.add(srcs, gt, xforms=TAGS)
+            r = search.result()
+            k_c = [b['threshold_index'] for b in r['best']]
+            return ops.rle_encode(
+                srcs, [b['threshold'] for b in r['best']],
+                [b['min_area'] for b in r['best']], xforms=TAGS, capacity=cap,
+                known_area=ops.plane_area(hist, k_c))
+        for _ in range(2):
+            rr = step_reread()
+        barrier()
+        e0.record()
+        for _ in range(max(3, args.steps // 4)):
+            rr = step_reread()
+        e1.record()
+        barrier()
+        ms_rr = e0.elapsed_time(e1) / max(3, args.steps // 4)
+        side['pipeline_rereading_sources'] = {
+            'ms_per_step': ms_rr, 'value': planes / (ms_rr * 1e-3),
+            'same_runs': int(rr[0].numel() // 2) == n_runs}
+        validated &= int(rr[0].numel() // 2) == n_runs
+        del rr
 
-    def e2e_step():
-        e2e_search.reset()
-        e2e_search.add_host([h_logits], h_gt, chunk=args.e2e_chunk)
-        return e2e_search.result()
+    # ---- side: former headline, C2 = one untransformed source, no RLE ------
+    if not args.no_side:
+        c2 = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev,
+                               record_events=True)
 
-    for _ in range(2):
-        r2 = e2e_step()
-    barrier()
-    e0.record()
-    for _ in range(args.e2e_steps):
-        r2 = e2e_step()
-    e1.record()
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = e_img * c * world * args.e2e_steps / (float(t.item()) * 1e-3)
-    h2d = e_img * c * cfg['H'] * cfg['W'] * 3
+        def c2_step():
+            c2.reset()
+            c2.add(srcs[0], gt)
+            return c2.result()
+        for _ in range(3):
+            c2_step()
+        c2.kernel_events.clear()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            c2_step()
+        e1.record()
+        barrier()
+        ms_c2 = e0.elapsed_time(e1) / args.steps
+        k2 = float(np.mean([a.elapsed_time(b) for a, b in c2.kernel_events]))
+        by2 = hist_bytes_per_plane(cfg, 1) * planes
+        side['c2_single_source'] = {
+            'workload': 'C2: %d img x %d cls x %dx%d fp16, one source, '
+                        'histogram + search (no TTA, no RLE)' %
+                        (n_img, c, h, w),
+            'value': planes / (ms_c2 * 1e-3), 'ms_per_step': ms_c2,
+            'kernel': 'seg_hist_cell', 'avg_launch_ms': k2,
+            'achieved_gbs': by2 / (k2 * 1e-3) / 1e9,
+            'frac': by2 / (k2 * 1e-3) / 1e9 / measured_peak()[0]}
+        del c2
 
-    # the same call with the ground truth in its at-rest form (run-length
-    # pairs, as the competition CSVs hold it): decoded on the device
-    g_runs = ops.rle_encode([gt[:e_img]], 0.5, 0, activation=None)[:3]
-    h_runs = tuple(torch.empty(x.shape, dtype=x.dtype, pin_memory=True)
-                   .copy_(x) for x in g_runs)
-    torch.cuda.synchronize()
-
-    def e2e_step_runs():
-        e2e_search.reset()
-        e2e_search.add_host([h_logits], None, chunk=args.e2e_chunk,
-                            gt_runs=h_runs)
-        return e2e_search.result()
-
-    for _ in range(2):
-        r3 = e2e_step_runs()
-    barrier()
-    e0.record()
-    for _ in range(args.e2e_steps):
-        r3 = e2e_step_runs()
-    e1.record()
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_runs_value = e_img * c * world * args.e2e_steps / \
-        (float(t.item()) * 1e-3)
-    e2e_runs_ok = bool(np.array_equal(r3['score'], r2['score']))
-    h2d_runs = e_img * c * cfg['H'] * cfg['W'] * 2 + \
-        sum(x.numel() * x.element_size() for x in h_runs)
-    d2h = int(np.prod(r2['score'].shape)) * 8 + c * (1 + 2 * len(thr)) * 8
-
-    # every rank runs the side measurement on its own shard: its search
-    # combines ranks like the headline one
-    full = None
-    if args.full_images > 0:
-        del h_logits, h_gt
-        full, ok = full_pipeline(args, cfg, logits, gt, thr, dev,
-                                 measured_peak()[0], world, rank)
-        validated &= ok
+    # ---- end to end through the executor plugin -----------------------------
+    e2e = e2e_through_executor(args, cfg, srcs, gt, dev, world, barrier)
+    validated &= e2e.pop('ok')
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- CPU baseline on the same tensors (rank 0, N=1 semantics) -----------
-    cpu = None
-    if pool is not None:
-        n_cpu = max(64, 4 * cores)     # ~20-30 core-seconds of the oracle
-        k_img = min(n_img, (n_cpu + c - 1) // c)
-        lg_np = logits[:k_img].cpu().numpy().reshape(-1, cfg['H'], cfg['W'])
-        gt_np = gt[:k_img].cpu().numpy().reshape(-1, cfg['H'], cfg['W'])
-        n_cpu = min(n_cpu, len(lg_np))
-        rate, dt, table = cpu_rate(pool, cores, lg_np[:n_cpu], gt_np[:n_cpu],
-                                   cfg)
-        pool.close()
-        # the reference's own setting: one process, one thread
-        # (worker/tasks.py:122-126), on the first two planes
-        import torch as _t
-        _t.set_num_threads(1)
-        t0 = time.perf_counter()
-        for i in range(min(2, n_cpu)):
-            _cpu_plane((lg_np[i], gt_np[i], cfg['bins'],
-                        list(cfg['min_areas'])))
-        single = min(2, n_cpu) / (time.perf_counter() - t0)
-        cpu = {'value': rate, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-               'single_core_value': single, 'cpu_model': cpu_model(),
-               'sample': '%d planes of this run\'s C2 data, one plane per '
-                         'task over %d processes, %.1f s wall' %
-                         (n_cpu, cores, dt)}
-        # the CPU loop and the GPU search must agree on those planes
-        hs = ops.seg_hist([logits[:k_img]], gt[:k_img], thr, lut=search.lut)
-        for a_i, area in enumerate(cfg['min_areas']):
-            for k in (10, 50, 90):
-                got = ops.plane_dice(hs, [k] * c, [area] * c).cpu().numpy() \
-                    .reshape(-1)[:n_cpu]
-                ok = np.abs(got - table[:, k, a_i]) <= 1e-5 * np.maximum(
-                    np.abs(table[:, k, a_i]), 1e-12)
-                # straddling pixels (<= 4 ulp sigmoid gap CPU vs GPU) may move
-                validated &= ok.mean() > 0.9
-
     peak, peak_kind = measured_peak()
-    bytes_launch = algorithmic_bytes_per_plane(cfg) * planes
+    bytes_launch = hist_bytes_per_plane(cfg, 4) * planes
     achieved = bytes_launch / (kern_avg * 1e-3) / 1e9
+    step_bytes = bytes_launch + 8 * n_runs
+    step_ms = ms / args.steps
     out = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world,
         'steps': args.steps, 'warmup': max(args.warmup, 3),
-        'ms_per_step': ms / args.steps, 'higher_is_better': True,
-        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'ms_per_step': step_ms, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16',
         'data': 'synthetic',
         'config': {
-            'workload': workload_name(cfg) if not args.images else
-            workload_name(dict(cfg, n_img=n_img)),
+            'workload': workload_name(cfg, n_img),
             'planes_per_gpu': planes,
+            'arithmetic': 'fp16 logits, fp32 sigmoid / mean / compares, '
+                          'integer counts, fp64 dice',
             'cache': 'inputs %.1f GB per GPU per step, far larger than the '
-                     '126 MB L2; no flush needed' %
-                     (planes * cfg['H'] * cfg['W'] * 3 / 1e9),
-            'e2e': '%d images per GPU per step from pinned host memory in '
-                   'chunks of %d, copies overlapped with compute' %
-                   (e_img, args.e2e_chunk),
+                     '126 MB L2; no flush needed' % (planes * px * 9 / 1e9),
+            'e2e': e2e.pop('how'),
         },
-        'validated': bool(validated and e2e_runs_ok),
-        'parity': {'subset_planes': sub * c, 'straddling_pixels': moved,
-                   'best': res['best']},
+        'validated': bool(validated),
+        'parity': dict(parity or {}, best=best,
+                       same_best_every_step=same_best),
         'roofline': {
-            'bound': 'hbm', 'kernel': 'seg_hist_cell',
+            'bound': 'hbm', 'kernel': 'seg_hist_guarded<rows,bins>',
             'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
             'frac': achieved / peak, 'peak_kind': peak_kind,
             'frac_of_8000_nominal': achieved / 8000.0,
             'algorithmic_bytes_per_launch': bytes_launch,
+            'algorithmic_bytes_per_plane': hist_bytes_per_plane(cfg, 4),
             'avg_launch_ms': kern_avg,
-            'traffic': committed_traffic('seg_hist_c2'),
+            'traffic': committed('traffic.json', 'seg_hist_guarded_pipeline'),
+            'whole_step': {
+                'algorithmic_bytes': step_bytes,
+                'achieved': step_bytes / (step_ms * 1e-3) / 1e9,
+                'frac': step_bytes / (step_ms * 1e-3) / 1e9 / peak,
+                'note': '(4x2 + 1) B/px + 808 B per plane + 8 B per run, over '
+                        'the whole step incl. search, D2H and RLE; the bin '
+                        'plane (1 B/px written, read for the %d non-empty '
+                        'masks) is extra traffic, not algorithmic bytes' %
+                        n_nonempty},
         },
+        'pipeline': {'run_pairs': n_runs, 'nonempty_masks': n_nonempty,
+                     'planes': planes},
         'cpu_baseline': cpu,
-        'e2e': {'value': e2e_value, 'unit': UNIT,
-                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
-        'e2e_rle_gt': {'value': e2e_runs_value, 'unit': UNIT,
-                       'h2d_bytes_per_step': h2d_runs,
-                       'd2h_bytes_per_step': d2h,
-                       'same_scores_as_e2e': e2e_runs_ok,
-                       'note': 'ground truth passed as run-length pairs '
-                               '(SegSearch.add_host(gt_runs=...)), decoded '
-                               'on the device'},
-        'gpu_launches': 3 * args.steps,
+        'e2e': e2e,
+        'gpu_launches': 5 * args.steps,
         'clocks': clocks,
     }
-    if full is not None:
-        out['full_pipeline'] = full
+    out.update(side)
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
 
-def full_pipeline(args, cfg, logits, gt, thr, dev, peak, world=1, rank=0):
-    """BASELINE.json's target sentence taken literally, as a second number
-    beside the C2 headline: 4-flip TTA logits -> histogram search -> dice ->
-    RLE of every mask at the thresholds / min-areas the search just chose,
-    on Severstal-shaped planes.  Every rank on its own shard (the search
-    combines ranks); inputs resident in HBM; time = max over ranks."""
+def e2e_through_executor(args, cfg, srcs, gt, dev, world, barrier):
+    """The same pipeline through the plugin API a DAG YAML reaches:
+    Executor.from_config(...) -> ValidSegment -> executor(task=, ...).
+    Inputs start in pinned host memory; every step copies them to the device
+    (double-buffered, overlapped with the kernels) and reads the scores and
+    the RLE strings back."""
     import torch
-    import oracle
-    from mlcomp_b200 import ops, scoring
+    import torch.distributed as dist
+    from mlcomp_b200.worker.executors import Executor
+    from mlcomp_b200.worker import store
     c, h, w = cfg['n_cls'], cfg['H'], cfg['W']
-    n = min(args.full_images, logits.shape[0])
-    tags = [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]
-    xf = [ops.compose_tta(t) for t in tags]
-    base = logits[:n]
-    # variant k holds the logits as a model fed the flipped image emits them:
-    # the shared logits plus the variant's own N(0, 0.5) per pixel (so the
-    # variants disagree on ~2 % of the pixels, far more than real TTA does)
-    gen = torch.Generator(device=dev).manual_seed(77)
-    srcs = []
-    for dims in ((), (3,), (2,), (2, 3)):
-        v = base + 0.5 * torch.randn(base.shape, generator=gen, device=dev,
-                                     dtype=torch.float16)
-        srcs.append(v.flip(*dims).contiguous() if dims else v)
-        del v
-    g = gt[:n]
-    search = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev)
-    cap = n * c * h * w // 32
-
-    def step():
-        # pass 1 keeps every pixel's bin index (1 B/px); the RLE pass reads
-        # that instead of the four sources again
-        search.reset()
-        bins = search.add(srcs, g, xforms=xf, keep_bins=True)[1]
-        res = search.result()
-        t_c = [b['threshold'] for b in res['best']]
-        a_c = [b['min_area'] for b in res['best']]
-        k_c = [b['threshold_index'] for b in res['best']]
-        return res, t_c, a_c, ops.rle_from_bins(bins, k_c, a_c, capacity=cap)
-
-    def step_reread():       # the same without bins: RLE re-reads the sources
-        search.reset()
-        search.add(srcs, g, xforms=xf)
-        res = search.result()
-        return ops.rle_encode(srcs, [b['threshold'] for b in res['best']],
-                              [b['min_area'] for b in res['best']], xforms=xf,
-                              capacity=cap)
-
-    for _ in range(3):
-        res, t_c, a_c, (runs, off, cnt, area) = step()
+    e_img = min(srcs[0].shape[0], args.e2e_images)
+    host = [torch.empty((e_img, c, h, w), dtype=torch.float16,
+                        pin_memory=True).copy_(s[:e_img]) for s in srcs]
+    h_gt = torch.empty((e_img, c, h, w), dtype=torch.uint8,
+                       pin_memory=True).copy_(gt[:e_img])
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-    k = max(3, args.steps // 4)
-    e0.record()
-    for _ in range(k):
-        res, t_c, a_c, (runs, off, cnt, area) = step()
-    e1.record()
-    torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / k], dtype=torch.float64,
-                     device=dev)
-    if world > 1:
-        import torch.distributed as dist
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    config = {'executors': {'valid': {
+        'type': 'valid_segment', 'logits': host, 'tta': TAGS,
+        'targets': h_gt, 'bins': cfg['bins'],
+        'min_areas': list(cfg['min_areas']), 'part_size': args.e2e_chunk,
+        'prepare_submit': True}}}
+
+    def e2e_step():
+        ex = Executor.from_config(executor='valid', config=config,
+                                  additional_info={}, session=None,
+                                  logger=None)
+        out = ex(task=store.Task(name='bench'), task_provider=None,
+                 dag=store.Dag(name='bench'))
+        return ex, out
+
     for _ in range(2):
-        step_reread()
-    torch.cuda.synchronize()
+        ex, r = e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
     e0.record()
-    for _ in range(k):
-        rr = step_reread()
+    for _ in range(args.e2e_steps):
+        ex, r = e2e_step()
     e1.record()
-    torch.cuda.synchronize()
-    t2 = torch.tensor([e0.elapsed_time(e1) / k], dtype=torch.float64,
-                      device=dev)
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-    ms_reread = float(t2.item())
-    if rank != 0:
-        return None, True
-    same = ops.rle_strings(*rr[:3]) == ops.rle_strings(runs, off, cnt) \
-        if n <= 64 else bool(torch.equal(rr[2], cnt) and torch.equal(rr[3], area))
-
-    # parity on the first planes: histograms = the oracle's binning of the
-    # device's own fused probabilities, RLE strings = the oracle's mask2rle
-    # of (those probabilities >= chosen threshold) after the min-area rule
-    m = min(n, 2)
-    prob = ops.seg_prob([s_[:m] for s_ in srcs], xforms=xf).cpu().numpy()
-    hist = ops.seg_hist([s_[:m] for s_ in srcs], g[:m], thr,
-                        xforms=xf).cpu().numpy()
-    g_h = g[:m].cpu().numpy()
-    ok = True
-    for i in range(m):
-        for j in range(c):
-            ok &= bool(np.array_equal(
-                hist[i, j], oracle.bin_counts(g_h[i, j], prob[i, j], thr)))
-    r2 = ops.rle_encode([s_[:m] for s_ in srcs], t_c, a_c, xforms=xf)
-    got = ops.rle_strings(*r2[:3])
-    for i in range(m):
-        for j in range(c):
-            mask = prob[i, j] >= np.float32(t_c[j])
-            if mask.sum() < a_c[j]:
-                mask[:] = False
-            ok &= got[i * c + j] == oracle.rle_encode(mask.astype(np.uint8))
-    ok &= same
-    px = n * c * h * w
-    # pass 1 reads 4 x 2 + 1 and writes 1 byte per pixel, the RLE pass reads 1
-    nbytes = px * (4 * 2 + 1 + 1) + px
-    nbytes_reread = px * (4 * 2 + 1) + px * 4 * 2
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    sec = float(t.item()) * 1e-3
+    value = e_img * c * world * args.e2e_steps / sec
+    h2d = e_img * c * h * w * (4 * 2 + 1)
+    d2h = int(ex.d2h_bytes)
+    # the executor's answer must be the device-resident pipeline's answer on
+    # the same images
+    from mlcomp_b200 import ops, scoring
+    s2 = scoring.SegSearch(c, ops.threshold_grid(cfg['bins']),
+                           cfg['min_areas'], device=dev)
+    s2.reset()
+    s2.add([s[:e_img] for s in srcs], gt[:e_img], xforms=TAGS)
+    want = s2.result()
+    ok = [b['threshold_index'] for b in want['best']] == \
+        [b['threshold_index'] for b in ex.best] and \
+        abs(want['dice'] - r['res']) < 1e-9
+    ceiling = committed('h2d_ceiling.json', str(world))
+    gbs = h2d * world * args.e2e_steps / sec / 1e9
     return {
-        'workload': '4-flip TTA + 100 thr x %d min-area search + dice + RLE '
-                    'of every mask at the chosen point: %d img x %d cls x '
-                    '%dx%d fp16 x 4 variants per GPU' %
-                    (len(cfg['min_areas']), n, c, h, w),
-        'value': n * c * world / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms,
-        'algorithmic_bytes_per_step': nbytes,
-        'hbm_frac': nbytes / (ms * 1e-3) / 1e9 / peak,
-        'launches_per_step': 4, 'run_pairs': int(runs.numel() // 2),
-        'without_bins': {'ms_per_step': ms_reread,
-                         'algorithmic_bytes_per_step': nbytes_reread,
-                         'hbm_frac': nbytes_reread / (ms_reread * 1e-3) / 1e9 /
-                         peak},
-        'validated': ok,
-    }, ok
+        'value': value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
+        'd2h_bytes_per_step': d2h, 'ok': bool(ok),
+        'h2d_gbs_all_gpus': gbs,
+        'h2d_ceiling_gbs_all_gpus': ceiling,
+        'frac_of_h2d_ceiling': (gbs / ceiling) if ceiling else None,
+        'through': 'Executor.from_config -> ValidSegment(prepare_submit) '
+                   '-> executor(task=, task_provider=, dag=)',
+        'how': '%d images x 4 variants per GPU per step from pinned host '
+               'memory in parts of %d images, copies double-buffered against '
+               'the kernels; scores, run pairs and RLE text read back' %
+               (e_img, args.e2e_chunk),
+    }
 
 
 def main():
@@ -634,16 +743,15 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--images', type=int, default=0,
-                    help='images per GPU (default: the full C2 set)')
-    ap.add_argument('--e2e-images', type=int, default=1024)
-    ap.add_argument('--e2e-chunk', type=int, default=64)
+                    help='images per GPU (default: the full set, 6666)')
+    ap.add_argument('--e2e-images', type=int, default=512)
+    ap.add_argument('--e2e-chunk', type=int, default=32)
     ap.add_argument('--e2e-steps', type=int, default=5)
-    ap.add_argument('--full-images', type=int, default=512,
-                    help='images of the TTA+search+RLE side measurement '
-                         '(0 = skip)')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-side', action='store_true',
+                    help='skip the side measurements')
     args = ap.parse_args()
-    cfg = dict(C2)
+    cfg = dict(CFG)
     if args.impl == 'reference':
         run_reference(args, cfg)
     else:

@@ -15,7 +15,8 @@ from . import _lib
 from ._lib import (MLC_ACT_NONE, MLC_ACT_SIGMOID, MLC_F16, MLC_F32, MLC_U8,
                    MLC_XF_HFLIP, MLC_XF_TRANSPOSE, MLC_XF_VFLIP, check)
 
-__all__ = ['activation_code', 'compose_tta', 'confusion', 'seg_lut',
+__all__ = ['MLC_XF_HFLIP', 'MLC_XF_VFLIP', 'MLC_XF_TRANSPOSE',
+           'activation_code', 'compose_tta', 'confusion', 'seg_lut',
            'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
            'threshold_grid', 'counts_from_hist', 'rle_strings',
            'rle_strings_host', 'rle_decode', 'rle_parse', 'mask_composite',

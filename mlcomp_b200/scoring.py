@@ -13,7 +13,8 @@ import torch
 
 from . import ops
 
-__all__ = ['SegSearch', 'ClassifyScore', 'shard_range', 'combine_ranks']
+__all__ = ['SegSearch', 'ClassifyScore', 'HostStager', 'shard_range',
+           'combine_ranks']
 
 
 def _xf_code(x):
@@ -57,6 +58,117 @@ def combine_ranks(dice_sum, micro, n_img, group=None):
             ints[nm])
 
 
+class HostStager:
+    """Host -> device staging of image ranges, copies overlapped with compute.
+
+    ``arrays``: host arrays sharing their first dimension (torch CPU tensors,
+    numpy arrays, ``np.load(mmap_mode='r')`` maps).  ``fetch(lo, hi)`` returns
+    device views of rows [lo, hi) of every array; ``prefetch(lo, hi)`` starts
+    that copy ahead of time on a side stream (``n_buf`` device buffer sets in
+    rotation, so the copy of part i+1 runs while part i is being scored);
+    ``release()`` marks the most recently fetched buffer set as consumed by the
+    work queued so far on the current stream.
+
+    Pinned torch tensors are copied straight from where they lie.  Anything
+    else (pageable memory, memory-mapped .npy files) goes through pinned
+    bounce buffers filled by a few threads (numpy's copy releases the GIL), so
+    the DMA engine is never handed pageable memory.
+
+    Safe across successive passes over the data: a buffer set is only
+    overwritten after the copy stream has waited for the event recorded at its
+    last ``release()``.
+    """
+
+    def __init__(self, arrays, device, part, n_buf=2, threads=8):
+        self.arrays = list(arrays)
+        self.device = torch.device(device)
+        self.part = int(part)
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.pinned = [torch.is_tensor(a) and a.is_pinned()
+                       for a in self.arrays]
+        self.bufs = []
+        for _ in range(n_buf):
+            dev = [torch.empty((self.part,) + tuple(a.shape[1:]),
+                               dtype=self._dtype(a), device=self.device)
+                   for a in self.arrays]
+            host = [None if pin else
+                    torch.empty((self.part,) + tuple(a.shape[1:]),
+                                dtype=self._dtype(a), pin_memory=True)
+                    for a, pin in zip(self.arrays, self.pinned)]
+            self.bufs.append({'dev': dev, 'host': host,
+                              'copied': torch.cuda.Event(),
+                              'consumed': torch.cuda.Event(),
+                              'has_copied': False, 'has_consumed': False,
+                              'range': None})
+        self.next = 0
+        self.last = None
+        self.pool = None
+        if not all(self.pinned):
+            from concurrent.futures import ThreadPoolExecutor
+            self.pool = ThreadPoolExecutor(max_workers=threads)
+            self.threads = threads
+        self.h2d_bytes = 0
+
+    @staticmethod
+    def _dtype(a):
+        if torch.is_tensor(a):
+            return a.dtype
+        return torch.from_numpy(np.empty(0, dtype=a.dtype)).dtype
+
+    def _bounce(self, dst, a, lo, hi):
+        """rows [lo, hi) of a pageable / mapped array -> pinned dst."""
+        n = hi - lo
+        out = dst[:n].numpy()
+        src = a[lo:hi]
+        if torch.is_tensor(src):
+            src = src.numpy()
+        k = max(1, min(self.threads, n))
+        cuts = [(n * i) // k for i in range(k + 1)]
+        list(self.pool.map(
+            lambda i: np.copyto(out[cuts[i]:cuts[i + 1]],
+                                src[cuts[i]:cuts[i + 1]]), range(k)))
+
+    def prefetch(self, lo, hi):
+        for b in self.bufs:
+            if b['range'] == (lo, hi):
+                return b
+        b = self.bufs[self.next]
+        self.next = (self.next + 1) % len(self.bufs)
+        n = hi - lo
+        if n > self.part:
+            raise ValueError('part larger than the staging buffers')
+        if any(not p for p in self.pinned) and b['has_copied']:
+            b['copied'].synchronize()   # its bounce buffers are free again
+        for a, pin, hb in zip(self.arrays, self.pinned, b['host']):
+            if not pin:
+                self._bounce(hb, a, lo, hi)
+        with torch.cuda.stream(self.stream):
+            if b['has_consumed']:
+                self.stream.wait_event(b['consumed'])
+            for a, pin, hb, d in zip(self.arrays, self.pinned, b['host'],
+                                     b['dev']):
+                d[:n].copy_(a[lo:hi] if pin else hb[:n], non_blocking=True)
+                self.h2d_bytes += n * d[0].numel() * d.element_size()
+            b['copied'].record(self.stream)
+            b['has_copied'] = True
+        b['range'] = (lo, hi)
+        return b
+
+    def fetch(self, lo, hi):
+        b = self.prefetch(lo, hi)
+        torch.cuda.current_stream(self.device).wait_event(b['copied'])
+        b['range'] = None            # a later pass must copy again
+        self.last = b
+        return [d[:hi - lo] for d in b['dev']]
+
+    def release(self):
+        if self.last is not None:
+            self.last['consumed'].record(
+                torch.cuda.current_stream(self.device))
+            self.last['has_consumed'] = True
+            self.last = None
+
+
 class SegSearch:
     """Accumulates sum_i dice(i, c, t, a) and the global integer counts.
 
@@ -89,7 +201,6 @@ class SegSearch:
                                  device=self.device)
         self.n_img = 0
         self._fresh = False
-        self._copy_stream = None
         self._stage = None
         # (start, end) CUDA events around every histogram launch, for the
         # per-kernel roofline in bench.py
@@ -134,10 +245,19 @@ class SegSearch:
         return (hist, bins) if keep_bins else hist
 
     # -- host-resident chunks: copies overlapped with compute -----------------
+    def _stager(self, arrays, chunk):
+        key = tuple((id(a), tuple(a.shape), str(a.dtype)) for a in arrays) + \
+            (chunk,)
+        if self._stage is None or self._stage[0] != key:
+            self._stage = (key, HostStager(arrays, self.device, chunk))
+        return self._stage[1]
+
     def add_host(self, sources, gt, xforms=None, chunk=64, gt_runs=None):
         """Score host tensors (pinned for full speed).  The set is cut into
         chunks of ``chunk`` images; chunk i+1 is copied on a side stream
-        while chunk i is scored, through two staging buffers per input.
+        while chunk i is scored, through two staging buffers per input
+        (``HostStager``; successive calls may follow each other without a
+        synchronisation in between).
 
         ``gt_runs=(runs, off, cnt)`` (host tensors, the layout of
         ``ops.rle_parse`` / ``ops.rle_encode``; ``gt`` is then None): the
@@ -146,74 +266,34 @@ class SegSearch:
         (mlc_rle_decode) - 2 instead of 3 bytes per pixel cross PCIe."""
         if isinstance(sources, torch.Tensor):
             sources = [sources]
-        if gt_runs is not None:
-            return self._add_host_runs(sources, gt_runs, xforms, chunk)
-        n = gt.shape[0]
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-        key = (len(sources), tuple(sources[0].shape[1:]), sources[0].dtype,
-               tuple(gt.shape[1:]), chunk)
-        if self._stage is None or self._stage[0] != key:
-            bufs = []
-            for _ in range(2):
-                s = [torch.empty((chunk,) + tuple(x.shape[1:]), dtype=x.dtype,
-                                 device=self.device) for x in sources]
-                g = torch.empty((chunk,) + tuple(gt.shape[1:]),
-                                dtype=torch.uint8, device=self.device)
-                bufs.append((s, g, torch.cuda.Event(), torch.cuda.Event()))
-            self._stage = (key, bufs)
-        bufs = self._stage[1]
-        main = torch.cuda.current_stream(self.device)
-        for idx, lo in enumerate(range(0, n, chunk)):
-            hi = min(n, lo + chunk)
-            s_buf, g_buf, copied, consumed = bufs[idx & 1]
-            with torch.cuda.stream(self._copy_stream):
-                if idx >= 2:
-                    self._copy_stream.wait_event(consumed)
-                for d, x in zip(s_buf, sources):
-                    d[:hi - lo].copy_(x[lo:hi], non_blocking=True)
-                g_buf[:hi - lo].copy_(gt[lo:hi], non_blocking=True)
-                copied.record(self._copy_stream)
-            main.wait_event(copied)
-            self.add([d[:hi - lo] for d in s_buf], g_buf[:hi - lo], xforms)
-            consumed.record(main)
-
-    def _add_host_runs(self, sources, gt_runs, xforms, chunk):
+        sources = list(sources)
         n, c, h, w = sources[0].shape
-        if xforms is not None and any(x & ops.MLC_XF_TRANSPOSE
-                                      for x in map(_xf_code, xforms)):
-            raise ValueError('gt_runs needs the output geometry of the '
-                             'sources: no transposed variants')
-        runs, off, cnt = (t.to(self.device, non_blocking=True)
-                          for t in gt_runs)
-        off, cnt = off.reshape(-1), cnt.reshape(-1)
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-        key = ('runs', len(sources), tuple(sources[0].shape[1:]),
-               sources[0].dtype, chunk)
-        if self._stage is None or self._stage[0] != key:
-            bufs = []
-            for _ in range(2):
-                s = [torch.empty((chunk,) + tuple(x.shape[1:]), dtype=x.dtype,
-                                 device=self.device) for x in sources]
-                bufs.append((s, None, torch.cuda.Event(), torch.cuda.Event()))
-            self._stage = (key, bufs)
-        bufs = self._stage[1]
-        main = torch.cuda.current_stream(self.device)
-        for idx, lo in enumerate(range(0, n, chunk)):
-            hi = min(n, lo + chunk)
-            s_buf, _, copied, consumed = bufs[idx & 1]
-            with torch.cuda.stream(self._copy_stream):
-                if idx >= 2:
-                    self._copy_stream.wait_event(consumed)
-                for d, x in zip(s_buf, sources):
-                    d[:hi - lo].copy_(x[lo:hi], non_blocking=True)
-                copied.record(self._copy_stream)
-            g = ops.rle_decode(runs, off[lo * c:hi * c], cnt[lo * c:hi * c],
-                               h, w).view(hi - lo, c, h, w)
-            main.wait_event(copied)
-            self.add([d[:hi - lo] for d in s_buf], g, xforms)
-            consumed.record(main)
+        runs = off = cnt = None
+        if gt_runs is not None:
+            if xforms is not None and any(x & ops.MLC_XF_TRANSPOSE
+                                          for x in map(_xf_code, xforms)):
+                raise ValueError('gt_runs needs the output geometry of the '
+                                 'sources: no transposed variants')
+            runs, off, cnt = (t.to(self.device, non_blocking=True)
+                              for t in gt_runs)
+            off, cnt = off.reshape(-1), cnt.reshape(-1)
+            arrays = sources
+        else:
+            arrays = sources + [gt]
+        st = self._stager(arrays, chunk)
+        parts = [(lo, min(n, lo + chunk)) for lo in range(0, n, chunk)]
+        for i, (lo, hi) in enumerate(parts):
+            dev = st.fetch(lo, hi)
+            if i + 1 < len(parts):
+                st.prefetch(*parts[i + 1])
+            if gt_runs is not None:
+                g = ops.rle_decode(runs, off[lo * c:hi * c],
+                                   cnt[lo * c:hi * c], h, w) \
+                    .view(hi - lo, c, h, w)
+                self.add(dev, g, xforms)
+            else:
+                self.add(dev[:-1], dev[-1], xforms)
+            st.release()
 
     # -- combine + search -------------------------------------------------------
     def result(self, group=None):

@@ -41,22 +41,67 @@ def _to_device(x, dtype=None):
     return x.cuda(non_blocking=True).contiguous()
 
 
+def _is_host_array(x):
+    return isinstance(x, np.ndarray) or (torch.is_tensor(x) and not x.is_cuda)
+
+
 class _SegInputs:
-    """Shared plumbing: sources, tags, part slicing."""
+    """Shared plumbing: sources, tags, part slicing.
+
+    Host-resident inputs (arrays, pinned tensors, ``.npy`` paths) are staged
+    by a ``scoring.HostStager``: the part after the current one is already on
+    its way to the device while the current one is scored."""
 
     def _init_inputs(self, logits, tta, activation):
         self.sources = [_open(s) for s in (logits or [])]
         self.tta = [list(t) for t in (tta or [[]] * len(self.sources))]
         self.activation = activation
+        self._stager = None
+        self._parts = []
+        self._extra_host = []      # more arrays staged with the sources
 
     def count(self):
         if self.sources:
             return len(self.sources[0])
         return len(self.x)          # dataset attribute used by equations
 
+    def generate_parts(self, count):
+        self._parts = super().generate_parts(count)
+        return self._parts
+
+    def _staged(self):
+        """Device views of the current part of sources + _extra_host, or
+        None when the inputs are not plain host arrays."""
+        arrays = list(self.sources) + list(self._extra_host)
+        if not arrays or not all(_is_host_array(a) for a in arrays) or \
+                not all(a.dtype in (np.float16, np.float32, np.uint8,
+                                    torch.float16, torch.float32, torch.uint8)
+                        for a in arrays):
+            return None
+        if self._stager is None:
+            size = max(hi - lo for lo, hi in self._parts) if self._parts \
+                else self.part[1] - self.part[0]
+            self._stager = scoring.HostStager(arrays, 'cuda', size)
+        dev = self._stager.fetch(*self.part)
+        if self.part in self._parts:
+            i = self._parts.index(self.part)
+            if i + 1 < len(self._parts):
+                self._stager.prefetch(*self._parts[i + 1])
+        return dev
+
+    def _release_part(self):
+        if self._stager is not None:
+            self._stager.release()
+
     def solve(self, name):
         if name == 'y' and 'y' not in self.equations:
             lo, hi = self.part
+            dev = self._staged()
+            self._staged_extra = None
+            if dev is not None:
+                self._staged_extra = dev[len(self.sources):]
+                return [LogitSource(d, t, self.activation)
+                        for d, t in zip(dev, self.tta)]
             return [LogitSource(_to_device(s[lo:hi]), t, self.activation)
                     for s, t in zip(self.sources, self.tta)]
         return super().solve(name)
@@ -98,6 +143,19 @@ class ValidSegment(_SegInputs, Valid):
         self.builder = None
         self.scores = []
         self.best = None
+        # prepare_submit: also write the run-length csv of this very set at
+        # the point the search picks (out-of-fold predictions).  The per-pixel
+        # bin indices of every part stay on the device (1 B/px) until the
+        # thresholds are known; no second pass over the logits.
+        self._kept = []
+        self.rows = []
+        self.names = kwargs.get('names')
+        self.id_column = kwargs.get('id_column', 'ImageId')
+        self.rle_column = kwargs.get('rle_column', 'EncodedPixels')
+        self.d2h_bytes = 0
+        if self.targets is not None and self.targets_rle is None and \
+                _is_host_array(self.targets):
+            self._extra_host = [self.targets]
 
     def create_base(self):
         if self.session is not None and self.task is not None:
@@ -114,10 +172,17 @@ class ValidSegment(_SegInputs, Valid):
             self.search = scoring.SegSearch(n_cls, self.thr, self.min_areas,
                                             activation=act)
         lo, hi = self.part
-        gt = self._targets(lo, hi, tensors[0], tags[0])
-        hist = self.search.add(tensors, gt, tags)
+        extra = getattr(self, '_staged_extra', None)
+        gt = extra[0] if extra else self._targets(lo, hi, tensors[0], tags[0])
+        if self.prepare_submit:
+            hist, bins = self.search.add(tensors, gt, tags, keep_bins=True)
+            self._kept.append((lo, hist, bins))
+        else:
+            hist = self.search.add(tensors, gt, tags)
+        self._release_part()
         per_plane = ops.plane_dice(hist, [self.report_k] * n_cls, [0] * n_cls)
         res = per_plane.mean(dim=1).cpu().numpy()
+        self.d2h_bytes += res.nbytes
         self.scores.extend(res.tolist())
         return res
 
@@ -127,7 +192,7 @@ class ValidSegment(_SegInputs, Valid):
             return _to_device(self.targets[lo:hi], torch.uint8)
         c = like.shape[1]
         h, w = like.shape[2:]
-        if 'transpose' in tags0:
+        if ops.compose_tta(tags0) & ops.MLC_XF_TRANSPOSE:
             h, w = w, h
         if self._gt_runs is None:
             rows = self.targets_rle
@@ -144,7 +209,38 @@ class ValidSegment(_SegInputs, Valid):
     def score_final(self):
         out = self.search.result()
         self.best = out['best']
+        self.d2h_bytes += out['score'].nbytes + 8 * (
+            out['micro_P'].size + out['micro_I'].size + out['micro_T'].size)
+        if self.prepare_submit:
+            self._submit_kept()
         return out['dice']
+
+    def _submit_kept(self):
+        """Run-length strings of every kept part at the chosen point, read
+        from the bin planes (mask = bin > k); planes whose mask is empty or
+        under the min-area are known from the histograms and not read."""
+        k_c = [b['threshold_index'] for b in self.best]
+        a_c = [b['min_area'] for b in self.best]
+        for lo, hist, bins in self._kept:
+            runs, off, cnt, _ = ops.rle_from_bins(bins, k_c, a_c, hist=hist)
+            strings = ops.rle_strings(runs, off, cnt)
+            self.d2h_bytes += sum(len(t) for t in strings) + 12 * len(strings)
+            n, c = hist.shape[:2]
+            for i in range(n):
+                name = self.names[lo + i] if self.names is not None else lo + i
+                for j in range(c):
+                    self.rows.append({self.id_column: f'{name}_{j + 1}',
+                                      self.rle_column: strings[i * c + j]})
+        self._kept = []
+        folder = getattr(self, 'submit_folder', None)
+        if folder:
+            import pandas as pd
+            os.makedirs(folder, exist_ok=True)
+            path = os.path.join(folder,
+                                f'{self.model_name}_{self.suffix}.csv')
+            pd.DataFrame(self.rows, columns=[self.id_column,
+                                             self.rle_column]) \
+                .to_csv(path, index=False)
 
     def plot(self, preds, scores):
         if self.builder is None or self.builder.plot_count <= 0 or \

@@ -158,3 +158,112 @@ def test_guarded_split_planes_small_job(ops):
         .to(torch.uint8)
     check(ops, x, [[]] * 4, gt, oracle.threshold_grid(100))
     check(ops, x, FLIPS, gt, oracle.threshold_grid(100))
+
+
+# ------------------------------------------------- pipeline: known-area RLE
+def test_rle_known_area_skips_only_empty_masks(ops):
+    """mlc_rle_encode_known with areas from the histograms == mlc_rle_encode,
+    for the bin planes and for the sources; strings equal the oracle's."""
+    srcs, gt = synth_seg(6, 3, 64, 96, seed=71, n_src=4, empty=0.6)
+    seen = [forward_tta(s, t).to(DEV) for s, t in zip(srcs, FLIPS)]
+    thr = oracle.threshold_grid(100)
+    hist, bins = ops.seg_hist(seen, gt.to(DEV), thr, xforms=FLIPS, bins=True)
+    p = ops.seg_prob(seen, xforms=FLIPS).cpu().numpy()
+    for k_c, a_c in (([50, 70, 98], [0, 30, 0]), ([10, 99, 0], [5000, 1, 3])):
+        t_c = [float(thr[k]) for k in k_c]
+        area = ops.plane_area(hist, k_c)
+        want_area = torch.from_numpy(
+            np.stack([[(p[i, j] >= thr[k_c[j]]).sum() for j in range(3)]
+                      for i in range(6)])).int()
+        assert torch.equal(area.cpu(), want_area)
+        a = ops.rle_from_bins(bins, k_c, a_c, hist=hist)
+        b = ops.rle_from_bins(bins, k_c, a_c)
+        c = ops.rle_encode(seen, t_c, a_c, xforms=FLIPS, known_area=area)
+        d = ops.rle_encode(seen, t_c, a_c, xforms=FLIPS)
+        sa, sb, sc, sd = (ops.rle_strings(*x[:3]) for x in (a, b, c, d))
+        assert sa == sb == sc == sd
+        assert torch.equal(a[3], d[3]) and torch.equal(c[3], d[3])
+        k = 0
+        for i in range(6):
+            for j in range(3):
+                assert sa[k] == oracle.rle_submission(p[i, j], t_c[j], a_c[j])
+                k += 1
+        assert any(s == '' for s in sa) and any(s != '' for s in sa)
+
+
+def test_add_host_twice_without_sync(ops):
+    """Two add_host calls with different data and no synchronisation in
+    between must not overwrite staging buffers still being read."""
+    from mlcomp_b200 import scoring
+    s1, g1 = synth_seg(9, 2, 64, 96, seed=5, n_src=2)
+    s2, g2 = synth_seg(9, 2, 64, 96, seed=6, n_src=2)
+    tags = [[], ['hflip']]
+    a = scoring.SegSearch(2, min_areas=[0, 50])
+    a.reset()
+    a.add([s.to(DEV) for s in s1], g1.to(DEV), tags)
+    a.add([s.to(DEV) for s in s2], g2.to(DEV), tags)
+    b = scoring.SegSearch(2, min_areas=[0, 50])
+    b.reset()
+    # same host buffers reused for both sets: the second set is written into
+    # them only after the first call's copies were issued
+    hs = [s.clone().pin_memory() for s in s1]
+    hg = g1.clone().pin_memory()
+    b.add_host(hs, hg, tags, chunk=2)
+    torch.cuda.current_stream().synchronize()    # host buffers reusable
+    for d, s in zip(hs, s2):
+        d.copy_(s)
+    hg.copy_(g2)
+    b.add_host(hs, hg, tags, chunk=2)
+    b.add_host(hs, hg, tags, chunk=2)            # and once more, back to back
+    ra, rb = a.result(), b.result()
+    a2 = scoring.SegSearch(2, min_areas=[0, 50])
+    a2.reset()
+    a2.add([s.to(DEV) for s in s1], g1.to(DEV), tags)
+    a2.add([s.to(DEV) for s in s2], g2.to(DEV), tags)
+    a2.add([s.to(DEV) for s in s2], g2.to(DEV), tags)
+    ra = a2.result()
+    assert np.array_equal(ra['micro_P'], rb['micro_P'])
+    assert np.array_equal(ra['micro_I'], rb['micro_I'])
+    np.testing.assert_allclose(ra['score'], rb['score'], rtol=1e-12)
+
+
+def test_valid_segment_prepare_submit_from_host_arrays(ops, tmp_path):
+    """The executor path the bench's e2e takes: host arrays (pinned tensors,
+    and the same data as memory-mapped .npy files) staged part by part,
+    search, then the run-length csv at the chosen point from the kept bin
+    planes - against the device-resident pipeline and the oracle."""
+    from mlcomp_b200 import scoring
+    from mlcomp_b200.worker import store
+    from mlcomp_b200.worker.executors import Executor
+    srcs, gt = synth_seg(10, 2, 64, 96, seed=91, n_src=4, empty=0.4)
+    seen = [forward_tta(s, t).contiguous() for s, t in zip(srcs, FLIPS)]
+    paths = []
+    for k, s in enumerate(seen):
+        paths.append(str(tmp_path / f'v{k}.npy'))
+        np.save(paths[-1], s.numpy())
+    np.save(str(tmp_path / 'gt.npy'), gt.numpy())
+    areas = [0, 40, 400]
+    ref = scoring.SegSearch(2, min_areas=areas)
+    ref.reset()
+    hist, bins = ref.add([s.to(DEV) for s in seen], gt.to(DEV), FLIPS,
+                         keep_bins=True)
+    want = ref.result()
+    k_c = [b['threshold_index'] for b in want['best']]
+    a_c = [b['min_area'] for b in want['best']]
+    want_strings = ops.rle_strings(*ops.rle_from_bins(bins, k_c, a_c)[:3])
+    for logits, targets in (
+            ([s.pin_memory() for s in seen], gt.pin_memory()),
+            (paths, str(tmp_path / 'gt.npy'))):
+        cfg = {'executors': {'valid': {
+            'type': 'valid_segment', 'logits': logits, 'tta': FLIPS,
+            'targets': targets, 'min_areas': areas, 'part_size': 3,
+            'prepare_submit': True}}}
+        ex = Executor.from_config(executor='valid', config=cfg,
+                                  additional_info={})
+        out = ex(task=store.Task(name='t'), task_provider=None,
+                 dag=store.Dag(name='d'))
+        assert abs(out['res'] - want['dice']) < 1e-12
+        assert [b['threshold_index'] for b in ex.best] == k_c
+        assert [r['EncodedPixels'] for r in ex.rows] == want_strings
+        assert ex.rows[3]['ImageId'] == '1_2'
+        assert ex.d2h_bytes > 0
