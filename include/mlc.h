@@ -175,6 +175,18 @@ int mlc_dice_search_static(const uint32_t *hist_dev, int64_t n_img, int n_cls,
                            int empty_one, double eps, double *dice_sum_dev,
                            int64_t *micro_dev, void *stream);
 
+/* Fold the all-gathered partial results of the ranks of a sharded search
+ * (images split over GPUs).  No reference counterpart: the reference scores
+ * in one process (worker/tasks.py:106-131 pins one task to one GPU); this is
+ * the only step in which ranks exchange data, and it moves KBs.
+ *   gathered_dev [world][n_f64 + n_i64] int64: row r = rank r's buffer - the
+ *               first n_f64 entries are fp64 bit patterns (dice_sum), the
+ *               rest plain integers (micro counts, image count)
+ *   out_dev     [n_f64 + n_i64] int64: fp64 entries summed in rank order
+ *               (bit-identical on every rank), integers summed exactly */
+int mlc_combine_ranks(const int64_t *gathered_dev, int world, int64_t n_f64,
+                      int64_t n_i64, int64_t *out_dev, void *stream);
+
 /* Per-plane dice at one chosen (threshold index, min_area) per class:
  * dice_dev [n_img*n_cls] fp64 (the per-image `scores` the report builders
  * take, worker/reports/segmenation.py:148-150). */
@@ -254,7 +266,8 @@ int mlc_rle_format(const int32_t *runs_dev, const int64_t *off_dev,
  * uint8 planes mlc_seg_hist reads.
  *   runs_dev/off_dev/cnt_dev  as produced by mlc_rle_encode (or uploaded by
  *               the caller after parsing the strings); off < 0 = empty plane;
- *               runs may overlap and may run past the end (clipped)
+ *               runs may overlap; a run is clipped to the plane on both
+ *               sides (start < 1, past the end, negative length: no write)
  *   mask_dev    [n_planes][H][W] uint8 {0,1}, overwritten */
 int mlc_rle_decode(const int32_t *runs_dev, const int64_t *off_dev,
                    const int32_t *cnt_dev, int64_t n_planes, int H, int W,

@@ -47,6 +47,8 @@ SIGNATURES = {
     'mlc_dice_search_static': (c_int, [c_void_p, c_int64, c_int, c_int,
                                        POINTER(c_int32), c_int, c_int, c_double,
                                        c_void_p, c_void_p, c_void_p]),
+    'mlc_combine_ranks': (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p,
+                                  c_void_p]),
     'mlc_plane_dice': (c_int, [c_void_p, c_int64, c_int, c_int,
                                POINTER(c_int32), POINTER(c_int32), c_int,
                                c_double, c_void_p, c_void_p]),

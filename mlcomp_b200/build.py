@@ -31,7 +31,7 @@ LIB_DIR = os.path.join(HERE, 'lib')
 LIB = os.path.join(LIB_DIR, 'libmlcomp_b200.so')
 SOURCES = ['common.cu', 'confusion.cu', 'seg_hist.cu', 'seg_hist_guarded.cu',
            'dice_scan.cu', 'rle.cu', 'rle_format.cu', 'rle_decode.cu',
-           'composite.cu']
+           'composite.cu', 'exchange.cu']
 
 
 def nvcc_path():

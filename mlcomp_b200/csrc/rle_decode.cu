@@ -42,7 +42,10 @@ rle_decode_kernel(const __grid_constant__ DecArgs a) {
       __syncthreads();
       for (int r = threadIdx.x; r < n_runs; r += kDecThreads) {
         const int2 run = runs[r];
+        // clipped to the plane on both sides: a malformed row (start < 1,
+        // negative length, run past the end) must not write outside it
         long long p = (long long)run.x - 1, e = min(px, p + run.y);
+        p = max(p, 0ll);
         for (; p < e; ++p) out[(p % H) * W + p / H] = 1;
       }
       __syncthreads();
@@ -54,6 +57,7 @@ rle_decode_kernel(const __grid_constant__ DecArgs a) {
       const int2 run = runs[r];
       long long p = (long long)run.x - 1;               // 0-based, col-major
       long long e = min(px, p + (long long)run.y);      // exclusive
+      p = max(p, 0ll);  // start < 1 in a malformed row: clip, do not write
       while (p < e) {
         const int x = (int)(p / H), y = (int)(p - (long long)x * H);
         const int in_col = (int)min((long long)(H - y), e - p);  // this column

@@ -28,13 +28,13 @@ struct HistArgs {
   int items_per_row;     // row mode: W / 8 full items per row
   int flat;
   float scale, bias;
-  // seg_hist_guarded: f = q * g_kq + g_fb puts the bin index of the mean of
-  // the S sigmoids (q = their sum) into [128, 256), where a float has 16
-  // fractional bits; a pixel is decided when the fraction lies inside
-  // [g_lo, 65535 - g_lo] (g_span = 65535 - 2 g_lo), else it is evaluated
-  // exactly
-  float g_kq, g_fb;
-  uint32_t g_lo, g_span;
+  // seg_hist_guarded (see seg_hist_guarded.cu): grid position of the mean of
+  // the S sigmoids, f = q * g_kq + bias with q their sum, evaluated at
+  // f + 128 -/+ the error bound (16 fractional bits in [128, 256)); per-source
+  // item-index constants of the flips
+  float g_kq, g_fb_lo, g_fb_hi;
+  int g_b[MLC_MAX_SOURCES], g_cy[MLC_MAX_SOURCES], g_cx[MLC_MAX_SOURCES];
+  uint32_t g_rev;  // bit k: source k holds its items reversed (h-flip)
 };
 
 __device__ __forceinline__ void flush_bins(uint32_t *cnt, int nbins,

@@ -48,7 +48,9 @@ namespace mlc {
 #endif
 constexpr int kGThreads = MLC_G_THREADS;
 constexpr float kNegLog2e = -1.4426950408889634f;
-constexpr float kDLimit = 1.0e37f;  // products above this may have overflowed
+// denominators (products of up to four 1 + e^-x) from this bit pattern on -
+// 1e37f, +inf, every NaN - may have overflowed
+constexpr uint32_t kDLimitBits = 0x7CF0BDC2u;
 
 #ifdef MLC_DEV_KNOBS
 __device__ unsigned long long g_guard_slow_px;  // pixels sent to the exact path
@@ -88,19 +90,24 @@ __device__ __noinline__ uint32_t guarded_exact_bin(const HistArgs &a,
 }
 
 // q[i] (+)= sum over the NG sources of the group of 1 / (1 + 2^(x * -log2 e))
-// for the eight pixels of one item; dmax keeps the largest denominator.
-template <int NG>
+// for the eight pixels of one item; dmax keeps the largest denominator as a
+// bit pattern (unsigned order: finite positive < +inf < every NaN).
+// REV: bit j set = source j holds the item's pixels in reverse order (a
+// horizontal flip): pixel p is then element 7 - p of its words - resolved here
+// by naming the right register, not by moving data.
+template <int NG, int REV>
 __device__ __forceinline__ void group_sum(const uint32_t (&w)[4][4], bool first,
-                                          float (&q)[8], float &dmax) {
+                                          float (&q)[8], uint32_t &dmax) {
 #pragma unroll
   for (int h = 0; h < 4; ++h) {
     float a[4][2];
 #pragma unroll
     for (int j = 0; j < NG; ++j) {
-      const float2 x =
-          __half22float2(*reinterpret_cast<const __half2 *>(&w[j][h]));
-      a[j][0] = 1.0f + ex2_approx(x.x * kNegLog2e);
-      a[j][1] = 1.0f + ex2_approx(x.y * kNegLog2e);
+      const bool rev = (REV >> j) & 1;
+      const float2 x = __half22float2(
+          *reinterpret_cast<const __half2 *>(&w[j][rev ? 3 - h : h]));
+      a[j][0] = 1.0f + ex2_approx((rev ? x.y : x.x) * kNegLog2e);
+      a[j][1] = 1.0f + ex2_approx((rev ? x.x : x.y) * kNegLog2e);
     }
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
@@ -120,7 +127,7 @@ __device__ __forceinline__ void group_sum(const uint32_t (&w)[4][4], bool first,
         n = 1.0f;
         d = a[0][e];
       }
-      dmax = fmaxf(dmax, d);
+      dmax = max(dmax, __float_as_uint(d));
       const float g = n * rcp_approx(d);
       q[2 * h + e] = first ? g : q[2 * h + e] + g;
     }
@@ -133,25 +140,131 @@ __device__ __forceinline__ void reverse8(uint32_t (&w)[4]) {
   w[0] = t0; w[1] = t1; w[2] = t2; w[3] = t3;
 }
 
+// ---- the kernel ------------------------------------------------------------
+// NS: number of sources when it is one of the instantiated counts (the source
+// loop, the group structure and every per-source constant are then resolved
+// at compile time: ncu showed 29 of 61 instructions per pixel of the first,
+// run-time version were loop / flag / address bookkeeping and spills), 0 =
+// any count (run-time loop over groups of four).
 // ROWS: flipped sources, rows a whole number of aligned 16-byte items (flips
 // are item-index arithmetic); else no transforms, planes are flat arrays.
 // BINS: also write every pixel's bin index (mlc_seg_hist_bins).
+//
+// Per source k the host precomputes (HistArgs::g_*) the item index of output
+// item (y, xi) in the source plane as g_b[k] + g_cy[k] * y + g_cx[k] * xi
+// (flat mode: 0, 0, 1 with y = 0, xi = item) and whether its eight elements
+// come reversed (horizontal flip).
+template <int NG>
+__device__ __forceinline__ void load_group(const HistArgs &a, int k0,
+                                           const __half *const *base, int y,
+                                           int xi, uint32_t (&w)[4][4]) {
+#pragma unroll
+  for (int j = 0; j < NG; ++j) {
+    const int idx = a.g_b[k0 + j] + a.g_cy[k0 + j] * y + a.g_cx[k0 + j] * xi;
+    const uint4 r = ldg_stream16(base[j] + (size_t)(uint32_t)idx * 8);
+    w[j][0] = r.x; w[j][1] = r.y; w[j][2] = r.z; w[j][3] = r.w;
+  }
+}
+
+// One group of NG sources: reversal masks that occur in practice (none; the
+// (id, h, v, hv) order of a 4-flip TTA and its mirror; all) are resolved at
+// compile time, any other mask moves the data first.
+template <int NG, bool ROWS>
+__device__ __forceinline__ void do_group(const HistArgs &a, int k0, int rmask,
+                                         uint32_t (&w)[4][4], bool first,
+                                         float (&q)[8], uint32_t &dmax) {
+  constexpr int kAll = (1 << NG) - 1;
+  if (!ROWS || rmask == 0) {
+    group_sum<NG, 0>(w, first, q, dmax);
+  } else if (NG >= 2 && rmask == (0xA & kAll)) {
+    group_sum<NG, 0xA & kAll>(w, first, q, dmax);
+  } else if (NG >= 2 && rmask == (0x5 & kAll)) {
+    group_sum<NG, 0x5 & kAll>(w, first, q, dmax);
+  } else if (rmask == kAll) {
+    group_sum<NG, kAll>(w, first, q, dmax);
+  } else {
+#pragma unroll
+    for (int j = 0; j < NG; ++j)
+      if ((rmask >> j) & 1) reverse8(w[j]);
+    group_sum<NG, 0>(w, first, q, dmax);
+  }
+}
+
+// From the sums of sigmoids of one item to its histogram updates (and bin
+// bytes): grid position moved down / up by the error bound, exact evaluation
+// of the pixels the two disagree on, one shared-memory atomic per pixel.
 template <bool ROWS, bool BINS>
+__device__ __forceinline__ void finish_item(const HistArgs &a,
+                                            const float (&q)[8], uint32_t dmax,
+                                            uint2 g, uint32_t slot,
+                                            size_t plane_off, int it, int y,
+                                            int xi, const float *thr) {
+  const float kq = a.g_kq, fb_lo = a.g_fb_lo, fb_hi = a.g_fb_hi;
+  uint32_t fx[8], differ = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    fx[i] = __float_as_uint(fmaf(q[i], kq, fb_lo));
+    differ |= fx[i] ^ __float_as_uint(fmaf(q[i], kq, fb_hi));
+  }
+  // a product that may have overflowed, +inf or a NaN anywhere in the item (a
+  // NaN input makes every later product NaN): nothing of the item is trusted
+  const bool all = dmax >= kDLimitBits;
+  if ((differ >> 16) != 0u || all) {
+    // rare: the estimate cannot decide (or cannot be trusted for) some pixel
+    // of this item - those pixels are evaluated exactly
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint32_t hi = __float_as_uint(fmaf(q[i], kq, fb_hi));
+      if (all || ((fx[i] ^ hi) >> 16) != 0u) {
+        const int px = ROWS ? xi * 8 + i : it * 8 + i;
+        fx[i] = 0x43008000u |
+                (guarded_exact_bin(a, plane_off, ROWS ? y : 0, px, thr) << 16);
+      }
+    }
+  }
+  // bin = bits 16..22 of fx (the exponent field reads 0x4300 + bin)
+  if ((g.x | g.y) == 0u) {  // all background: the increment is 1
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      red_shared_add(((fx[i] >> 9) & 0x3F80u) | slot, 1u);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint32_t gb = ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
+      red_shared_add(((fx[i] >> 9) & 0x3F80u) | slot, gb ? 0x10000u : 1u);
+    }
+  }
+  if (BINS) {
+    // byte 2 of each fx is its bin (< 128)
+    uint2 v;
+    v.x = prmt32(prmt32(fx[0], fx[1], 0x0062u), prmt32(fx[2], fx[3], 0x0062u),
+                 0x5410u);
+    v.y = prmt32(prmt32(fx[4], fx[5], 0x0062u), prmt32(fx[6], fx[7], 0x0062u),
+                 0x5410u);
+    *reinterpret_cast<uint2 *>(a.bins + plane_off + (size_t)it * 8) = v;
+  }
+}
+
+template <int NS, bool ROWS, bool BINS>
 __global__ void __launch_bounds__(kGThreads, MLC_G_MINB)
 seg_hist_guarded(const __grid_constant__ HistArgs a) {
   extern __shared__ __align__(16) uint32_t gsm[];
   const int B = a.B, nbins = B + 1;
-  uint32_t *cnt = gsm;                                   // [nbins][32]
-  float *thr = reinterpret_cast<float *>(gsm + nbins * 32);  // [B]
+  // the counters [nbins][32] start on a 16 KiB boundary of the shared window:
+  // a counter's address is then (bin << 7) | lane * 4 | base, one LOP3
+  const uint32_t gsm_sa = (uint32_t)__cvta_generic_to_shared(gsm);
+  const uint32_t cnt_sa = (gsm_sa + 16383u) & ~16383u;
+  uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
+  float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
   for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) cnt[i] = 0;
   for (int i = threadIdx.x; i < B; i += blockDim.x) thr[i] = a.thr.v[i];
   __syncthreads();
-  const uint32_t lane4 = (threadIdx.x & 31) * 4;
-  const uint32_t cnt_sa = (uint32_t)__cvta_generic_to_shared(cnt);
+  const uint32_t slot = cnt_sa | ((threadIdx.x & 31) * 4);
   const long long n_units = a.n_planes * a.units_per_plane;
-  const int S = a.src.n;
-  const float kq = a.g_kq, fb = a.g_fb;
-  const uint32_t lo = a.g_lo, span = a.g_span;
+  const int S = NS ? NS : a.src.n;
+  // position on the threshold grid, shifted into [128, 256) (16 fractional
+  // bits), once moved down and once up by the error bound: a pixel is
+  // decided when both land in the same bin
   const int ipr = a.items_per_row;  // ROWS: W / 8
 
   for (long long unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
@@ -170,85 +283,65 @@ seg_hist_guarded(const __grid_constant__ HistArgs a) {
       dy = (int)blockDim.x / ipr;
       dx = (int)blockDim.x - dy * ipr;
     }
+    // this plane of the first sources (the others are added per item)
+    constexpr int kHoist = NS > 0 && NS <= 4 ? NS : 1;
+    const __half *base[4];
+#pragma unroll
+    for (int j = 0; j < kHoist; ++j)
+      base[j] = static_cast<const __half *>(a.src.ptr[j]) + plane_off;
     for (; it < i1; it += blockDim.x) {
       float q[8];
-      float dmax = 0.f;
-      for (int k0 = 0; k0 < S; k0 += 4) {
-        const int ng = min(4, S - k0);
-        uint32_t w[4][4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (j < ng) {
-            size_t e0;
-            if (ROWS) {
-              const int xf = a.src.xf[k0 + j];
-              const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
-              const int xs = (xf & MLC_XF_HFLIP) ? ipr - 1 - xi : xi;
-              e0 = plane_off + (size_t)(ys * ipr + xs) * 8;
-            } else {
-              e0 = plane_off + (size_t)it * 8;
-            }
-            const uint4 r = ldg_stream16(
-                static_cast<const __half *>(a.src.ptr[k0 + j]) + e0);
-            w[j][0] = r.x; w[j][1] = r.y; w[j][2] = r.z; w[j][3] = r.w;
+      uint32_t dmax = 0u;
+      uint32_t w[4][4];
+      if (NS == 0) {
+        for (int k0 = 0; k0 < S; k0 += 4) {
+          const int ng = min(4, S - k0);
+          const int rm = (a.g_rev >> k0) & 0xF;
+          for (int j = 0; j < ng; ++j)
+            base[j] = static_cast<const __half *>(a.src.ptr[k0 + j]) +
+                      plane_off;
+          if (ng == 4) {
+            load_group<4>(a, k0, base, y, xi, w);
+            do_group<4, ROWS>(a, k0, rm, w, k0 == 0, q, dmax);
+          } else if (ng == 3) {
+            load_group<3>(a, k0, base, y, xi, w);
+            do_group<3, ROWS>(a, k0, rm & 7, w, k0 == 0, q, dmax);
+          } else if (ng == 2) {
+            load_group<2>(a, k0, base, y, xi, w);
+            do_group<2, ROWS>(a, k0, rm & 3, w, k0 == 0, q, dmax);
+          } else {
+            load_group<1>(a, k0, base, y, xi, w);
+            do_group<1, ROWS>(a, k0, rm & 1, w, k0 == 0, q, dmax);
           }
         }
-        if (ROWS) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (j < ng && (a.src.xf[k0 + j] & MLC_XF_HFLIP)) reverse8(w[j]);
-        }
-        if (ng == 4) group_sum<4>(w, k0 == 0, q, dmax);
-        else if (ng == 3) group_sum<3>(w, k0 == 0, q, dmax);
-        else if (ng == 2) group_sum<2>(w, k0 == 0, q, dmax);
-        else group_sum<1>(w, k0 == 0, q, dmax);
-      }
-      const uint2 g = ldg_stream8(gtp + (size_t)it * 8);
-      // bin index and distance to the grid lines of every pixel
-      uint32_t fx[8], worst = 0;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        fx[i] = __float_as_uint(fmaf(q[i], kq, fb));
-        worst = max(worst, (fx[i] - lo) & 0xFFFFu);
-      }
-      if (worst > span || !(dmax < kDLimit)) {
-        // rare: the estimate cannot decide (or cannot be trusted for) some
-        // pixel of this item - those pixels are evaluated exactly
-        const bool all = !(dmax < kDLimit);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (all || ((fx[i] - lo) & 0xFFFFu) > span) {
-            const int px = ROWS ? xi * 8 + i : it * 8 + i;
-            fx[i] = 0x43008000u |
-                    (guarded_exact_bin(a, plane_off, ROWS ? y : 0, px, thr)
-                     << 16);
-          }
-        }
-      }
-      // bin = bits 16..22 of fx (the exponent field reads 0x4300 + bin)
-      if ((g.x | g.y) == 0u) {  // all background: the increment is 1
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-          red_shared_add(cnt_sa + (((fx[i] >> 9) & 0x3F80u) | lane4), 1u);
       } else {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const uint32_t gb = ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
-          red_shared_add(cnt_sa + (((fx[i] >> 9) & 0x3F80u) | lane4),
-                         gb ? 0x10000u : 1u);
+        for (int k0 = 0; k0 < NS; k0 += 4) {
+          constexpr int kFull = NS / 4 * 4;
+          if (NS > 4) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (k0 + j < NS)
+                base[j] = static_cast<const __half *>(a.src.ptr[k0 + j]) +
+                          plane_off;
+          }
+          if (k0 < kFull) {
+            load_group<4>(a, k0, base, y, xi, w);
+            do_group<4, ROWS>(a, k0, (a.g_rev >> k0) & 0xF, w, k0 == 0, q,
+                              dmax);
+          } else {
+            constexpr int kRest = NS % 4 ? NS % 4 : 1;
+            load_group<kRest>(a, k0, base, y, xi, w);
+            do_group<kRest, ROWS>(a, k0,
+                                  (a.g_rev >> k0) & ((1 << kRest) - 1), w,
+                                  k0 == 0, q, dmax);
+          }
         }
       }
-      if (BINS) {
-        // byte 2 of each fx is its bin (< 128)
-        uint2 v;
-        v.x = prmt32(prmt32(fx[0], fx[1], 0x0062u), prmt32(fx[2], fx[3], 0x0062u),
-                     0x5410u);
-        v.y = prmt32(prmt32(fx[4], fx[5], 0x0062u), prmt32(fx[6], fx[7], 0x0062u),
-                     0x5410u);
-        *reinterpret_cast<uint2 *>(a.bins + plane_off + (size_t)it * 8) = v;
-      }
+      finish_item<ROWS, BINS>(a, q, dmax, ldg_stream8(gtp + (size_t)it * 8),
+                              slot, plane_off, it, y, xi, thr);
+      xi += dx;
       if (ROWS) {
-        xi += dx;
         y += dy;
         if (xi >= ipr) {
           xi -= ipr;
@@ -259,6 +352,147 @@ seg_hist_guarded(const __grid_constant__ HistArgs a) {
     uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
     flush_bins(cnt, nbins, out, a.units_per_plane > 1);
   }
+}
+
+// ---- the same kernel fed through cp.async ----------------------------------
+// ncu on seg_hist_guarded (4-flip TTA): 46 % of the cycles between two issues
+// of a warp are spent waiting for its four 128-bit loads (8 warps per
+// scheduler, all at the same point of the loop), issue slots 67 % busy.  Here
+// every thread copies the NEXT item's 16 bytes per source + 8 truth bytes into
+// its own shared-memory slots (cp.async: no registers held while the data is
+// in flight) before it works on the current one, then reads them back with
+// LDS - a thread only ever touches its own slots, so cp.async.wait_group is
+// all the synchronisation needed.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src)
+               : "memory");
+}
+__device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y)
+               : "r"(addr));
+  return v;
+}
+
+template <int NS, bool ROWS, bool BINS>
+__global__ void __launch_bounds__(1024, 1)
+seg_hist_guarded_pf(const __grid_constant__ HistArgs a) {
+  extern __shared__ __align__(16) uint32_t gsm[];
+  const int B = a.B, nbins = B + 1;
+  const uint32_t gsm_sa = (uint32_t)__cvta_generic_to_shared(gsm);
+  const uint32_t cnt_sa = (gsm_sa + 16383u) & ~16383u;
+  uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
+  float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
+  for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) cnt[i] = 0;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) thr[i] = a.thr.v[i];
+  __syncthreads();
+  const uint32_t slot = cnt_sa | ((threadIdx.x & 31) * 4);
+  const uint32_t nt = blockDim.x;
+  // stages behind the threshold table: [2][NS][nt] x 16 B, then [2][nt] x 8 B
+  const uint32_t st_sa = (cnt_sa + nbins * 128 + B * 4 + 15u) & ~15u;
+  const uint32_t my_src = st_sa + threadIdx.x * 16u;
+  const uint32_t my_gt = st_sa + 2u * NS * nt * 16u + threadIdx.x * 8u;
+  const long long n_units = a.n_planes * a.units_per_plane;
+  const int ipr = a.items_per_row;
+
+  for (long long unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+    const long long plane = unit / a.units_per_plane;
+    const int sub = (int)(unit - plane * a.units_per_plane);
+    const size_t plane_off = (size_t)plane * a.plane_px;
+    const uint8_t *gtp = a.gt + plane_off;
+    const int i0 = (int)((long long)sub * a.items_per_unit);
+    const int i1 = (int)min(a.items_per_plane, (long long)i0 + a.items_per_unit);
+    int it = i0 + (int)threadIdx.x;
+    int y = 0, xi = it;
+    int dy = 0, dx = (int)nt;
+    if (ROWS) {
+      y = it / ipr;
+      xi = it - y * ipr;
+      dy = (int)nt / ipr;
+      dx = (int)nt - dy * ipr;
+    }
+    auto issue = [&](int it_, int y_, int xi_, uint32_t stage) {
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        const int idx = a.g_b[j] + a.g_cy[j] * y_ + a.g_cx[j] * xi_;
+        cp_async16(my_src + (stage * NS + j) * nt * 16u,
+                   static_cast<const __half *>(a.src.ptr[j]) + plane_off +
+                       (size_t)(uint32_t)idx * 8);
+      }
+      cp_async8(my_gt + stage * nt * 8u, gtp + (size_t)it_ * 8);
+    };
+    uint32_t stage = 0;
+    if (it < i1) issue(it, y, xi, 0u);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (; it < i1; it += nt) {
+      int y2 = y, xi2 = xi + dx;
+      if (ROWS) {
+        y2 += dy;
+        if (xi2 >= ipr) {
+          xi2 -= ipr;
+          ++y2;
+        }
+      }
+      if (it + (int)nt < i1) issue(it + (int)nt, y2, xi2, stage ^ 1u);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      float q[8];
+      uint32_t dmax = 0u;
+      uint32_t w[4][4];
+#pragma unroll
+      for (int k0 = 0; k0 < NS; k0 += 4) {
+        constexpr int kFull = NS / 4 * 4;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (k0 + j < NS) {
+            const uint4 r = lds_u4(my_src + (stage * NS + k0 + j) * nt * 16u);
+            w[j][0] = r.x; w[j][1] = r.y; w[j][2] = r.z; w[j][3] = r.w;
+          }
+        if (k0 < kFull) {
+          do_group<4, ROWS>(a, k0, (a.g_rev >> k0) & 0xF, w, k0 == 0, q, dmax);
+        } else {
+          constexpr int kRest = NS % 4 ? NS % 4 : 1;
+          do_group<kRest, ROWS>(a, k0, (a.g_rev >> k0) & ((1 << kRest) - 1), w,
+                                k0 == 0, q, dmax);
+        }
+      }
+      finish_item<ROWS, BINS>(a, q, dmax, lds_u2(my_gt + stage * nt * 8u), slot,
+                              plane_off, it, y, xi, thr);
+      y = y2;
+      xi = xi2;
+      stage ^= 1u;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
+    flush_bins(cnt, nbins, out, a.units_per_plane > 1);
+  }
+}
+
+template <int NS>
+static void (*pick_guarded_pf(bool rows, bool bins))(HistArgs) {
+  return bins ? (rows ? seg_hist_guarded_pf<NS, true, true>
+                      : seg_hist_guarded_pf<NS, false, true>)
+              : (rows ? seg_hist_guarded_pf<NS, true, false>
+                      : seg_hist_guarded_pf<NS, false, false>);
+}
+
+template <int NS>
+static void (*pick_guarded(bool rows, bool bins))(HistArgs) {
+  return bins ? (rows ? seg_hist_guarded<NS, true, true>
+                      : seg_hist_guarded<NS, false, true>)
+              : (rows ? seg_hist_guarded<NS, true, false>
+                      : seg_hist_guarded<NS, false, false>);
 }
 
 bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
@@ -279,26 +513,68 @@ bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
   }
   if (g > 1e-3) return false;
   const double u = 5.9604644775390625e-8;  // 2^-24
-  // error of the estimated mean against the reference mean, in grid steps,
-  // + grid irregularity + rounding of scale / S + rounding of the final fma
+  // error of the estimated mean against the reference mean, in grid steps
+  // (DESIGN.md section 3), + grid irregularity + rounding of scale / S +
+  // rounding of the two fma (constant and result: 2^-17 each at [128, 256))
   const double eps = sc * (24.0 + 0.25 * S) * u + g + u * (B + 1) +
-                     7.62939453125e-6;
-  const double lo = eps * 65536.0 + 2.0;
-  if (lo > 4096.0) return false;
+                     2.0 * 7.62939453125e-6;
+  const double steps = eps * 65536.0 + 2.0;   // in units of 2^-16
+  if (steps > 4096.0) return false;
+  const double e = ((double)(long long)steps + 1.0) / 65536.0;
   a.g_kq = (float)(sc / (double)S);
-  a.g_fb = (float)(bi + 128.0);
-  a.g_lo = (uint32_t)lo + 1u;
-  a.g_span = 65535u - 2u * a.g_lo;
-  const size_t smem = (size_t)(B + 1) * 32 * 4 + (size_t)B * 4;
+  a.g_fb_lo = (float)(bi + 128.0 - e);
+  a.g_fb_hi = (float)(bi + 128.0 + e);
+  // item index of output item (y, xi) in source k
+  const int ipr = a.items_per_row;
+  a.g_rev = 0u;
+  for (int k = 0; k < S; ++k) {
+    const int xf = rows ? a.src.xf[k] : 0;
+    const int vy = (xf & MLC_XF_VFLIP) ? 1 : 0, hx = (xf & MLC_XF_HFLIP) ? 1 : 0;
+    a.g_cy[k] = rows ? (vy ? -ipr : ipr) : 0;
+    a.g_cx[k] = hx ? -1 : 1;
+    a.g_b[k] = rows ? (vy ? (a.H - 1) * ipr : 0) + (hx ? ipr - 1 : 0) : 0;
+    if (hx) a.g_rev |= 1u << k;
+  }
+  // 16 KiB of slack to align the counters inside the shared window
+  const size_t smem = 16384 + (size_t)(B + 1) * 32 * 4 + (size_t)B * 4 + 16;
   const long long n_units = a.n_planes * a.units_per_plane;
   const int grid = (int)(n_units < (1ll << 22) ? n_units : (1ll << 22));
-  void (*k)(HistArgs) =
-      a.bins ? (rows ? seg_hist_guarded<true, true> : seg_hist_guarded<false, true>)
-             : (rows ? seg_hist_guarded<true, false>
-                     : seg_hist_guarded<false, false>);
-  k<<<grid, kGThreads, smem, st>>>(a);
-  const cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) *rc = cuda_fail(e, "seg_hist_guarded");
+  const bool bins = a.bins != nullptr;
+  // cp.async-fed variant: two stages of S x 16 + 8 bytes per thread; two
+  // 512-thread CTAs per SM when they fit the 227 KiB, else one of 1024
+  const size_t per_thread = 2 * ((size_t)S * 16 + 8);
+  const size_t sm_bytes = 227 * 1024;
+  int pf_threads = 0;
+#ifndef MLC_G_NO_PF
+  if (S >= 2 && S <= 5) {
+    if (2 * (smem + 512 * per_thread + 1024) <= sm_bytes) pf_threads = 512;
+    else if (smem + 1024 * per_thread + 1024 <= sm_bytes) pf_threads = 1024;
+  }
+#endif
+  if (pf_threads) {
+    void (*k)(HistArgs) = S == 2   ? pick_guarded_pf<2>(rows, bins)
+                          : S == 3 ? pick_guarded_pf<3>(rows, bins)
+                          : S == 4 ? pick_guarded_pf<4>(rows, bins)
+                                   : pick_guarded_pf<5>(rows, bins);
+    const size_t pf_smem = smem + pf_threads * per_thread;
+    const cudaError_t ea = cudaFuncSetAttribute(
+        k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pf_smem);
+    if (ea != cudaSuccess) {
+      *rc = cuda_fail(ea, "cudaFuncSetAttribute(seg_hist_guarded_pf)");
+      return true;
+    }
+    k<<<grid, pf_threads, pf_smem, st>>>(a);
+  } else {
+    void (*k)(HistArgs) = S == 2   ? pick_guarded<2>(rows, bins)
+                          : S == 3 ? pick_guarded<3>(rows, bins)
+                          : S == 4 ? pick_guarded<4>(rows, bins)
+                          : S == 5 ? pick_guarded<5>(rows, bins)
+                          : S == 8 ? pick_guarded<8>(rows, bins)
+                                   : pick_guarded<0>(rows, bins);
+    k<<<grid, kGThreads, smem, st>>>(a);
+  }
+  const cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) *rc = cuda_fail(err, "seg_hist_guarded");
   return true;
 }
 

@@ -254,10 +254,11 @@ def _areas(min_areas, n_cls):
 
 
 def dice_search(hist, min_areas=(0,), empty_one=True, eps=1e-6,
-                want_micro=True):
+                want_micro=True, out=None, micro=None):
     """Histograms -> sum over images of dice for every (class, threshold,
     min-area) (mlc_dice_search).  Returns (dice_sum fp64 [C,B,A],
-    micro int64 [C, 1+2B] = {T, P[k], I[k]} or None)."""
+    micro int64 [C, 1+2B] = {T, P[k], I[k]} or None); ``out`` / ``micro``:
+    contiguous device tensors of those shapes to write into."""
     lib = _lib.load()
     hist = _need_cuda(hist, 'hist', (torch.int32,))
     if hist.dim() != 4 or hist.shape[2] != 2:
@@ -267,9 +268,14 @@ def dice_search(hist, min_areas=(0,), empty_one=True, eps=1e-6,
     areas, areas_p = _areas(min_areas, c)
     a = areas.shape[1]
     dev = hist.device
-    out = torch.empty((c, b, a), dtype=torch.float64, device=dev)
-    micro = torch.empty((c, 1 + 2 * b), dtype=torch.int64, device=dev) \
-        if want_micro else None
+    if out is None:
+        out = torch.empty((c, b, a), dtype=torch.float64, device=dev)
+    if micro is None and want_micro:
+        micro = torch.empty((c, 1 + 2 * b), dtype=torch.int64, device=dev)
+    _need_cuda(out, 'out', (torch.float64,))
+    if out.numel() != c * b * a or \
+            (micro is not None and micro.numel() != c * (1 + 2 * b)):
+        raise ValueError('out / micro have the wrong size')
     need = lib.mlc_dice_search_workspace(n, c, b, a)
     work = torch.empty(max(need, 8), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
@@ -429,6 +435,9 @@ def rle_parse(strings, device='cuda'):
     for a in arrays:
         if a.size % 2:
             raise ValueError('an RLE string needs an even number of values')
+        if a.size and (a[0::2].min() < 1 or a[1::2].min() < 0):
+            raise ValueError('RLE starts are 1-based and lengths are not '
+                             'negative (rle.py:22-26)')
     cnt = np.array([a.size // 2 for a in arrays], dtype=np.int32)
     off = np.concatenate([[0], np.cumsum(2 * cnt.astype(np.int64))[:-1]]) \
         if len(arrays) else np.zeros(0, np.int64)

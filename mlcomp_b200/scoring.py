@@ -14,7 +14,7 @@ import torch
 from . import ops
 
 __all__ = ['SegSearch', 'ClassifyScore', 'HostStager', 'shard_range',
-           'combine_ranks']
+           'combine_ranks', 'combine_packed']
 
 
 def _xf_code(x):
@@ -26,36 +26,59 @@ def shard_range(n, rank, world):
     return (n * rank) // world, (n * (rank + 1)) // world
 
 
-def combine_ranks(dice_sum, micro, n_img, group=None):
-    """The one exchange step of the sharded path.
+def combine_packed(packed, n_f64, group=None):
+    """The one exchange step of the sharded path on a packed
+    int64 buffer: the first ``n_f64`` entries are fp64 bit patterns (the
+    ``dice_sum`` partials), the rest integers (``micro`` counts, image count).
 
-    ONE all_gather of a packed int64 buffer per rank: the fp64 ``dice_sum``
-    (bit pattern), the int64 ``micro`` counts and ``n_img``.  Integers are
-    then summed (exact, order-independent); the fp64 partial sums are added
-    in rank order on every rank, so every rank (and every rerun at the same
-    world size) holds bit-identical scores.  Works on whatever device the
-    tensors live on (NCCL for CUDA, gloo for the CPU tests).  No-op without
-    an initialised process group or at world size 1."""
+    ONE collective (all_gather of the buffer) and ONE kernel
+    (mlc_combine_ranks): integers are summed (exact, order-independent), the
+    fp64 partial sums are added in rank order on every rank, so every rank
+    (and every rerun at the same world size) holds bit-identical scores.
+    NCCL for CUDA tensors; CPU tensors (the gloo tests of the host logic) are
+    folded with the same rule by torch.  No-op without an initialised process
+    group or at world size 1."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or \
+            dist.get_world_size(group) == 1:
+        return packed
+    world = dist.get_world_size(group)
+    n = packed.numel()
+    rows = torch.empty((world, n), dtype=torch.int64, device=packed.device)
+    dist.all_gather_into_tensor(rows, packed.contiguous(), group=group)
+    out = torch.empty_like(packed)
+    if packed.is_cuda:
+        from . import _lib
+        lib = _lib.load()
+        with torch.cuda.device(packed.device):
+            _lib.check(lib.mlc_combine_ranks(
+                rows.data_ptr(), world, n_f64, n - n_f64, out.data_ptr(),
+                torch.cuda.current_stream().cuda_stream))
+        return out
+    parts = rows[:, :n_f64].contiguous().view(torch.float64)
+    total = parts[0].clone()
+    for r in range(1, world):
+        total += parts[r]
+    out[:n_f64] = total.view(torch.int64)
+    out[n_f64:] = rows[:, n_f64:].sum(dim=0)
+    return out
+
+
+def combine_ranks(dice_sum, micro, n_img, group=None):
+    """``combine_packed`` for separate tensors: returns the combined
+    (dice_sum, micro, n_img)."""
     import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized()) or \
             dist.get_world_size(group) == 1:
         return dice_sum, micro, n_img
-    world = dist.get_world_size(group)
     nd, nm = dice_sum.numel(), micro.numel()
-    mine = torch.cat([dice_sum.contiguous().view(torch.int64).reshape(-1),
-                      micro.reshape(-1),
-                      torch.tensor([n_img], dtype=torch.int64,
-                                   device=micro.device)])
-    rows = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(rows, mine, group=group)
-    everyone = torch.stack(rows)
-    parts = everyone[:, :nd].contiguous().view(torch.float64)
-    total = parts[0].clone()
-    for r in range(1, world):
-        total += parts[r]
-    ints = everyone[:, nd:].sum(dim=0)
-    return (total.reshape(dice_sum.shape), ints[:nm].reshape(micro.shape),
-            ints[nm])
+    packed = torch.cat([dice_sum.contiguous().view(torch.int64).reshape(-1),
+                        micro.reshape(-1),
+                        torch.tensor([n_img], dtype=torch.int64,
+                                     device=micro.device)])
+    out = combine_packed(packed, nd, group)
+    return (out[:nd].view(torch.float64).reshape(dice_sum.shape),
+            out[nd:nd + nm].reshape(micro.shape), out[-1])
 
 
 class HostStager:
@@ -195,10 +218,15 @@ class SegSearch:
         self.lut = ops.seg_lut(self.thr, activation, self.device) \
             if use_lut and activation != 'softmax' else None
         b, a = len(self.thr), self.min_areas.shape[1]
-        self.dice_sum = torch.zeros((self.n_cls, b, a), dtype=torch.float64,
-                                    device=self.device)
-        self.micro = torch.zeros((self.n_cls, 1 + 2 * b), dtype=torch.int64,
-                                 device=self.device)
+        # one buffer for everything that is exchanged / read back: the fp64
+        # dice sums (as bit patterns), the int64 counts, the image count
+        nd, nm = self.n_cls * b * a, self.n_cls * (1 + 2 * b)
+        self._nd = nd
+        self.packed = torch.zeros(nd + nm + 1, dtype=torch.int64,
+                                  device=self.device)
+        self.dice_sum = self.packed[:nd].view(torch.float64) \
+            .view(self.n_cls, b, a)
+        self.micro = self.packed[nd:nd + nm].view(self.n_cls, 1 + 2 * b)
         self.n_img = 0
         self._fresh = False
         self._stage = None
@@ -233,12 +261,13 @@ class SegSearch:
         if self.record_events:
             ev[1].record()
             self.kernel_events.append(ev)
-        dsum, micro = ops.dice_search(hist, self.min_areas, self.empty_one,
-                                      self.eps)
-        if self._fresh:
-            self.dice_sum, self.micro = dsum, micro
+        if self._fresh:     # first chunk of a pass: written in place
+            ops.dice_search(hist, self.min_areas, self.empty_one, self.eps,
+                            out=self.dice_sum, micro=self.micro)
             self._fresh = False
         else:
+            dsum, micro = ops.dice_search(hist, self.min_areas,
+                                          self.empty_one, self.eps)
             self.dice_sum += dsum
             self.micro += micro
         self.n_img += hist.shape[0]
@@ -298,18 +327,15 @@ class SegSearch:
     # -- combine + search -------------------------------------------------------
     def result(self, group=None):
         """Combine ranks (``combine_ranks``) and search the grid."""
-        dice_sum, micro, n_img = combine_ranks(self.dice_sum, self.micro,
-                                               self.n_img, group)
-        # one device->host copy for everything the host-side search needs
-        packed = torch.cat([
-            dice_sum.reshape(-1).view(torch.int64), micro.reshape(-1),
-            torch.as_tensor(n_img, dtype=torch.int64,
-                            device=micro.device).reshape(1)]).cpu().numpy()
-        nd = dice_sum.numel()
+        self.packed[-1:].fill_(self.n_img)
+        # one collective + one kernel, then one device->host copy for
+        # everything the host-side search needs
+        packed = combine_packed(self.packed, self._nd, group).cpu().numpy()
+        nd = self._nd
         n_img = int(packed[-1])
-        score = packed[:nd].view(np.float64).reshape(dice_sum.shape) / \
+        score = packed[:nd].view(np.float64).reshape(self.dice_sum.shape) / \
             max(n_img, 1)                                     # [C, B, A]
-        m = packed[nd:-1].reshape(micro.shape)
+        m = packed[nd:-1].reshape(self.micro.shape)
         b = len(self.thr)
         t_sum, p_sum, i_sum = m[:, 0], m[:, 1:1 + b], m[:, 1 + b:]
         best = []

@@ -37,6 +37,15 @@ def fuse(sources):
     act = sources[0].activation
     ts = [s.tensor.contiguous() for s in sources]
     if ts[0].dim() == 2:                           # classification logits
+        if act == 'softmax':
+            # over the class dim of [n, C], as apply_activation does it
+            # (utils/torch.py:16-17); mean as everywhere: fp32, left to
+            # right, one divide by S
+            acc = None
+            for t in ts:
+                p = torch.softmax(t.float(), 1)
+                acc = p if acc is None else acc + p
+            return acc / float(len(ts))
         ts = [t[None, None] for t in ts]
         return ops.seg_prob(ts, None, act)[0, 0]
     return ops.seg_prob(ts, [s.tags for s in sources], act)
@@ -56,7 +65,9 @@ def apply_activation(x, activation):
         shape = x.shape
         y = x.contiguous()
         y = y.reshape(1, 1, -1, shape[-1]) if y.dim() != 4 else y
-        return ops.seg_prob([y], None, 'sigmoid').reshape(shape)
+        # torch.sigmoid keeps the dtype: an fp16 tensor is evaluated in
+        # fp32 and rounded back, which is what the cast does
+        return ops.seg_prob([y], None, 'sigmoid').reshape(shape).to(x.dtype)
     if activation == 'softmax':
         if x.is_cuda and x.dim() == 4 and \
                 x.dtype in (torch.float16, torch.float32):

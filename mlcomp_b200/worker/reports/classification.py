@@ -16,17 +16,25 @@ from mlcomp_b200.worker.store import (Report, ReportImg, ReportSeries,
                                       ReportTasks, now)
 
 
-def resize_saving_ratio(img, size):          # mlcomp/utils/img.py:7-16
-    if not size:
+def fit_within(img, limit):
+    """Shrink ``img`` (H, W[, ch]) so that it fits ``limit = (max_h, max_w)``,
+    one axis after the other, keeping the aspect ratio and truncating the
+    scaled length - the two-step rule of mlcomp/utils/img.py:7-16 (a falsy
+    limit, or a falsy entry of it, leaves that axis alone)."""
+    if not limit:
         return img
     import cv2
-    if size[0] and img.shape[0] > size[0]:
-        k = size[0] / img.shape[0]
-        img = cv2.resize(img, (int(k * img.shape[1]), size[0]))
-    if size[1] and img.shape[1] > size[1]:
-        k = size[1] / img.shape[1]
-        img = cv2.resize(img, (size[1], int(k * img.shape[0])))
+    for axis in (0, 1):
+        cap = limit[axis]
+        if not cap or img.shape[axis] <= cap:
+            continue
+        other = int(cap / img.shape[axis] * img.shape[1 - axis])
+        h, w = (cap, other) if axis == 0 else (other, cap)
+        img = cv2.resize(img, (w, h))          # cv2 takes (width, height)
     return img
+
+
+resize_saving_ratio = fit_within       # the reference's name for it
 
 
 def _device_preds(preds):
