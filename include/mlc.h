@@ -129,6 +129,33 @@ int mlc_seg_prob(const void *const *src_dev_ptrs, const int32_t *xform,
                  int n_src, int dtype, int64_t n_img, int n_cls, int H, int W,
                  int act, float *prob_dev, void *stream);
 
+/* ---- segmentation: arg-max masks ----------------------------------------
+ * The multiclass deployment: per pixel the first maximal class of the fused
+ * class scores.  Replaces apply_activation(x, 'softmax') (utils/torch.py:16-17)
+ * -> TtaWrap.inverse (contrib/transform/tta.py:20-31) -> mean over sources ->
+ * numpy arg-max over the class axis (the rule of worker/reports/
+ * classification.py:111,136: a NaN beats everything, ties go to the lowest
+ * index) -> the sums of dice_numpy (contrib/metrics/dice.py:10-11,20) on the
+ * resulting one-hot masks.  Scores are computed exactly as mlc_seg_prob does,
+ * so label == argmax(mlc_seg_prob) bit for bit.  act: NONE, SIGMOID, SOFTMAX.
+ *   gt_onehot_dev [n_img][n_cls][H][W] uint8 or NULL (non-zero = set)
+ *   gt_label_dev  [n_img][H][W] uint8 or NULL; values >= n_cls are ignored
+ *                 (at most one of the two)
+ *   label_dev     [n_img][H][W] uint8 class index (n_cls <= 255), or NULL
+ *   onehot_dev    [n_img][n_cls][H][W] uint8 {0,1} = (label == class), or
+ *                 NULL: the masks mlc_rle_encode (MLC_U8, thr 0.5) and the
+ *                 report builders take
+ *   counts_dev    [n_img][n_cls][3] int64 {T, P, I} of those masks, or NULL
+ *                 (T and I are 0 without a truth), overwritten
+ *   cm_dev        [n_cls][n_cls] int64 pixel confusion, rows = truth, cols =
+ *                 prediction, or NULL (needs gt_label_dev), overwritten */
+int mlc_seg_argmax(const void *const *src_dev_ptrs, const int32_t *xform,
+                   int n_src, int dtype, int64_t n_img, int n_cls, int H,
+                   int W, int act, const uint8_t *gt_onehot_dev,
+                   const uint8_t *gt_label_dev, uint8_t *label_dev,
+                   uint8_t *onehot_dev, int64_t *counts_dev, int64_t *cm_dev,
+                   void *stream);
+
 /* ---- segmentation: histograms -> dice for the whole search grid --------
  * Replaces the loop of dice_numpy calls (contrib/metrics/dice.py:4-23) over
  * thresholds x min-areas x planes.  From hist: T = sum_j hist[1][j],

@@ -39,6 +39,10 @@ SIGNATURES = {
     'mlc_seg_prob': (c_int, [POINTER(c_void_p), POINTER(c_int32), c_int, c_int,
                              c_int64, c_int, c_int, c_int, c_int, c_void_p,
                              c_void_p]),
+    'mlc_seg_argmax': (c_int, [POINTER(c_void_p), POINTER(c_int32), c_int,
+                               c_int, c_int64, c_int, c_int, c_int, c_int,
+                               c_void_p, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_void_p, c_void_p]),
     'mlc_dice_search_workspace': (c_size_t, [c_int64, c_int, c_int, c_int]),
     'mlc_dice_search': (c_int, [c_void_p, c_int64, c_int, c_int,
                                 POINTER(c_int32), c_int, c_int, c_double,

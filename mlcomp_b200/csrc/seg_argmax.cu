@@ -1,0 +1,226 @@
+// Segmentation arg-max: per pixel, the first maximal class of the fused
+// (un-flipped, activated, averaged) class scores - the multiclass deployment
+// of the same executors.  Contract: include/mlc.h (mlc_seg_argmax).
+//
+// Reference arithmetic: apply_activation(x, 'softmax') = torch.softmax(x, 1)
+// per source (utils/torch.py:16-17), TtaWrap.inverse (tta.py:20-31), the
+// builder-defined fp32 mean over sources (as everywhere in this library), then
+// numpy's arg-max over the class axis as in worker/reports/classification.py
+// :111,136 - a NaN beats everything, ties go to the lowest index.  The class
+// scores are computed exactly as mlc_seg_prob computes them (same max / sum /
+// divide order, same mean rule), so label == argmax(mlc_seg_prob) bit for bit.
+//
+// One thread per pixel.  Per source the three steps of the soft-max (running
+// maximum over the classes, sum of expf(x - max) in class order, the divide)
+// re-read the pixel's class values; they stay in L1 (the working set of a CTA
+// is 256 px x S x C values), so DRAM sees every logit once.
+#include "mlc_common.cuh"
+
+namespace mlc {
+
+constexpr int kAmThreads = 256;
+constexpr int kAmMaxSmemClasses = 64;  // C x C table in shared memory
+
+struct ArgmaxArgs {
+  SrcSet src;
+  const uint8_t *gt_onehot;  // [n][C][H][W] or null
+  const uint8_t *gt_label;   // [n][H][W] or null
+  uint8_t *label;            // [n][H][W] or null
+  uint8_t *onehot;           // [n][C][H][W] or null
+  unsigned long long *counts;  // [n][C][3] = {T, P, I} or null
+  unsigned long long *cm;      // [C][C] rows = truth, cols = prediction, or null
+  long long n_img;
+  int C, H, W;
+  int act;
+  int chunks_per_img;
+};
+
+// element (class plane `pl`, output pixel (y, x)) of source k, un-transformed
+template <typename T>
+__device__ __forceinline__ float am_fetch(const ArgmaxArgs &a, int k,
+                                          long long pl, int y, int x) {
+  const int xf = a.src.xf[k];
+  const T *p = static_cast<const T *>(a.src.ptr[k]) +
+               (size_t)pl * a.H * a.W;
+  if (!(xf & MLC_XF_TRANSPOSE)) {
+    const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+    const int xs = (xf & MLC_XF_HFLIP) ? a.W - 1 - x : x;
+    return to_f32<T>(p[(size_t)ys * a.W + xs]);
+  }
+  // source plane is [W][H]: out[y][x] = src[ys][xs], (u, v) = (x, y)
+  const int ys = (xf & MLC_XF_VFLIP) ? a.W - 1 - x : x;
+  const int xs = (xf & MLC_XF_HFLIP) ? a.H - 1 - y : y;
+  return to_f32<T>(p[(size_t)ys * a.H + xs]);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kAmThreads)
+seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
+  extern __shared__ unsigned int am_smem[];  // [C][3] (+ [C][C])
+  const int C = a.C;
+  unsigned int *s_cnt = am_smem;
+  unsigned int *s_cm = am_smem + 3 * C;
+  const bool cm_smem = a.cm && C <= kAmMaxSmemClasses;
+  const long long px = (long long)a.H * a.W;
+  const long long n_chunks = a.n_img * a.chunks_per_img;
+  const long long per = (px + a.chunks_per_img - 1) / a.chunks_per_img;
+  const int S = a.src.n;
+
+  for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+    const long long img = chunk / a.chunks_per_img;
+    const long long p0 = (chunk - img * a.chunks_per_img) * per;
+    const long long p1 = min(px, p0 + per);
+    for (int i = threadIdx.x; i < 3 * C + (cm_smem ? C * C : 0);
+         i += blockDim.x)
+      am_smem[i] = 0;
+    __syncthreads();
+    for (long long p = p0 + threadIdx.x; p < p1; p += blockDim.x) {
+      const int y = (int)(p / a.W), x = (int)(p - (long long)y * a.W);
+      const long long pl0 = img * C;  // class-0 plane of this image
+      // soft-max: per source the running maximum over the classes and the
+      // sum of expf(x - max) in class order (torch's spatial soft-max)
+      float mk[MLC_MAX_SOURCES], zk[MLC_MAX_SOURCES];
+      if (a.act == MLC_ACT_SOFTMAX) {
+        for (int k = 0; k < S; ++k) {
+          float m = -3.402823466e+38f;
+          for (int j = 0; j < C; ++j) {
+            const float t = am_fetch<T>(a, k, pl0 + j, y, x);
+            m = m < t ? t : m;
+          }
+          float sum = 0.f;
+          for (int j = 0; j < C; ++j)
+            sum += expf(am_fetch<T>(a, k, pl0 + j, y, x) - m);
+          mk[k] = m;
+          zk[k] = sum;
+        }
+      }
+      // arg-max over the classes of mean_k act_k(c); numpy order
+      float best = 0.f;
+      int best_c = 0;
+      bool best_nan = false;
+      for (int c = 0; c < C; ++c) {
+        float v = 0.f;
+        for (int k = 0; k < S; ++k) {
+          const float t = am_fetch<T>(a, k, pl0 + c, y, x);
+          const float q = a.act == MLC_ACT_SOFTMAX ? expf(t - mk[k]) / zk[k]
+                                                   : activate(t, a.act);
+          v = k == 0 ? q : v + q;
+        }
+        float w[8] = {v, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        mean8(w, S);
+        v = w[0];
+        const bool is_nan = !(v == v);
+        if (c == 0 || (!best_nan && (is_nan || v > best))) {
+          best = v;
+          best_c = c;
+          best_nan = is_nan;
+        }
+      }
+      if (a.label) a.label[img * px + p] = (uint8_t)best_c;
+      if (a.onehot)
+        for (int c = 0; c < C; ++c)
+          a.onehot[(img * C + c) * px + p] = c == best_c ? 1 : 0;
+      if (a.counts) {
+        atomicAdd(&s_cnt[best_c * 3 + 1], 1u);  // P
+        if (a.gt_onehot) {
+          for (int c = 0; c < C; ++c) {
+            if (a.gt_onehot[(img * C + c) * px + p]) {
+              atomicAdd(&s_cnt[c * 3 + 0], 1u);  // T
+              if (c == best_c) atomicAdd(&s_cnt[c * 3 + 2], 1u);  // I
+            }
+          }
+        } else if (a.gt_label) {
+          const int g = a.gt_label[img * px + p];
+          if (g < C) {
+            atomicAdd(&s_cnt[g * 3 + 0], 1u);
+            if (g == best_c) atomicAdd(&s_cnt[g * 3 + 2], 1u);
+          }
+        }
+      }
+      if (a.cm && a.gt_label) {
+        const int g = a.gt_label[img * px + p];
+        if (g < C) {  // labels outside [0, C) are dropped (sklearn's rule)
+          if (cm_smem) atomicAdd(&s_cm[g * C + best_c], 1u);
+          else atomicAdd(&a.cm[(size_t)g * C + best_c], 1ull);
+        }
+      }
+    }
+    __syncthreads();
+    if (a.counts)
+      for (int i = threadIdx.x; i < 3 * C; i += blockDim.x)
+        if (s_cnt[i]) atomicAdd(&a.counts[img * 3 * C + i], (unsigned long long)s_cnt[i]);
+    if (cm_smem)
+      for (int i = threadIdx.x; i < C * C; i += blockDim.x)
+        if (s_cm[i]) atomicAdd(&a.cm[i], (unsigned long long)s_cm[i]);
+    __syncthreads();
+  }
+}
+
+}  // namespace mlc
+
+using namespace mlc;
+
+extern "C" int mlc_seg_argmax(const void *const *src_dev_ptrs,
+                              const int32_t *xform, int n_src, int dtype,
+                              int64_t n_img, int n_cls, int H, int W, int act,
+                              const uint8_t *gt_onehot_dev,
+                              const uint8_t *gt_label_dev, uint8_t *label_dev,
+                              uint8_t *onehot_dev, int64_t *counts_dev,
+                              int64_t *cm_dev, void *stream) {
+  MLC_REQUIRE(dtype == MLC_F16 || dtype == MLC_F32,
+              "dtype %d is not MLC_F16/MLC_F32", dtype);
+  MLC_REQUIRE(act == MLC_ACT_NONE || act == MLC_ACT_SIGMOID ||
+                  act == MLC_ACT_SOFTMAX,
+              "unknown activation code %d", act);
+  MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && n_cls <= 255 && H >= 1 && W >= 1,
+              "bad shape n_img=%lld n_cls=%d (max 255) H=%d W=%d",
+              (long long)n_img, n_cls, H, W);
+  MLC_REQUIRE((long long)H * W < (1ll << 31), "plane of %d x %d too large", H,
+              W);
+  MLC_REQUIRE(label_dev || onehot_dev || counts_dev || cm_dev,
+              "no output requested");
+  MLC_REQUIRE(!cm_dev || gt_label_dev,
+              "the pixel confusion matrix needs gt_label_dev");
+  MLC_REQUIRE(!(gt_onehot_dev && gt_label_dev),
+              "pass the truth as one-hot planes or as a label map, not both");
+  ArgmaxArgs a;
+  if (int rc = fill_srcset(a.src, src_dev_ptrs, xform, n_src,
+                           dtype == MLC_F16 ? 2 : 4, H, W))
+    return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (counts_dev)
+    MLC_CUDA(cudaMemsetAsync(counts_dev, 0, (size_t)n_img * n_cls * 3 * 8, st));
+  if (cm_dev)
+    MLC_CUDA(cudaMemsetAsync(cm_dev, 0, (size_t)n_cls * n_cls * 8, st));
+  if (n_img == 0) return MLC_OK;
+  a.gt_onehot = gt_onehot_dev;
+  a.gt_label = gt_label_dev;
+  a.label = label_dev;
+  a.onehot = onehot_dev;
+  a.counts = reinterpret_cast<unsigned long long *>(counts_dev);
+  a.cm = reinterpret_cast<unsigned long long *>(cm_dev);
+  a.n_img = n_img;
+  a.C = n_cls;
+  a.H = H;
+  a.W = W;
+  a.act = act;
+  // chunks of >= 16 Ki pixels, enough of them to fill the machine
+  const long long px = (long long)H * W;
+  long long chunks = 1;
+  const long long want = 8ll * sm_count();
+  if (n_img < want) chunks = min((want + n_img - 1) / n_img, (px + 16383) / 16384);
+  // a chunk's 32-bit shared counters must not overflow
+  chunks = max(chunks, (px + (1ll << 30) - 1) >> 30);
+  a.chunks_per_img = (int)max(1ll, chunks);
+  const size_t smem =
+      (size_t)(3 * n_cls + (cm_dev && n_cls <= kAmMaxSmemClasses
+                                ? n_cls * n_cls : 0)) * 4;
+  const long long n_chunks = n_img * a.chunks_per_img;
+  const int grid = (int)min(n_chunks, 16ll * sm_count());
+  if (dtype == MLC_F16)
+    seg_argmax_kernel<__half><<<grid, kAmThreads, smem, st>>>(a);
+  else
+    seg_argmax_kernel<float><<<grid, kAmThreads, smem, st>>>(a);
+  MLC_LAUNCH_CHECK("seg_argmax_kernel");
+  return MLC_OK;
+}

@@ -69,8 +69,14 @@ __device__ __forceinline__ float rcp_approx(float y) {
 
 // Exact bin of one output pixel: what seg_hist_generic computes.
 __device__ __noinline__ uint32_t guarded_exact_bin(const HistArgs &a,
-                                                   size_t plane_off, int y,
-                                                   int x, const float *thr) {
+                                                   long long plane, int it,
+                                                   int i, bool rows,
+                                                   uint32_t thr_sa) {
+  const size_t plane_off = (size_t)plane * a.plane_px;
+  const int y = rows ? it / a.items_per_row : 0;
+  const int x = (it - y * (rows ? a.items_per_row : 0)) * 8 + i;
+  const float *thr = static_cast<const float *>(
+      __cvta_shared_to_generic((size_t)thr_sa));
   float p = 0.f;
   for (int k = 0; k < a.src.n; ++k) {
     const int xf = a.src.xf[k];
@@ -193,12 +199,14 @@ __device__ __forceinline__ void do_group(const HistArgs &a, int k0, int rmask,
 // From the sums of sigmoids of one item to its histogram updates (and bin
 // bytes): grid position moved down / up by the error bound, exact evaluation
 // of the pixels the two disagree on, one shared-memory atomic per pixel.
+// slot: shared address of this lane's column of counters (16 KiB aligned base
+// | lane * 4); the threshold table lies behind the counters.
 template <bool ROWS, bool BINS>
 __device__ __forceinline__ void finish_item(const HistArgs &a,
                                             const float (&q)[8], uint32_t dmax,
                                             uint2 g, uint32_t slot,
-                                            size_t plane_off, int it, int y,
-                                            int xi, const float *thr) {
+                                            long long plane, int it,
+                                            size_t bins_item) {
   const float kq = a.g_kq, fb_lo = a.g_fb_lo, fb_hi = a.g_fb_hi;
   uint32_t fx[8], differ = 0;
 #pragma unroll
@@ -215,11 +223,11 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const uint32_t hi = __float_as_uint(fmaf(q[i], kq, fb_hi));
-      if (all || ((fx[i] ^ hi) >> 16) != 0u) {
-        const int px = ROWS ? xi * 8 + i : it * 8 + i;
+      if (all || ((fx[i] ^ hi) >> 16) != 0u)
         fx[i] = 0x43008000u |
-                (guarded_exact_bin(a, plane_off, ROWS ? y : 0, px, thr) << 16);
-      }
+                (guarded_exact_bin(a, plane, it, i, ROWS,
+                                   (slot & ~16383u) + (a.B + 1) * 128u)
+                 << 16);
     }
   }
   // bin = bits 16..22 of fx (the exponent field reads 0x4300 + bin)
@@ -241,7 +249,7 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
                  0x5410u);
     v.y = prmt32(prmt32(fx[4], fx[5], 0x0062u), prmt32(fx[6], fx[7], 0x0062u),
                  0x5410u);
-    *reinterpret_cast<uint2 *>(a.bins + plane_off + (size_t)it * 8) = v;
+    reinterpret_cast<uint2 *>(a.bins)[bins_item] = v;
   }
 }
 
@@ -339,7 +347,8 @@ seg_hist_guarded(const __grid_constant__ HistArgs a) {
         }
       }
       finish_item<ROWS, BINS>(a, q, dmax, ldg_stream8(gtp + (size_t)it * 8),
-                              slot, plane_off, it, y, xi, thr);
+                              slot, plane, it,
+                              (size_t)plane * (size_t)(a.plane_px >> 3) + it);
       xi += dx;
       if (ROWS) {
         y += dy;
@@ -385,8 +394,98 @@ __device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
   return v;
 }
 
-template <int NS, bool ROWS, bool BINS>
-__global__ void __launch_bounds__(1024, 1)
+// One unit (a plane or a slice of it) of the cp.async-fed kernel.
+// REV >= 0: the reversal mask of the NS sources, known at compile time (the
+// flipped sources' pixels are picked by register naming); REV < 0: any mask,
+// flipped items are reversed with four PRMT each.
+// NT: threads per CTA (compile time: every shared-memory slot of a thread is
+// then a constant offset from its first one).
+template <int NS, int NT, bool ROWS, bool BINS, int REV>
+__device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
+                                        uint32_t sub, uint32_t slot,
+                                        uint32_t my_slot) {
+  // a thread's slots of one stage: NS x 16 B of logits at a stride of NT x 16,
+  // then 16 B holding the 8 truth bytes; the other stage kStage further on
+  constexpr uint32_t kStage = (NS + 1) * NT * 16u;
+  const int ipr = a.items_per_row;
+  // 32-bit item index from the start of the tensors (the host checked that
+  // all items fit): one IMAD.WIDE per source on top of the kernel argument
+  const uint32_t ipp = (uint32_t)a.items_per_plane;
+  const uint32_t p0 = plane * ipp;
+  const int i0 = (int)(sub * (uint32_t)a.items_per_unit);
+  const int i1 = (int)min(ipp, (uint32_t)i0 + (uint32_t)a.items_per_unit);
+  int it = i0 + (int)threadIdx.x;
+  // (yn, xn): row / item-in-row of the NEXT item to fetch
+  int yn = 0, xn = it;
+  if (ROWS) {
+    yn = it / ipr;
+    xn = it - yn * ipr;
+  }
+  // a step of NT items = g_dy rows + g_dx items (host: NT / ipr, NT % ipr)
+  auto issue = [&](int it_, uint32_t dst) {
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      const uint32_t idx =
+          p0 + (uint32_t)(a.g_b[j] + a.g_cy[j] * yn + a.g_cx[j] * xn);
+      cp_async16(dst + j * NT * 16u,
+                 static_cast<const uint4 *>(a.src.ptr[j]) + idx);
+    }
+    cp_async8(dst + NS * NT * 16u,
+              reinterpret_cast<const uint2 *>(a.gt) + (p0 + (uint32_t)it_));
+    xn += ROWS ? a.g_dx : NT;
+    if (ROWS) {
+      yn += a.g_dy;
+      if (xn >= ipr) {
+        xn -= ipr;
+        ++yn;
+      }
+    }
+  };
+  // current / next stage: cur + nxt is constant
+  uint32_t cur = my_slot;
+  const uint32_t both = 2u * my_slot + kStage;
+  if (it < i1) issue(it, cur);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  for (; it < i1; it += NT) {
+    if (it + NT < i1) issue(it + NT, both - cur);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    const uint32_t cur_src = cur;
+    float q[8];
+    uint32_t dmax = 0u;
+    uint32_t w[4][4];
+    // NS <= 8: a first group of up to four sources, then the rest
+    constexpr int kA = NS < 4 ? NS : 4, kB = NS - kA;
+#pragma unroll
+    for (int j = 0; j < kA; ++j) {
+      const uint4 r = lds_u4(cur_src + j * NT * 16u);
+      w[j][0] = r.x; w[j][1] = r.y; w[j][2] = r.z; w[j][3] = r.w;
+    }
+    if constexpr (REV >= 0)
+      group_sum<kA, REV & ((1 << kA) - 1)>(w, true, q, dmax);
+    else
+      do_group<kA, ROWS>(a, 0, a.g_rev & ((1 << kA) - 1), w, true, q, dmax);
+    if constexpr (kB > 0) {
+#pragma unroll
+      for (int j = 0; j < kB; ++j) {
+        const uint4 r = lds_u4(cur_src + (4 + j) * NT * 16u);
+        w[j][0] = r.x; w[j][1] = r.y; w[j][2] = r.z; w[j][3] = r.w;
+      }
+      if constexpr (REV >= 0)
+        group_sum<kB, (REV >> 4) & ((1 << kB) - 1)>(w, false, q, dmax);
+      else
+        do_group<kB, ROWS>(a, 4, (a.g_rev >> 4) & ((1 << kB) - 1), w, false, q,
+                           dmax);
+    }
+    finish_item<ROWS, BINS>(a, q, dmax, lds_u2(cur + NS * NT * 16u), slot,
+                            blockIdx.x, it, p0 + (uint32_t)it);
+    cur = both - cur;
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+template <int NS, int NT, bool ROWS, bool BINS>
+__global__ void __launch_bounds__(NT, 1024 / NT)
 seg_hist_guarded_pf(const __grid_constant__ HistArgs a) {
   extern __shared__ __align__(16) uint32_t gsm[];
   const int B = a.B, nbins = B + 1;
@@ -394,97 +493,40 @@ seg_hist_guarded_pf(const __grid_constant__ HistArgs a) {
   const uint32_t cnt_sa = (gsm_sa + 16383u) & ~16383u;
   uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
   float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
-  for (int i = threadIdx.x; i < nbins * 32; i += blockDim.x) cnt[i] = 0;
-  for (int i = threadIdx.x; i < B; i += blockDim.x) thr[i] = a.thr.v[i];
+  for (int i = threadIdx.x; i < nbins * 32; i += NT) cnt[i] = 0;
+  for (int i = threadIdx.x; i < B; i += NT) thr[i] = a.thr.v[i];
   __syncthreads();
   const uint32_t slot = cnt_sa | ((threadIdx.x & 31) * 4);
-  const uint32_t nt = blockDim.x;
-  // stages behind the threshold table: [2][NS][nt] x 16 B, then [2][nt] x 8 B
+  // two stages behind the threshold table, (NS + 1) x NT x 16 B each
   const uint32_t st_sa = (cnt_sa + nbins * 128 + B * 4 + 15u) & ~15u;
-  const uint32_t my_src = st_sa + threadIdx.x * 16u;
-  const uint32_t my_gt = st_sa + 2u * NS * nt * 16u + threadIdx.x * 8u;
-  const long long n_units = a.n_planes * a.units_per_plane;
-  const int ipr = a.items_per_row;
-
-  for (long long unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-    const long long plane = unit / a.units_per_plane;
-    const int sub = (int)(unit - plane * a.units_per_plane);
-    const size_t plane_off = (size_t)plane * a.plane_px;
-    const uint8_t *gtp = a.gt + plane_off;
-    const int i0 = (int)((long long)sub * a.items_per_unit);
-    const int i1 = (int)min(a.items_per_plane, (long long)i0 + a.items_per_unit);
-    int it = i0 + (int)threadIdx.x;
-    int y = 0, xi = it;
-    int dy = 0, dx = (int)nt;
-    if (ROWS) {
-      y = it / ipr;
-      xi = it - y * ipr;
-      dy = (int)nt / ipr;
-      dx = (int)nt - dy * ipr;
-    }
-    auto issue = [&](int it_, int y_, int xi_, uint32_t stage) {
-#pragma unroll
-      for (int j = 0; j < NS; ++j) {
-        const int idx = a.g_b[j] + a.g_cy[j] * y_ + a.g_cx[j] * xi_;
-        cp_async16(my_src + (stage * NS + j) * nt * 16u,
-                   static_cast<const __half *>(a.src.ptr[j]) + plane_off +
-                       (size_t)(uint32_t)idx * 8);
-      }
-      cp_async8(my_gt + stage * nt * 8u, gtp + (size_t)it_ * 8);
-    };
-    uint32_t stage = 0;
-    if (it < i1) issue(it, y, xi, 0u);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    for (; it < i1; it += nt) {
-      int y2 = y, xi2 = xi + dx;
-      if (ROWS) {
-        y2 += dy;
-        if (xi2 >= ipr) {
-          xi2 -= ipr;
-          ++y2;
-        }
-      }
-      if (it + (int)nt < i1) issue(it + (int)nt, y2, xi2, stage ^ 1u);
-      asm volatile("cp.async.commit_group;" ::: "memory");
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-      float q[8];
-      uint32_t dmax = 0u;
-      uint32_t w[4][4];
-#pragma unroll
-      for (int k0 = 0; k0 < NS; k0 += 4) {
-        constexpr int kFull = NS / 4 * 4;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (k0 + j < NS) {
-            const uint4 r = lds_u4(my_src + (stage * NS + k0 + j) * nt * 16u);
-            w[j][0] = r.x; w[j][1] = r.y; w[j][2] = r.z; w[j][3] = r.w;
-          }
-        if (k0 < kFull) {
-          do_group<4, ROWS>(a, k0, (a.g_rev >> k0) & 0xF, w, k0 == 0, q, dmax);
-        } else {
-          constexpr int kRest = NS % 4 ? NS % 4 : 1;
-          do_group<kRest, ROWS>(a, k0, (a.g_rev >> k0) & ((1 << kRest) - 1), w,
-                                k0 == 0, q, dmax);
-        }
-      }
-      finish_item<ROWS, BINS>(a, q, dmax, lds_u2(my_gt + stage * nt * 8u), slot,
-                              plane_off, it, y, xi, thr);
-      y = y2;
-      xi = xi2;
-      stage ^= 1u;
-    }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
-    flush_bins(cnt, nbins, out, a.units_per_plane > 1);
-  }
+  const uint32_t my_slot = st_sa + threadIdx.x * 16u;
+  constexpr int kAll = (1 << NS) - 1;
+  const int rev = ROWS ? (int)(a.g_rev & kAll) : 0;
+  // one CTA per unit, grid = (planes, slices of a plane): both indices are
+  // special registers, so everything derived from them stays in the uniform
+  // datapath (a division by units_per_plane would not)
+  const uint32_t upp = gridDim.y;
+  const uint32_t plane = blockIdx.x, sub = blockIdx.y;
+  if (rev == 0)
+    pf_unit<NS, NT, ROWS, BINS, 0>(a, plane, sub, slot, my_slot);
+  else if (rev == (0xA & kAll))
+    pf_unit<NS, NT, ROWS, BINS, 0xA & kAll>(a, plane, sub, slot, my_slot);
+  else if (rev == (0x5 & kAll))
+    pf_unit<NS, NT, ROWS, BINS, 0x5 & kAll>(a, plane, sub, slot, my_slot);
+  else if (rev == kAll)
+    pf_unit<NS, NT, ROWS, BINS, kAll>(a, plane, sub, slot, my_slot);
+  else
+    pf_unit<NS, NT, ROWS, BINS, -1>(a, plane, sub, slot, my_slot);
+  uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
+  flush_bins(cnt, nbins, out, upp > 1);
 }
 
-template <int NS>
+template <int NS, int NT>
 static void (*pick_guarded_pf(bool rows, bool bins))(HistArgs) {
-  return bins ? (rows ? seg_hist_guarded_pf<NS, true, true>
-                      : seg_hist_guarded_pf<NS, false, true>)
-              : (rows ? seg_hist_guarded_pf<NS, true, false>
-                      : seg_hist_guarded_pf<NS, false, false>);
+  return bins ? (rows ? seg_hist_guarded_pf<NS, NT, true, true>
+                      : seg_hist_guarded_pf<NS, NT, false, true>)
+              : (rows ? seg_hist_guarded_pf<NS, NT, true, false>
+                      : seg_hist_guarded_pf<NS, NT, false, false>);
 }
 
 template <int NS>
@@ -542,20 +584,26 @@ bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
   const bool bins = a.bins != nullptr;
   // cp.async-fed variant: two stages of S x 16 + 8 bytes per thread; two
   // 512-thread CTAs per SM when they fit the 227 KiB, else one of 1024
-  const size_t per_thread = 2 * ((size_t)S * 16 + 8);
+  const size_t per_thread = 2 * ((size_t)S + 1) * 16;
   const size_t sm_bytes = 227 * 1024;
   int pf_threads = 0;
 #ifndef MLC_G_NO_PF
-  if (S >= 2 && S <= 5) {
-    if (2 * (smem + 512 * per_thread + 1024) <= sm_bytes) pf_threads = 512;
-    else if (smem + 1024 * per_thread + 1024 <= sm_bytes) pf_threads = 1024;
+  // (its 32-bit item index must reach every item of the tensors)
+  if (S >= 2 && S <= 5 && a.n_planes * a.items_per_plane < (1ll << 32) &&
+      a.n_planes < (1ll << 31) && a.units_per_plane < 65536) {
+    if (S <= 4 && 2 * (smem + 512 * per_thread + 1024) <= sm_bytes)
+      pf_threads = 512;
+    else if (S == 5 && smem + 1024 * per_thread + 1024 <= sm_bytes)
+      pf_threads = 1024;
   }
 #endif
   if (pf_threads) {
-    void (*k)(HistArgs) = S == 2   ? pick_guarded_pf<2>(rows, bins)
-                          : S == 3 ? pick_guarded_pf<3>(rows, bins)
-                          : S == 4 ? pick_guarded_pf<4>(rows, bins)
-                                   : pick_guarded_pf<5>(rows, bins);
+    a.g_dy = rows ? pf_threads / ipr : 0;
+    a.g_dx = rows ? pf_threads % ipr : pf_threads;
+    void (*k)(HistArgs) = S == 2   ? pick_guarded_pf<2, 512>(rows, bins)
+                          : S == 3 ? pick_guarded_pf<3, 512>(rows, bins)
+                          : S == 4 ? pick_guarded_pf<4, 512>(rows, bins)
+                                   : pick_guarded_pf<5, 1024>(rows, bins);
     const size_t pf_smem = smem + pf_threads * per_thread;
     const cudaError_t ea = cudaFuncSetAttribute(
         k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pf_smem);
@@ -563,7 +611,8 @@ bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
       *rc = cuda_fail(ea, "cudaFuncSetAttribute(seg_hist_guarded_pf)");
       return true;
     }
-    k<<<grid, pf_threads, pf_smem, st>>>(a);
+    k<<<dim3((unsigned)a.n_planes, (unsigned)a.units_per_plane), pf_threads,
+        pf_smem, st>>>(a);
   } else {
     void (*k)(HistArgs) = S == 2   ? pick_guarded<2>(rows, bins)
                           : S == 3 ? pick_guarded<3>(rows, bins)

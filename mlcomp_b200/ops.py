@@ -20,7 +20,7 @@ __all__ = ['MLC_XF_HFLIP', 'MLC_XF_VFLIP', 'MLC_XF_TRANSPOSE',
            'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
            'threshold_grid', 'counts_from_hist', 'rle_strings',
            'rle_strings_host', 'rle_decode', 'rle_parse', 'mask_composite',
-           'rle_from_bins', 'plane_area',
+           'rle_from_bins', 'plane_area', 'seg_argmax',
            'mask_outline']
 
 
@@ -240,6 +240,46 @@ def seg_prob(sources, xforms=None, activation='sigmoid'):
         check(lib.mlc_seg_prob(ptrs, xf, len(sources), _dtype_code(sources[0]),
                                n, c, h, w, activation_code(activation),
                                _ptr(out), _stream()))
+    return out
+
+
+def seg_argmax(sources, xforms=None, activation='softmax', gt_onehot=None,
+               gt_label=None, want_label=True, want_onehot=False,
+               want_counts=False, want_confusion=False):
+    """Per-pixel arg-max over the classes of the fused scores
+    (mlc_seg_argmax): first maximal class, NaN maximal, ties -> lowest.
+    Returns a dict with the requested outputs: 'label' uint8 [n, H, W],
+    'onehot' uint8 [n, C, H, W], 'counts' int64 [n, C, 3] = {T, P, I} of the
+    one-hot masks, 'confusion' int64 [C, C] (rows = truth; needs gt_label)."""
+    lib = _lib.load()
+    sources, ptrs, xf, n, c, h, w = _sources(sources, xforms)
+    dev = sources[0].device
+    if c > 255:
+        raise ValueError('at most 255 classes')
+    if gt_onehot is not None:
+        _need_cuda(gt_onehot, 'gt_onehot', (torch.uint8,))
+        if tuple(gt_onehot.shape) != (n, c, h, w):
+            raise ValueError(f'gt_onehot must be {(n, c, h, w)} uint8')
+    if gt_label is not None:
+        _need_cuda(gt_label, 'gt_label', (torch.uint8,))
+        if tuple(gt_label.shape) != (n, h, w):
+            raise ValueError(f'gt_label must be {(n, h, w)} uint8')
+    out = {}
+    if want_label:
+        out['label'] = torch.empty((n, h, w), dtype=torch.uint8, device=dev)
+    if want_onehot:
+        out['onehot'] = torch.empty((n, c, h, w), dtype=torch.uint8,
+                                    device=dev)
+    if want_counts:
+        out['counts'] = torch.empty((n, c, 3), dtype=torch.int64, device=dev)
+    if want_confusion:
+        out['confusion'] = torch.empty((c, c), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.mlc_seg_argmax(
+            ptrs, xf, len(sources), _dtype_code(sources[0]), n, c, h, w,
+            activation_code(activation), _ptr(gt_onehot), _ptr(gt_label),
+            _ptr(out.get('label')), _ptr(out.get('onehot')),
+            _ptr(out.get('counts')), _ptr(out.get('confusion')), _stream()))
     return out
 
 

@@ -44,8 +44,10 @@ def combine_packed(packed, n_f64, group=None):
         return packed
     world = dist.get_world_size(group)
     n = packed.numel()
-    rows = torch.empty((world, n), dtype=torch.int64, device=packed.device)
-    dist.all_gather_into_tensor(rows, packed.contiguous(), group=group)
+    flat = torch.empty(world * n, dtype=torch.int64, device=packed.device)
+    dist.all_gather_into_tensor(flat, packed.contiguous().reshape(-1),
+                                group=group)
+    rows = flat.view(world, n)
     out = torch.empty_like(packed)
     if packed.is_cuda:
         from . import _lib

@@ -19,6 +19,7 @@ __all__ = [
     'fuse_probs', 'plane_counts', 'bin_counts', 'dice_from_counts',
     'dice_grid_slow', 'dice_grid_fast', 'grid_scores', 'best_point',
     'micro_stats', 'rle_submission', 'encode_pred', 'plot_mask', 'TTA_TAGS',
+    'seg_argmax', 'onehot_counts',
 ]
 
 TTA_TAGS = ('hflip', 'vflip', 'transpose')
@@ -195,6 +196,28 @@ def fuse_probs(sources, tags_per_source, activation='sigmoid') -> np.ndarray:
         p = p.detach().cpu().numpy().astype(np.float32)       # torch.py:29
         acc = p.copy() if acc is None else acc + p
     return acc / np.float32(len(sources))
+
+
+def seg_argmax(sources, tags_per_source, activation='softmax') -> np.ndarray:
+    """Arg-max masks of the multiclass path: apply_activation(x, 'softmax')
+    per source (utils/torch.py:16-17), TtaWrap.inverse, the mean over sources
+    (:func:`fuse_probs`), then numpy's arg-max over the class axis, the call
+    the reference makes at worker/reports/classification.py:111,136 (first
+    maximal index; a NaN counts as maximal).  int64 [N, H, W]."""
+    return np.argmax(fuse_probs(sources, tags_per_source, activation), axis=1)
+
+
+def onehot_counts(label, gt_onehot):
+    """{T, P, I} of dice.py:10-11,20 for the one-hot masks (label == c):
+    int64 [N, C, 3]."""
+    n, c = gt_onehot.shape[:2]
+    out = np.zeros((n, c, 3), np.int64)
+    for i in range(n):
+        for j in range(c):
+            m = label[i] == j
+            g = gt_onehot[i, j] != 0
+            out[i, j] = (g.sum(), m.sum(), (m & g).sum())
+    return out
 
 
 def bin_counts(gt, prob, thr):
