@@ -35,7 +35,7 @@ struct HistArgs {
   float g_kq, g_fb_lo, g_fb_hi;
   int g_b[MLC_MAX_SOURCES], g_cy[MLC_MAX_SOURCES], g_cx[MLC_MAX_SOURCES];
   uint32_t g_rev;  // bit k: source k holds its items reversed (h-flip)
-  int g_dy, g_dx;  // a step of one CTA's threads in rows / items of a row
+  uint32_t g_ipr_magic;  // floor(2^32 / items_per_row) + 1
 };
 
 __device__ __forceinline__ void flush_bins(uint32_t *cnt, int nbins,

@@ -394,6 +394,9 @@ __device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
   return v;
 }
 
+// next unassigned item of the CTA's unit (see pf_unit)
+__shared__ unsigned int s_next_item;
+
 // One unit (a plane or a slice of it) of the cp.async-fed kernel.
 // REV >= 0: the reversal mask of the NS sources, known at compile time (the
 // flipped sources' pixels are picked by register naming); REV < 0: any mask,
@@ -414,42 +417,43 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
   const uint32_t p0 = plane * ipp;
   const int i0 = (int)(sub * (uint32_t)a.items_per_unit);
   const int i1 = (int)min(ipp, (uint32_t)i0 + (uint32_t)a.items_per_unit);
-  int it = i0 + (int)threadIdx.x;
-  // (yn, xn): row / item-in-row of the NEXT item to fetch
-  int yn = 0, xn = it;
-  if (ROWS) {
-    yn = it / ipr;
-    xn = it - yn * ipr;
-  }
-  // a step of NT items = g_dy rows + g_dx items (host: NT / ipr, NT % ipr)
+  // Items are handed out to the warps 32 at a time from a counter in shared
+  // memory (ncu on the statically split version: 14 % of the warp samples sat
+  // at the barrier before the flush - the scheduler lets some warps run ahead
+  // and they then idle while the rest finish): a warp fetches its next 32
+  // items' data while it works on the current ones, and all warps finish
+  // within one round of each other.
+  const int lane = threadIdx.x & 31;
+  int it = i0 + (int)threadIdx.x;  // the first round is static
   auto issue = [&](int it_, uint32_t dst) {
+    int y_ = 0, x_ = it_;
+    if (ROWS) {  // exact for it_ * ipr < 2^32 (checked by the host)
+      y_ = (int)__umulhi((uint32_t)it_, a.g_ipr_magic);
+      x_ = it_ - y_ * ipr;
+    }
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
       const uint32_t idx =
-          p0 + (uint32_t)(a.g_b[j] + a.g_cy[j] * yn + a.g_cx[j] * xn);
+          p0 + (uint32_t)(a.g_b[j] + a.g_cy[j] * y_ + a.g_cx[j] * x_);
       cp_async16(dst + j * NT * 16u,
                  static_cast<const uint4 *>(a.src.ptr[j]) + idx);
     }
     cp_async8(dst + NS * NT * 16u,
               reinterpret_cast<const uint2 *>(a.gt) + (p0 + (uint32_t)it_));
-    xn += ROWS ? a.g_dx : NT;
-    if (ROWS) {
-      yn += a.g_dy;
-      if (xn >= ipr) {
-        xn -= ipr;
-        ++yn;
-      }
-    }
   };
-  // current / next stage: cur + nxt is constant
-  uint32_t cur = my_slot;
-  const uint32_t both = 2u * my_slot + kStage;
-  if (it < i1) issue(it, cur);
+  bool odd = false;  // which of the two stages holds the current item
+  if (it < i1) issue(it, my_slot);
   asm volatile("cp.async.commit_group;" ::: "memory");
-  for (; it < i1; it += NT) {
-    if (it + NT < i1) issue(it + NT, both - cur);
+  while (true) {
+    uint32_t nb = 0;
+    if (lane == 0) nb = atomicAdd(&s_next_item, 32u);
+    nb = __shfl_sync(0xffffffffu, nb, 0);
+    const int itn = (int)nb + lane;
+    if (itn < i1) issue(itn, odd ? my_slot : my_slot + kStage);
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 1;" ::: "memory");
+    if (it < i1) {
+    const uint32_t cur = odd ? my_slot + kStage : my_slot;
     const uint32_t cur_src = cur;
     float q[8];
     uint32_t dmax = 0u;
@@ -479,7 +483,10 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
     }
     finish_item<ROWS, BINS>(a, q, dmax, lds_u2(cur + NS * NT * 16u), slot,
                             blockIdx.x, it, p0 + (uint32_t)it);
-    cur = both - cur;
+    }
+    if ((int)nb >= i1) break;  // the same for all lanes of the warp
+    it = itn;
+    odd = !odd;
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
@@ -495,6 +502,8 @@ seg_hist_guarded_pf(const __grid_constant__ HistArgs a) {
   float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
   for (int i = threadIdx.x; i < nbins * 32; i += NT) cnt[i] = 0;
   for (int i = threadIdx.x; i < B; i += NT) thr[i] = a.thr.v[i];
+  if (threadIdx.x == 0)  // the first NT items of the unit are taken statically
+    s_next_item = blockIdx.y * (uint32_t)a.items_per_unit + NT;
   __syncthreads();
   const uint32_t slot = cnt_sa | ((threadIdx.x & 31) * 4);
   // two stages behind the threshold table, (NS + 1) x NT x 16 B each
@@ -597,9 +606,12 @@ bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
       pf_threads = 1024;
   }
 #endif
+  // y = item / ipr as __umulhi(item, magic): exact while item * ipr < 2^32
+  // (and ipr >= 2: the magic of 1 does not fit 32 bits)
+  if (rows && (ipr < 2 || a.items_per_plane * (long long)ipr >= (1ll << 32)))
+    pf_threads = 0;
   if (pf_threads) {
-    a.g_dy = rows ? pf_threads / ipr : 0;
-    a.g_dx = rows ? pf_threads % ipr : pf_threads;
+    a.g_ipr_magic = rows ? (uint32_t)((1ull << 32) / (unsigned)ipr + 1) : 0u;
     void (*k)(HistArgs) = S == 2   ? pick_guarded_pf<2, 512>(rows, bins)
                           : S == 3 ? pick_guarded_pf<3, 512>(rows, bins)
                           : S == 4 ? pick_guarded_pf<4, 512>(rows, bins)
