@@ -68,24 +68,39 @@ __device__ __forceinline__ float rcp_approx(float y) {
 }
 
 // Exact bin of one output pixel: what seg_hist_generic computes.
+// stage_sa != 0: the item's raw source words still lie in this thread's
+// shared-memory slots (source k at stage_sa + k * stage_stride, 16 bytes in
+// SOURCE order) - read them there instead of going back to global memory.
 __device__ __noinline__ uint32_t guarded_exact_bin(const HistArgs &a,
                                                    long long plane, int it,
                                                    int i, bool rows,
-                                                   uint32_t thr_sa) {
-  const size_t plane_off = (size_t)plane * a.plane_px;
-  const int y = rows ? it / a.items_per_row : 0;
-  const int x = (it - y * (rows ? a.items_per_row : 0)) * 8 + i;
+                                                   uint32_t thr_sa,
+                                                   uint32_t stage_sa,
+                                                   uint32_t stage_stride) {
   const float *thr = static_cast<const float *>(
       __cvta_shared_to_generic((size_t)thr_sa));
   float p = 0.f;
-  for (int k = 0; k < a.src.n; ++k) {
-    const int xf = a.src.xf[k];
-    const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
-    const int xs = (xf & MLC_XF_HFLIP) ? a.W - 1 - x : x;
-    const __half *pl = static_cast<const __half *>(a.src.ptr[k]) + plane_off;
-    const float v =
-        activate(__half2float(pl[(size_t)ys * a.W + xs]), MLC_ACT_SIGMOID);
-    p = k == 0 ? v : p + v;
+  if (stage_sa) {
+    for (int k = 0; k < a.src.n; ++k) {
+      const int e = (rows && ((a.g_rev >> k) & 1)) ? 7 - i : i;
+      const uint32_t h = lds_u16(stage_sa + k * stage_stride + e * 2);
+      const float v = activate(
+          __half2float(__ushort_as_half((unsigned short)h)), MLC_ACT_SIGMOID);
+      p = k == 0 ? v : p + v;
+    }
+  } else {
+    const size_t plane_off = (size_t)plane * a.plane_px;
+    const int y = rows ? it / a.items_per_row : 0;
+    const int x = (it - y * (rows ? a.items_per_row : 0)) * 8 + i;
+    for (int k = 0; k < a.src.n; ++k) {
+      const int xf = a.src.xf[k];
+      const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+      const int xs = (xf & MLC_XF_HFLIP) ? a.W - 1 - x : x;
+      const __half *pl = static_cast<const __half *>(a.src.ptr[k]) + plane_off;
+      const float v =
+          activate(__half2float(pl[(size_t)ys * a.W + xs]), MLC_ACT_SIGMOID);
+      p = k == 0 ? v : p + v;
+    }
   }
   float q[8] = {p, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   mean8(q, a.src.n);
@@ -206,7 +221,9 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
                                             const float (&q)[8], uint32_t dmax,
                                             uint2 g, uint32_t slot,
                                             long long plane, int it,
-                                            size_t bins_item) {
+                                            size_t bins_item,
+                                            uint32_t stage_sa = 0u,
+                                            uint32_t stage_stride = 0u) {
   const float kq = a.g_kq, fb_lo = a.g_fb_lo, fb_hi = a.g_fb_hi;
   uint32_t fx[8], differ = 0;
 #pragma unroll
@@ -226,7 +243,8 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
       if (all || ((fx[i] ^ hi) >> 16) != 0u)
         fx[i] = 0x43008000u |
                 (guarded_exact_bin(a, plane, it, i, ROWS,
-                                   (slot & ~16383u) + (a.B + 1) * 128u)
+                                   (slot & ~16383u) + (a.B + 1) * 128u,
+                                   stage_sa, stage_stride)
                  << 16);
     }
   }
@@ -482,7 +500,7 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
                            dmax);
     }
     finish_item<ROWS, BINS>(a, q, dmax, lds_u2(cur + NS * NT * 16u), slot,
-                            blockIdx.x, it, p0 + (uint32_t)it);
+                            blockIdx.x, it, p0 + (uint32_t)it, cur, NT * 16u);
     }
     if ((int)nb >= i1) break;  // the same for all lanes of the warp
     it = itn;
