@@ -405,6 +405,14 @@ __device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
                : "r"(addr));
   return v;
 }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
   uint2 v;
   asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y)
@@ -442,7 +450,8 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
   // items' data while it works on the current ones, and all warps finish
   // within one round of each other.
   const int lane = threadIdx.x & 31;
-  int it = i0 + (int)threadIdx.x;  // the first round is static
+  const uint32_t next_sa = (uint32_t)__cvta_generic_to_shared(&s_next_item);
+  const int it = i0 + (int)threadIdx.x;  // the first round is static
   auto issue = [&](int it_, uint32_t dst) {
     int y_ = 0, x_ = it_;
     if (ROWS) {  // exact for it_ * ipr < 2^32 (checked by the host)
@@ -459,19 +468,38 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
     cp_async8(dst + NS * NT * 16u,
               reinterpret_cast<const uint2 *>(a.gt) + (p0 + (uint32_t)it_));
   };
+  // The index of the item a stage holds travels with it (third word of the
+  // truth slot): nothing but the stage parity is carried around the loop in
+  // registers - the loop body needs all 64 of them, and a carried index was
+  // spilled and waited for at the end of every round.
+  constexpr uint32_t kIdxOff = NS * NT * 16u + 8u;
   bool odd = false;  // which of the two stages holds the current item
+  st_shared_u32(my_slot + kIdxOff, (uint32_t)it);
   if (it < i1) issue(it, my_slot);
   asm volatile("cp.async.commit_group;" ::: "memory");
   while (true) {
+    const uint32_t cur = odd ? my_slot + kStage : my_slot;
+    const int it = (int)lds_u32(cur + kIdxOff);
+    if (it - lane >= i1) break;  // the same for all lanes of the warp
+    // (inline PTX: atomicAdd() on a uniform address makes the compiler build
+    // its warp-aggregation sequence, ~20 instructions, around one lane)
     uint32_t nb = 0;
-    if (lane == 0) nb = atomicAdd(&s_next_item, 32u);
+    if (lane == 0)
+      asm volatile("atom.shared.add.u32 %0, [%1], 32;"
+                   : "=r"(nb)
+                   : "r"(next_sa)
+                   : "memory");
     nb = __shfl_sync(0xffffffffu, nb, 0);
-    const int itn = (int)nb + lane;
-    if (itn < i1) issue(itn, odd ? my_slot : my_slot + kStage);
+    {
+      const int itn = (int)nb + lane;
+      const uint32_t nxt = odd ? my_slot : my_slot + kStage;
+      st_shared_u32(nxt + kIdxOff, (uint32_t)itn);
+      if (itn < i1) issue(itn, nxt);
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 1;" ::: "memory");
+    odd = !odd;
     if (it < i1) {
-    const uint32_t cur = odd ? my_slot + kStage : my_slot;
     const uint32_t cur_src = cur;
     float q[8];
     uint32_t dmax = 0u;
@@ -502,9 +530,6 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
     finish_item<ROWS, BINS>(a, q, dmax, lds_u2(cur + NS * NT * 16u), slot,
                             blockIdx.x, it, p0 + (uint32_t)it, cur, NT * 16u);
     }
-    if ((int)nb >= i1) break;  // the same for all lanes of the warp
-    it = itn;
-    odd = !odd;
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
