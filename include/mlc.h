@@ -176,6 +176,20 @@ int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img, int n_cls,
                     int64_t *micro_dev, void *work_dev, size_t work_bytes,
                     void *stream);
 
+/* mlc_dice_search that also sums the intersection-over-union of the same
+ * masks: iou = I / (T + P - I + eps) per (plane, threshold, min-area), with
+ * the min-area rule (an emptied prediction has P = I = 0) and the empty rule
+ * (T = P = 0 -> 1 when empty_one) of dice.py:13-18 applied alike.  The
+ * reference has no IoU (contrib/metrics/dice.py:4-23 is dice only): this
+ * output is builder-defined and pinned only against this repo's oracle.
+ *   iou_sum_dev [n_cls][n_thr][n_area] fp64, overwritten
+ *   work_dev    at least 2 x mlc_dice_search_workspace(...) bytes */
+int mlc_dice_iou_search(const uint32_t *hist_dev, int64_t n_img, int n_cls,
+                        int n_thr, const int32_t *min_area_host, int n_area,
+                        int empty_one, double eps, double *dice_sum_dev,
+                        double *iou_sum_dev, int64_t *micro_dev,
+                        void *work_dev, size_t work_bytes, void *stream);
+
 /* mlc_dice_search without a workspace argument, for callers that cannot
  * allocate device memory: a scoring loop sharing the GPU with an inference
  * engine that reserved the whole card at start-up, or a thin ctypes binding

@@ -48,6 +48,10 @@ SIGNATURES = {
                                 POINTER(c_int32), c_int, c_int, c_double,
                                 c_void_p, c_void_p, c_void_p, c_size_t,
                                 c_void_p]),
+    'mlc_dice_iou_search': (c_int, [c_void_p, c_int64, c_int, c_int,
+                                    POINTER(c_int32), c_int, c_int, c_double,
+                                    c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_size_t, c_void_p]),
     'mlc_dice_search_static': (c_int, [c_void_p, c_int64, c_int, c_int,
                                        POINTER(c_int32), c_int, c_int, c_double,
                                        c_void_p, c_void_p, c_void_p]),

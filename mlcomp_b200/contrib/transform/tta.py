@@ -8,12 +8,27 @@ _BY_CLASS = {'HorizontalFlip': 'hflip', 'VerticalFlip': 'vflip',
 
 
 def parse_albu_short(config, always_apply=False):
-    """utils/config.py:93-104 reduced to the tag vocabulary."""
+    """utils/config.py:93-104 reduced to the tag vocabulary: the short string
+    form returns the tag itself; the dict form (``{'name':
+    'HorizontalFlip', ...}``, which the reference hands to ``parse_albu``,
+    :77-90) is accepted for the three transforms TtaWrap can invert
+    (tta.py:22-29) and for a ``Compose`` of them (-> list of tags).  Any other
+    albumentations class cannot be built here (albumentations is not a
+    dependency of this package) and raises."""
     if isinstance(config, str):
         if config in ('hflip', 'vflip', 'transpose'):
             return config
         raise Exception(f'Unknwon augmentation {config}')
-    raise AssertionError('only the short string form is supported here')
+    assert type(config) == dict
+    assert 'name' in config, f'name is required in {config}'
+    name = config['name']
+    if name == 'Compose':
+        return [parse_albu_short(c, always_apply)
+                for c in config.get('items', [])]
+    if name in _BY_CLASS:
+        return _BY_CLASS[name]
+    raise Exception(f'augmentation {name} has no test-time inverse '
+                    '(TtaWrap undoes HorizontalFlip, VerticalFlip, Transpose)')
 
 
 class TtaWrap:

@@ -44,6 +44,7 @@ __device__ __forceinline__ unsigned long long block_suffix_sum(
 struct SearchArgs {
   const uint32_t *hist;
   double *partial;               // [n_chunks][C][B][A]
+  double *partial_iou;           // same shape, or null
   unsigned long long *micro;     // [C][1+2B] or null
   AreaTable areas;               // [C][A]
   long long n_img;
@@ -63,9 +64,9 @@ dice_search_kernel(const __grid_constant__ SearchArgs a) {
   const int nb = a.B + 1;
   const long long n0 = (long long)chunk * a.imgs_per_chunk;
   const long long n1 = min(a.n_img, n0 + a.imgs_per_chunk);
-  double acc[MLC_MAX_AREAS];
+  double acc[MLC_MAX_AREAS], acc_iou[MLC_MAX_AREAS];
 #pragma unroll
-  for (int m = 0; m < MLC_MAX_AREAS; ++m) acc[m] = 0.0;
+  for (int m = 0; m < MLC_MAX_AREAS; ++m) acc[m] = acc_iou[m] = 0.0;
   unsigned long long sumP = 0, sumI = 0, sumT = 0;
   int area[MLC_MAX_AREAS];
 #pragma unroll
@@ -106,6 +107,20 @@ dice_search_kernel(const __grid_constant__ SearchArgs a) {
       for (int m = 0; m < MLC_MAX_AREAS; ++m)
         if (m < a.A)
           acc[m] += (area[m] > 0 && p < (unsigned)area[m]) ? d_zero : d_full;
+      if (a.partial_iou) {
+        // IoU of the same masks under the same two rules: I / (T + P - I +
+        // eps); an emptied prediction has I = P = 0 (builder-defined: the
+        // reference has no IoU)
+        const double u_full =
+            (a.empty_one && t == 0 && p == 0)
+                ? 1.0
+                : (double)i / ((double)((unsigned long long)t + p - i) + a.eps);
+#pragma unroll
+        for (int m = 0; m < MLC_MAX_AREAS; ++m)
+          if (m < a.A)
+            acc_iou[m] +=
+                (area[m] > 0 && p < (unsigned)area[m]) ? d_zero : u_full;
+      }
       sumP += p;
       sumI += i;
       if (j == 0) sumT += t;
@@ -118,6 +133,13 @@ dice_search_kernel(const __grid_constant__ SearchArgs a) {
 #pragma unroll
     for (int m = 0; m < MLC_MAX_AREAS; ++m)
       if (m < a.A) out[m] = acc[m];
+    if (a.partial_iou) {
+      double *o2 = a.partial_iou +
+                   (((size_t)chunk * a.C + c) * a.B + j) * a.A;
+#pragma unroll
+      for (int m = 0; m < MLC_MAX_AREAS; ++m)
+        if (m < a.A) o2[m] = acc_iou[m];
+    }
     if (a.micro) {
       unsigned long long *mo = a.micro + (size_t)c * (1 + 2 * a.B);
       if (j == 0 && sumT) atomicAdd(mo, sumT);
@@ -202,12 +224,12 @@ extern "C" size_t mlc_dice_search_workspace(int64_t n_img, int n_cls, int n_thr,
          sizeof(double);
 }
 
-extern "C" int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img,
-                               int n_cls, int n_thr,
-                               const int32_t *min_area_host, int n_area,
-                               int empty_one, double eps, double *dice_sum_dev,
-                               int64_t *micro_dev, void *work_dev,
-                               size_t work_bytes, void *stream) {
+static int dice_search_impl(const uint32_t *hist_dev, int64_t n_img,
+                            int n_cls, int n_thr,
+                            const int32_t *min_area_host, int n_area,
+                            int empty_one, double eps, double *dice_sum_dev,
+                            double *iou_sum_dev, int64_t *micro_dev,
+                            void *work_dev, size_t work_bytes, void *stream) {
   MLC_REQUIRE(hist_dev && dice_sum_dev && min_area_host,
               "hist/dice_sum/min_area pointer is null");
   MLC_REQUIRE(n_img >= 0 && n_cls >= 1 && n_cls <= MLC_MAX_CLASSES_SEG,
@@ -217,7 +239,8 @@ extern "C" int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img,
               n_thr, MLC_MAX_THR);
   MLC_REQUIRE(n_area >= 1 && n_area <= MLC_MAX_AREAS,
               "n_area=%d outside [1, %d]", n_area, MLC_MAX_AREAS);
-  const size_t need = mlc_dice_search_workspace(n_img, n_cls, n_thr, n_area);
+  const size_t one = mlc_dice_search_workspace(n_img, n_cls, n_thr, n_area);
+  const size_t need = iou_sum_dev ? 2 * one : one;
   if (!work_dev || work_bytes < need) {
     set_error("workspace of %zu bytes needed, %zu given", need, work_bytes);
     return MLC_ERR_CAPACITY;
@@ -229,11 +252,17 @@ extern "C" int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img,
                              (size_t)n_cls * (1 + 2 * n_thr) * 8, st));
   if (n_img == 0) {
     MLC_CUDA(cudaMemsetAsync(dice_sum_dev, 0, (size_t)cells * 8, st));
+    if (iou_sum_dev)
+      MLC_CUDA(cudaMemsetAsync(iou_sum_dev, 0, (size_t)cells * 8, st));
     return MLC_OK;
   }
   SearchArgs a;
   a.hist = hist_dev;
   a.partial = static_cast<double *>(work_dev);
+  a.partial_iou = iou_sum_dev
+                      ? reinterpret_cast<double *>(
+                            static_cast<char *>(work_dev) + one)
+                      : nullptr;
   a.micro = reinterpret_cast<unsigned long long *>(micro_dev);
   for (int i = 0; i < n_cls * n_area; ++i) {
     MLC_REQUIRE(min_area_host[i] >= 0, "min_area[%d] is negative", i);
@@ -253,7 +282,36 @@ extern "C" int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img,
   dice_reduce_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, st>>>(
       a.partial, dice_sum_dev, n_chunks, cells);
   MLC_LAUNCH_CHECK("dice_reduce_kernel");
+  if (iou_sum_dev) {
+    dice_reduce_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, st>>>(
+        a.partial_iou, iou_sum_dev, n_chunks, cells);
+    MLC_LAUNCH_CHECK("dice_reduce_kernel");
+  }
   return MLC_OK;
+}
+
+extern "C" int mlc_dice_search(const uint32_t *hist_dev, int64_t n_img,
+                               int n_cls, int n_thr,
+                               const int32_t *min_area_host, int n_area,
+                               int empty_one, double eps, double *dice_sum_dev,
+                               int64_t *micro_dev, void *work_dev,
+                               size_t work_bytes, void *stream) {
+  return dice_search_impl(hist_dev, n_img, n_cls, n_thr, min_area_host, n_area,
+                          empty_one, eps, dice_sum_dev, nullptr, micro_dev,
+                          work_dev, work_bytes, stream);
+}
+
+extern "C" int mlc_dice_iou_search(const uint32_t *hist_dev, int64_t n_img,
+                                   int n_cls, int n_thr,
+                                   const int32_t *min_area_host, int n_area,
+                                   int empty_one, double eps,
+                                   double *dice_sum_dev, double *iou_sum_dev,
+                                   int64_t *micro_dev, void *work_dev,
+                                   size_t work_bytes, void *stream) {
+  MLC_REQUIRE(iou_sum_dev, "iou_sum_dev is null");
+  return dice_search_impl(hist_dev, n_img, n_cls, n_thr, min_area_host, n_area,
+                          empty_one, eps, dice_sum_dev, iou_sum_dev, micro_dev,
+                          work_dev, work_bytes, stream);
 }
 
 extern "C" int mlc_plane_dice(const uint32_t *hist_dev, int64_t n_img,

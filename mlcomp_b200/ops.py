@@ -17,7 +17,7 @@ from ._lib import (MLC_ACT_NONE, MLC_ACT_SIGMOID, MLC_F16, MLC_F32, MLC_U8,
 
 __all__ = ['MLC_XF_HFLIP', 'MLC_XF_VFLIP', 'MLC_XF_TRANSPOSE',
            'activation_code', 'compose_tta', 'confusion', 'seg_lut',
-           'seg_hist', 'seg_prob', 'dice_search', 'plane_dice', 'rle_encode',
+           'seg_hist', 'seg_prob', 'dice_search', 'dice_iou_search', 'plane_dice', 'rle_encode',
            'threshold_grid', 'counts_from_hist', 'rle_strings',
            'rle_strings_host', 'rle_decode', 'rle_parse', 'mask_composite',
            'rle_from_bins', 'plane_area', 'seg_argmax',
@@ -291,6 +291,29 @@ def _areas(min_areas, n_cls):
         raise ValueError('min_areas must be [A] or [n_cls, A]')
     a = np.ascontiguousarray(a.astype(np.int32))
     return a, a.ctypes.data_as(ctypes.POINTER(c_int32))
+
+
+def dice_iou_search(hist, min_areas=(0,), empty_one=True, eps=1e-6):
+    """``dice_search`` plus the IoU sums of the same masks
+    (mlc_dice_iou_search): (dice_sum, iou_sum fp64 [C,B,A], micro)."""
+    lib = _lib.load()
+    hist = _need_cuda(hist, 'hist', (torch.int32,))
+    n, c, _, nb = hist.shape
+    b = nb - 1
+    areas, areas_p = _areas(min_areas, c)
+    a = areas.shape[1]
+    dev = hist.device
+    dice = torch.empty((c, b, a), dtype=torch.float64, device=dev)
+    iou = torch.empty((c, b, a), dtype=torch.float64, device=dev)
+    micro = torch.empty((c, 1 + 2 * b), dtype=torch.int64, device=dev)
+    need = 2 * lib.mlc_dice_search_workspace(n, c, b, a)
+    work = torch.empty(max(need, 8), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.mlc_dice_iou_search(
+            _ptr(hist), n, c, b, areas_p, a, int(bool(empty_one)), float(eps),
+            _ptr(dice), _ptr(iou), _ptr(micro), _ptr(work), work.numel(),
+            _stream()))
+    return dice, iou, micro
 
 
 def dice_search(hist, min_areas=(0,), empty_one=True, eps=1e-6,

@@ -204,7 +204,7 @@ class SegSearch:
 
     def __init__(self, n_cls, thr=None, min_areas=(0,), activation='sigmoid',
                  empty_one=True, eps=1e-6, device='cuda', use_lut=True,
-                 record_events=False):
+                 record_events=False, iou=False):
         self.n_cls = int(n_cls)
         self.thr = ops.threshold_grid(100) if thr is None else \
             np.asarray(thr, dtype=np.float32)
@@ -223,12 +223,16 @@ class SegSearch:
         # one buffer for everything that is exchanged / read back: the fp64
         # dice sums (as bit patterns), the int64 counts, the image count
         nd, nm = self.n_cls * b * a, self.n_cls * (1 + 2 * b)
-        self._nd = nd
-        self.packed = torch.zeros(nd + nm + 1, dtype=torch.int64,
+        self.iou = bool(iou)     # also the per-plane (macro) IoU of every cell
+        nf = nd * (2 if self.iou else 1)
+        self._nd, self._nf = nd, nf
+        self.packed = torch.zeros(nf + nm + 1, dtype=torch.int64,
                                   device=self.device)
         self.dice_sum = self.packed[:nd].view(torch.float64) \
             .view(self.n_cls, b, a)
-        self.micro = self.packed[nd:nd + nm].view(self.n_cls, 1 + 2 * b)
+        self.iou_sum = self.packed[nd:nf].view(torch.float64) \
+            .view(self.n_cls, b, a) if self.iou else None
+        self.micro = self.packed[nf:nf + nm].view(self.n_cls, 1 + 2 * b)
         self.n_img = 0
         self._fresh = False
         self._stage = None
@@ -263,7 +267,19 @@ class SegSearch:
         if self.record_events:
             ev[1].record()
             self.kernel_events.append(ev)
-        if self._fresh:     # first chunk of a pass: written in place
+        if self.iou:
+            dsum, usum, micro = ops.dice_iou_search(
+                hist, self.min_areas, self.empty_one, self.eps)
+            if self._fresh:
+                self.dice_sum.copy_(dsum)
+                self.iou_sum.copy_(usum)
+                self.micro.copy_(micro)
+                self._fresh = False
+            else:
+                self.dice_sum += dsum
+                self.iou_sum += usum
+                self.micro += micro
+        elif self._fresh:     # first chunk of a pass: written in place
             ops.dice_search(hist, self.min_areas, self.empty_one, self.eps,
                             out=self.dice_sum, micro=self.micro)
             self._fresh = False
@@ -332,12 +348,12 @@ class SegSearch:
         self.packed[-1:].fill_(self.n_img)
         # one collective + one kernel, then one device->host copy for
         # everything the host-side search needs
-        packed = combine_packed(self.packed, self._nd, group).cpu().numpy()
-        nd = self._nd
+        packed = combine_packed(self.packed, self._nf, group).cpu().numpy()
+        nd, nf = self._nd, self._nf
         n_img = int(packed[-1])
         score = packed[:nd].view(np.float64).reshape(self.dice_sum.shape) / \
             max(n_img, 1)                                     # [C, B, A]
-        m = packed[nd:-1].reshape(self.micro.shape)
+        m = packed[nf:-1].reshape(self.micro.shape)
         b = len(self.thr)
         t_sum, p_sum, i_sum = m[:, 0], m[:, 1:1 + b], m[:, 1 + b:]
         best = []
@@ -348,7 +364,18 @@ class SegSearch:
                          'min_area': int(self.min_areas[c, a]),
                          'dice': float(score[c, k, a])})
         union = t_sum[:, None] + p_sum
+        extra = {}
+        if self.iou:
+            # mean over images of the per-plane IoU at every (t, a): not in
+            # the reference (builder-defined, see oracle.iou_from_counts)
+            extra['iou_score'] = packed[nd:nf].view(np.float64) \
+                .reshape(self.dice_sum.shape) / max(n_img, 1)
+            extra['iou'] = float(np.mean([
+                extra['iou_score'][r['class'], r['threshold_index'],
+                                   list(self.min_areas[r['class']])
+                                   .index(r['min_area'])] for r in best]))
         return {
+            **extra,
             'n_img': int(n_img),
             'score': score,
             'best': best,

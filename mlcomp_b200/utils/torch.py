@@ -25,11 +25,49 @@ class LogitSource:
         return self.tensor.shape[0]
 
     def __getitem__(self, sl):
+        if isinstance(sl, int):
+            return self._host()[sl]
         return LogitSource(self.tensor[sl], self.tags, self.activation)
 
     def prob(self):
         """Materialise what the reference's ``_infer`` returns."""
         return fuse([self])
+
+    # -- array protocol: user code written against the reference receives
+    # ``preds`` as the NumPy array ``infer`` returned (utils/torch.py:29) and
+    # calls ``preds.argmax(axis=1)``, iterates over rows, ``np.array(...)``s
+    # them (examples/digit-recognizer/executors/valid.py:45-76,
+    # infer.py:62-74).  The same calls work on a LogitSource; the arg-max is
+    # taken on the device (mlc_confusion), everything else materialises the
+    # probabilities once.
+    @property
+    def shape(self):
+        return tuple(self.tensor.shape)
+
+    def _host(self):
+        if getattr(self, '_np', None) is None:
+            object.__setattr__(self, '_np', self.prob().cpu().numpy())
+        return self._np
+
+    def __array__(self, dtype=None, copy=None):
+        a = self._host()
+        return a.astype(dtype) if dtype is not None else a
+
+    def __iter__(self):
+        return iter(self._host())
+
+    def argmax(self, axis=None):
+        import numpy as np
+        if self.tensor.dim() == 2 and axis in (1, -1):
+            p = self.prob() if self.activation else self.tensor
+            p = p.contiguous()
+            if p.dtype not in (torch.float16, torch.float32):
+                p = p.float()
+            dummy = torch.zeros(p.shape[0], dtype=torch.int64,
+                                device=p.device)
+            am = ops.confusion(p, dummy, want_argmax=True)[2]
+            return am.cpu().numpy().astype(np.int64)
+        return np.argmax(self._host(), axis=axis)
 
 
 def fuse(sources):

@@ -121,7 +121,7 @@ class ValidSegment(_SegInputs, Valid):
     def __init__(self, logits=None, tta=None, targets=None, imgs=None,
                  bins=100, min_areas=(0,), activation='sigmoid',
                  report_threshold=0.5, colors=None, targets_rle=None,
-                 **kwargs):
+                 argmax=False, **kwargs):
         kwargs.setdefault('layout', 'img_segment')
         super().__init__(**kwargs)
         self._init_inputs(logits, tta, activation)
@@ -139,6 +139,12 @@ class ValidSegment(_SegInputs, Valid):
                                             np.float32(report_threshold)))
         self.report_k = min(self.report_k, len(self.thr) - 1)
         self.colors = colors
+        # argmax=True: the multiclass deployment - per pixel the first maximal
+        # class of the fused scores (activation 'softmax' as a rule); the
+        # masks are (label == c), there is no threshold to search, the score
+        # is the mean over images and classes of their dice (empty_one rule)
+        self.argmax = bool(argmax)
+        self._dice_rows = []
         self.search = None
         self.builder = None
         self.scores = []
@@ -165,9 +171,31 @@ class ValidSegment(_SegInputs, Valid):
                 name=self.name, plot_count=self.plot_count,
                 colors=self.colors)
 
+    def _score_argmax(self, tensors, tags, act, gt):
+        out = ops.seg_argmax(tensors, tags, act, gt_onehot=gt,
+                             want_label=False, want_counts=True,
+                             want_onehot=self.prepare_submit)
+        counts = out['counts'].cpu().numpy()             # [n, C, 3] T, P, I
+        self.d2h_bytes += counts.nbytes
+        t, p, i = (counts[..., k].astype(np.float64) for k in range(3))
+        dice = np.where((t == 0) & (p == 0), 1.0, 2 * i / (t + p + 1e-6))
+        self._dice_rows.append(dice)                     # dice.py:17-23
+        if self.prepare_submit:
+            self._kept.append((self.part[0], out['onehot']))
+        self._release_part()
+        res = dice.mean(axis=1)
+        self.scores.extend(res.tolist())
+        return res
+
     def score(self, preds):
         tensors, tags, act = self._as_sources(preds)
         n_cls = tensors[0].shape[1]
+        if self.argmax:
+            lo, hi = self.part
+            extra = getattr(self, '_staged_extra', None)
+            gt = extra[0] if extra else self._targets(lo, hi, tensors[0],
+                                                      tags[0])
+            return self._score_argmax(tensors, tags, act, gt)
         if self.search is None:
             self.search = scoring.SegSearch(n_cls, self.thr, self.min_areas,
                                             activation=act)
@@ -207,6 +235,21 @@ class ValidSegment(_SegInputs, Valid):
                               h, w).view(hi - lo, c, h, w)
 
     def score_final(self):
+        if self.argmax:
+            dice = np.concatenate(self._dice_rows)           # [N, C]
+            per_class = dice.mean(axis=0)
+            self.best = [{'class': c, 'threshold': None, 'min_area': 0,
+                          'threshold_index': None, 'dice': float(d)}
+                         for c, d in enumerate(per_class)]
+            if self.prepare_submit:
+                for lo, onehot in self._kept:
+                    runs, off, cnt, _ = ops.rle_encode([onehot], 0.5, 0,
+                                                       activation=None)
+                    self._rows_from(lo, onehot.shape[0], onehot.shape[1],
+                                    ops.rle_strings(runs, off, cnt))
+                self._kept = []
+                self._write_rows()
+            return float(per_class.mean())
         out = self.search.result()
         self.best = out['best']
         self.d2h_bytes += out['score'].nbytes + 8 * (
@@ -224,14 +267,19 @@ class ValidSegment(_SegInputs, Valid):
         for lo, hist, bins in self._kept:
             runs, off, cnt, _ = ops.rle_from_bins(bins, k_c, a_c, hist=hist)
             strings = ops.rle_strings(runs, off, cnt)
-            self.d2h_bytes += sum(len(t) for t in strings) + 12 * len(strings)
-            n, c = hist.shape[:2]
-            for i in range(n):
-                name = self.names[lo + i] if self.names is not None else lo + i
-                for j in range(c):
-                    self.rows.append({self.id_column: f'{name}_{j + 1}',
-                                      self.rle_column: strings[i * c + j]})
+            self._rows_from(lo, hist.shape[0], hist.shape[1], strings)
         self._kept = []
+        self._write_rows()
+
+    def _rows_from(self, lo, n, c, strings):
+        self.d2h_bytes += sum(len(t) for t in strings) + 12 * len(strings)
+        for i in range(n):
+            name = self.names[lo + i] if self.names is not None else lo + i
+            for j in range(c):
+                self.rows.append({self.id_column: f'{name}_{j + 1}',
+                                  self.rle_column: strings[i * c + j]})
+
+    def _write_rows(self):
         folder = getattr(self, 'submit_folder', None)
         if folder:
             import pandas as pd
@@ -262,6 +310,8 @@ class ValidSegment(_SegInputs, Valid):
             self.builder.process_scores({'dice': score})
 
     def result_extra(self):
+        if self.argmax:
+            return {'dice_per_class': [b['dice'] for b in self.best]}
         return {'thresholds': [b['threshold'] for b in self.best],
                 'min_areas': [b['min_area'] for b in self.best],
                 'dice_per_class': [b['dice'] for b in self.best]}

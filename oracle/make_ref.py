@@ -25,13 +25,21 @@ FILES = {
     'rle.py': 'mlcomp/contrib/transform/rle.py',        # mask2rle, rle2mask
     'tensors.py': 'mlcomp/contrib/torch/tensors.py',    # flip
 }
+# the reference's only in-tree users of the Valid / Infer bases: run as they
+# are by tests/test_reference_examples.py on the bases of this package
+EXAMPLES = {
+    'examples/valid.py': 'examples/digit-recognizer/executors/valid.py',
+    'examples/infer.py': 'examples/digit-recognizer/executors/infer.py',
+    'examples/dataset.py': 'examples/digit-recognizer/dataset.py',
+}
 
 
 def make():
     """Copy the files; returns True when oracle/_ref is complete."""
     if os.path.isdir(REF_ROOT):
         os.makedirs(DEST, exist_ok=True)
-        for name, rel in FILES.items():
+        os.makedirs(os.path.join(DEST, 'examples'), exist_ok=True)
+        for name, rel in list(FILES.items()) + list(EXAMPLES.items()):
             shutil.copyfile(os.path.join(REF_ROOT, rel),
                             os.path.join(DEST, name))
     return all(os.path.exists(os.path.join(DEST, n)) for n in FILES)

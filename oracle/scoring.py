@@ -19,7 +19,7 @@ __all__ = [
     'fuse_probs', 'plane_counts', 'bin_counts', 'dice_from_counts',
     'dice_grid_slow', 'dice_grid_fast', 'grid_scores', 'best_point',
     'micro_stats', 'rle_submission', 'encode_pred', 'plot_mask', 'TTA_TAGS',
-    'seg_argmax', 'onehot_counts',
+    'seg_argmax', 'onehot_counts', 'iou_from_counts',
 ]
 
 TTA_TAGS = ('hflip', 'vflip', 'transpose')
@@ -254,6 +254,26 @@ def dice_from_counts(t, p, i, min_area=None, empty_one=True, eps=1e-6):
         p = np.where(small, 0, p)
         i = np.where(small, 0, i)
     d = 2.0 * i / (np.float64(t) + p + eps)
+    if empty_one and t == 0:
+        d = np.where(p == 0, 1.0, d)
+    return d
+
+
+def iou_from_counts(t, p, i, min_area=None, empty_one=True, eps=1e-6):
+    """BUILDER-DEFINED, UNPINNED: the reference has no IoU
+    (contrib/metrics/dice.py:4-23 is dice only).  Same masks
+    and the same two rules as :func:`dice_from_counts` - the min-area rule
+    empties the prediction (dice.py:13-15), empty truth and prediction score 1
+    (dice.py:17-18) - with I / (T + P - I + eps) in place of 2I / (T + P +
+    eps).  Self-consistent only: it checks the kernel against this formula,
+    not against the reference."""
+    p = np.asarray(p, dtype=np.int64)
+    i = np.asarray(i, dtype=np.int64)
+    if min_area:
+        small = p < min_area
+        p = np.where(small, 0, p)
+        i = np.where(small, 0, i)
+    d = i / (np.float64(t) + p - i + eps)
     if empty_one and t == 0:
         d = np.where(p == 0, 1.0, d)
     return d

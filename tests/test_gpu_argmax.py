@@ -125,3 +125,58 @@ def test_argmax_severstal_shape_rle_and_dice(ops):
             t, p, ii = counts[i, j]
             assert oracle.dice_from_counts(t, p, ii) == \
                 oracle.plane_dice(g, m.astype(np.float32), threshold=0.5)
+
+
+def test_iou_sums_match_oracle_formula(ops):
+    """mlc_dice_iou_search: dice sums unchanged, IoU sums = the oracle's
+    (builder-defined, unpinned) formula on the same integer counts."""
+    from test_gpu_parity import synth_seg
+    n, c, h, w = 7, 3, 48, 64
+    srcs, gt = synth_seg(n, c, h, w, seed=12, empty=0.4)
+    thr = oracle.threshold_grid(100)
+    areas = [0, 10, 200, 5000]
+    hist = ops.seg_hist([srcs[0].to(DEV)], gt.to(DEV), thr)
+    d0, m0 = ops.dice_search(hist, areas)
+    d1, u1, m1 = ops.dice_iou_search(hist, areas)
+    assert torch.equal(d0, d1) and torch.equal(m0, m1)
+    prob = ops.seg_prob([srcs[0].to(DEV)]).cpu().numpy()
+    want = np.zeros((c, len(thr), len(areas)))
+    for i in range(n):
+        for j in range(c):
+            t, p, ii = oracle.plane_counts(gt[i, j].numpy(), prob[i, j], thr)
+            for m, a in enumerate(areas):
+                want[j, :, m] += oracle.iou_from_counts(t, p, ii, a)
+    np.testing.assert_allclose(u1.cpu().numpy(), want, rtol=1e-12, atol=0)
+
+
+def test_valid_segment_argmax_executor(ops, tmp_path):
+    """``type: valid_segment`` with activation 'softmax' and argmax: score =
+    mean dice of the one-hot arg-max masks; csv = their run-length strings."""
+    from mlcomp_b200.worker import store
+    from mlcomp_b200.worker.executors import Executor
+    n, c, h, w = 5, 3, 32, 48
+    tags = [[], ['hflip']]
+    seen, gt_label = make(n, c, h, w, 2, 99, torch.float32, tags)
+    g1 = np.stack([(gt_label.numpy() == j) for j in range(c)], axis=1) \
+        .astype(np.uint8)
+    cfg = {'executors': {'valid': {
+        'type': 'valid_segment', 'logits': [s.numpy() for s in seen],
+        'tta': tags, 'targets': g1, 'activation': 'softmax', 'argmax': True,
+        'part_size': 2, 'prepare_submit': True}}}
+    ex = Executor.from_config(executor='valid', config=cfg,
+                              additional_info={})
+    out = ex(task=store.Task(name='t'), task_provider=None,
+             dag=store.Dag(name='d'))
+    label = ops.seg_argmax([s.to(DEV) for s in seen], tags, 'softmax')[
+        'label'].cpu().numpy()
+    dice = np.zeros((n, c))
+    for i in range(n):
+        for j in range(c):
+            m = (label[i] == j).astype(np.float32)
+            dice[i, j] = oracle.plane_dice(g1[i, j].astype(np.float32), m,
+                                           threshold=0.5)
+            assert ex.rows[i * c + j]['EncodedPixels'] == \
+                oracle.rle_encode(m.astype(np.uint8))
+    assert abs(out['res'] - dice.mean()) < 1e-12
+    np.testing.assert_allclose(out['dice_per_class'], dice.mean(axis=0),
+                               rtol=1e-12)
