@@ -540,6 +540,39 @@ def run_ours(args, cfg):
     del out
 
     side = {}
+    # ---- strong scaling: the SAME 6,666-image set split over the ranks -----
+    if world > 1:
+        lo, hi = scoring.shard_range(n_img, rank, world)
+        m = hi - lo
+        part = [s_[:m] for s_ in srcs]
+        gpart = gt[:m]
+
+        def strong_step():
+            search.reset()
+            h_, b_ = search.add(part, gpart, xforms=TAGS, keep_bins=True)
+            r_ = search.result()
+            return ops.rle_from_bins(
+                b_, [b['threshold_index'] for b in r_['best']],
+                [b['min_area'] for b in r_['best']], capacity=cap, hist=h_)
+        for _ in range(3):
+            strong_step()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            strong_step()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64,
+                         device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_s = float(t.item()) / args.steps
+        side['strong_scaling'] = {
+            'workload': 'the %d-image set split over %d ranks '
+                        '(scoring.shard_range), whole pipeline + exchange' %
+                        (n_img, world),
+            'images_per_rank': m, 'ms_per_step': ms_s,
+            'value': planes / (ms_s * 1e-3), 'unit': UNIT,
+            'speedup_vs_one_gpu_step': (ms / args.steps) / ms_s}
     # ---- side: the pass without bins, RLE re-reading the sources -----------
     if not args.no_side:
         def step_reread():

@@ -871,6 +871,14 @@ static int rle_encode_impl(const void *const *src_dev_ptrs,
   a.W = W;
   a.Hw = (H + 31) / 32;
   a.act = act;
+#ifdef MLC_BOUNDS_CHECK
+  {
+    BoundsList bl;
+    for (int k = 0; k < n_src; ++k)
+      bl.add(src_dev_ptrs[k], (size_t)a.n_planes * H * W * eb);
+    MLC_CUDA(bounds_commit(bl, st));
+  }
+#endif
   const size_t smem = (size_t)W * (a.Hw | 1) * 4;
   if (smem > kRleMaxSmem) {
     // the column-walking fallback: 8 bytes of shared memory per column

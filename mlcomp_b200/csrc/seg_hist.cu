@@ -1251,6 +1251,17 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
   a.scale = (n_thr > 1 && span > 0) ? (float)(n_thr - 1) / span : 0.f;
   a.bias = 1.0f - thr_host[0] * a.scale;
 
+#ifdef MLC_BOUNDS_CHECK
+  {
+    BoundsList bl;
+    const size_t eb = dtype == MLC_F16 ? 2 : 4;
+    for (int k = 0; k < n_src; ++k)
+      bl.add(src_dev_ptrs[k], (size_t)a.n_planes * a.plane_px * eb);
+    bl.add(gt_dev, (size_t)a.n_planes * a.plane_px);
+    bl.add(lut_dev, MLC_LUT_BYTES);
+    MLC_CUDA(bounds_commit(bl, st));
+  }
+#endif
   const int sms = sm_count();
   // (the per-code table kernels do not write bins: one source is cheap to
   // read again)
@@ -1454,6 +1465,15 @@ extern "C" int mlc_seg_prob(const void *const *src_dev_ptrs,
   const long long total = a.n_planes * a.items_per_plane;
   const int grid = (int)min((total + 255) / 256, 32ll * sm_count());
   cudaStream_t st = (cudaStream_t)stream;
+#ifdef MLC_BOUNDS_CHECK
+  {
+    BoundsList bl;
+    const size_t eb = dtype == MLC_F16 ? 2 : 4;
+    for (int k = 0; k < n_src; ++k)
+      bl.add(src_dev_ptrs[k], (size_t)a.n_planes * a.plane_px * eb);
+    MLC_CUDA(bounds_commit(bl, st));
+  }
+#endif
   bool aligned = ((long long)H * W) % 8 == 0 && ((uintptr_t)prob_dev % 16) == 0;
   for (int k = 0; k < n_src; ++k)
     aligned = aligned && ((uintptr_t)src_dev_ptrs[k] % 16) == 0;

@@ -391,10 +391,12 @@ seg_hist_guarded(const __grid_constant__ HistArgs a) {
 // LDS - a thread only ever touches its own slots, so cp.async.wait_group is
 // all the synchronisation needed.
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+  MLC_CHECK_LOAD(src, 16);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src)
                : "memory");
 }
 __device__ __forceinline__ void cp_async8(uint32_t dst, const void *src) {
+  MLC_CHECK_LOAD(src, 8);
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src)
                : "memory");
 }
@@ -591,6 +593,19 @@ static void (*pick_guarded(bool rows, bool bins))(HistArgs) {
 
 bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
   *rc = MLC_OK;
+#ifdef MLC_BOUNDS_CHECK
+  {
+    BoundsList bl;
+    for (int k = 0; k < a.src.n; ++k)
+      bl.add(a.src.ptr[k], (size_t)a.n_planes * a.plane_px * 2);
+    bl.add(a.gt, (size_t)a.n_planes * a.plane_px);
+    const cudaError_t e = bounds_commit(bl, st);
+    if (e != cudaSuccess) {
+      *rc = cuda_fail(e, "bounds_commit");
+      return true;
+    }
+  }
+#endif
   const int B = a.B, S = a.src.n;
   if (B < 2 || B > 120 || S < 1) return false;
   if (a.plane_px % 8 != 0 || a.items_per_plane != a.plane_px / 8) return false;
