@@ -1372,6 +1372,16 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
       a.items_per_plane = ipp;
       a.items_per_unit = ipu;
     }
+    if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID &&
+        ((!vec && !vrows) || (a.plane_px % 8) != 0) &&
+        hist_variant() != 4 && hist_variant() != 6) {
+      // rows of any width / alignment: the same estimate fed through
+      // enclosing-vector copies (declines transposes, unaligned tensors,
+      // irregular grids)
+      HistArgs b = a;
+      int rc = MLC_OK;
+      if (seg_hist_guarded_un_launch(b, st, &rc)) return rc;
+    }
     if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID && hist_variant() != 4) {
       // activation table in shared memory: one 1024-thread CTA per SM
       const size_t tab_smem = kActTabBytes;

@@ -90,8 +90,10 @@ __device__ __noinline__ uint32_t guarded_exact_bin(const HistArgs &a,
     }
   } else {
     const size_t plane_off = (size_t)plane * a.plane_px;
-    const int y = rows ? it / a.items_per_row : 0;
-    const int x = (it - y * (rows ? a.items_per_row : 0)) * 8 + i;
+    // it < 0: (-it - 1, i) is the pixel (y, x) itself (row tails)
+    const int y = it < 0 ? -it - 1 : (rows ? it / a.items_per_row : 0);
+    const int x =
+        it < 0 ? i : (it - y * (rows ? a.items_per_row : 0)) * 8 + i;
     for (int k = 0; k < a.src.n; ++k) {
       const int xf = a.src.xf[k];
       const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
@@ -216,7 +218,7 @@ __device__ __forceinline__ void do_group(const HistArgs &a, int k0, int rmask,
 // of the pixels the two disagree on, one shared-memory atomic per pixel.
 // slot: shared address of this lane's column of counters (16 KiB aligned base
 // | lane * 4); the threshold table lies behind the counters.
-template <bool ROWS, bool BINS>
+template <bool ROWS, int BINS>  // BINS: 0 none, 1 aligned item, 2 any offset
 __device__ __forceinline__ void finish_item(const HistArgs &a,
                                             const float (&q)[8], uint32_t dmax,
                                             uint2 g, uint32_t slot,
@@ -267,7 +269,21 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
                  0x5410u);
     v.y = prmt32(prmt32(fx[4], fx[5], 0x0062u), prmt32(fx[6], fx[7], 0x0062u),
                  0x5410u);
-    reinterpret_cast<uint2 *>(a.bins)[bins_item] = v;
+    if (BINS == 1) {
+      reinterpret_cast<uint2 *>(a.bins)[bins_item] = v;
+    } else {  // bins_item is a byte offset of any alignment
+      uint8_t *dst = a.bins + bins_item;
+      if ((reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
+        reinterpret_cast<uint32_t *>(dst)[0] = v.x;
+        reinterpret_cast<uint32_t *>(dst)[1] = v.y;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          dst[i] = (uint8_t)(v.x >> (8 * i));
+          dst[4 + i] = (uint8_t)(v.y >> (8 * i));
+        }
+      }
+    }
   }
 }
 
@@ -364,7 +380,7 @@ seg_hist_guarded(const __grid_constant__ HistArgs a) {
           }
         }
       }
-      finish_item<ROWS, BINS>(a, q, dmax, ldg_stream8(gtp + (size_t)it * 8),
+      finish_item<ROWS, BINS ? 1 : 0>(a, q, dmax, ldg_stream8(gtp + (size_t)it * 8),
                               slot, plane, it,
                               (size_t)plane * (size_t)(a.plane_px >> 3) + it);
       xi += dx;
@@ -529,7 +545,7 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
         do_group<kB, ROWS>(a, 4, (a.g_rev >> 4) & ((1 << kB) - 1), w, false, q,
                            dmax);
     }
-    finish_item<ROWS, BINS>(a, q, dmax, lds_u2(cur + NS * NT * 16u), slot,
+    finish_item<ROWS, BINS ? 1 : 0>(a, q, dmax, lds_u2(cur + NS * NT * 16u), slot,
                             blockIdx.x, it, p0 + (uint32_t)it, cur, NT * 16u);
     }
   }
@@ -583,6 +599,185 @@ static void (*pick_guarded_pf(bool rows, bool bins))(HistArgs) {
                       : seg_hist_guarded_pf<NS, NT, false, false>);
 }
 
+// ---- rows of any width and alignment (350 x 525 ...) -------------------------
+// Same arithmetic; what changes is how an item's 8 values per source reach the
+// registers.  An 8-element window that starts at an arbitrary element lies in
+// the two 16-byte aligned vectors that enclose it: a thread copies those (one
+// when the window is aligned) with cp.async into its own shared-memory slots,
+// and when they have arrived picks the window with one of eight fixed shuffles
+// (window8_from_enclosing).  ONE stage: the words of the current item are
+// taken into registers first, then the copies of the thread's next item go
+// into the same slots and are in flight while the current item is computed.
+// Full items of the rows go through this path; the W % 8 pixels at the end of
+// each row are few (1.5 % at W = 525) and are evaluated exactly, one by one.
+// Requires 16-byte aligned source tensors (every vector that is read then
+// contains at least one byte of the window it is read for) and no transpose.
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void *src) {
+  MLC_CHECK_LOAD(src, 4);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src)
+               : "memory");
+}
+
+template <int NS, int NT, bool BINS, int REV>
+__device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
+                                        uint32_t sub, uint32_t upp,
+                                        uint32_t slot, uint32_t my_slot) {
+  // per thread: source j's two vectors at (2j, 2j + 1) * NT * 16, then 16 bytes
+  // of truth words (3) + the index of the item the slots hold
+  constexpr uint32_t kMisc = 2u * NS * NT * 16u;
+  const int ipr = a.items_per_row, W = a.W, H = a.H;
+  const size_t plane_off = (size_t)plane * a.plane_px;
+  const uint32_t full = (uint32_t)a.full_items;
+  const uint32_t ipu = (full + upp - 1) / upp;
+  const int i0 = (int)(sub * ipu);
+  const int i1 = (int)min(full, (uint32_t)i0 + ipu);
+  const int lane = threadIdx.x & 31;
+  const uint32_t next_sa = (uint32_t)__cvta_generic_to_shared(&s_next_item);
+  // element index of output pixel (y, x0) in source j (x0 = first of 8)
+  auto elem = [&](int j, int y_, int x0) {
+    return a.g_b[j] + a.g_cy[j] * y_ + a.g_cx[j] * x0;
+  };
+  auto issue = [&](int it_) {
+    const int y_ = (int)__umulhi((uint32_t)it_, a.g_ipr_magic);
+    const int x0 = (it_ - y_ * ipr) * 8;
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      const uintptr_t p = reinterpret_cast<uintptr_t>(
+          static_cast<const __half *>(a.src.ptr[j]) + plane_off +
+          elem(j, y_, x0));
+      const uintptr_t v0 = p & ~(uintptr_t)15;
+      cp_async16(my_slot + (2 * j) * NT * 16u,
+                 reinterpret_cast<const void *>(v0));
+      if (p & 15)
+        cp_async16(my_slot + (2 * j + 1) * NT * 16u,
+                   reinterpret_cast<const void *>(v0 + 16));
+    }
+    const uintptr_t g = reinterpret_cast<uintptr_t>(a.gt + plane_off +
+                                                    (size_t)y_ * W + x0);
+    const uintptr_t g0 = g & ~(uintptr_t)3;
+    cp_async4(my_slot + kMisc, reinterpret_cast<const void *>(g0));
+    cp_async4(my_slot + kMisc + 4, reinterpret_cast<const void *>(g0 + 4));
+    if (g & 3)
+      cp_async4(my_slot + kMisc + 8, reinterpret_cast<const void *>(g0 + 8));
+  };
+  {
+    const int it = i0 + (int)threadIdx.x;  // the first round is static
+    st_shared_u32(my_slot + kMisc + 12, (uint32_t)it);
+    if (it < i1) issue(it);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  while (true) {
+    const int it = (int)lds_u32(my_slot + kMisc + 12);
+    if (it - lane >= i1) break;  // the same for all lanes of the warp
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    uint32_t w[4][4];
+    uint2 g = make_uint2(0u, 0u);
+    if (it < i1) {
+      const int y_ = (int)__umulhi((uint32_t)it, a.g_ipr_magic);
+      const int x0 = (it - y_ * ipr) * 8;
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        // (sources are 16-byte aligned: the offset inside the first vector
+        // is that of the element index)
+        const uint32_t off =
+            (uint32_t)((plane_off + (size_t)elem(j, y_, x0)) & 7);
+        const uint4 lo4 = lds_u4(my_slot + (2 * j) * NT * 16u);
+        const uint4 hi4 = lds_u4(my_slot + (2 * j + 1) * NT * 16u);
+        const uint32_t t[8] = {lo4.x, lo4.y, lo4.z, lo4.w,
+                               hi4.x, hi4.y, hi4.z, hi4.w};
+        window8_from_enclosing(t, off,
+                               REV < 0 && ((a.g_rev >> j) & 1) != 0, w[j]);
+      }
+      const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(
+                              a.gt + plane_off + (size_t)y_ * W + x0) & 3) * 8;
+      const uint32_t t0 = lds_u32(my_slot + kMisc),
+                     t1 = lds_u32(my_slot + kMisc + 4),
+                     t2 = lds_u32(my_slot + kMisc + 8);
+      g = make_uint2(__funnelshift_r(t0, t1, sh), __funnelshift_r(t1, t2, sh));
+    }
+    // the slots are free: fetch this thread's next item into them
+    uint32_t nb = 0;
+    if (lane == 0)
+      asm volatile("atom.shared.add.u32 %0, [%1], 32;"
+                   : "=r"(nb)
+                   : "r"(next_sa)
+                   : "memory");
+    nb = __shfl_sync(0xffffffffu, nb, 0);
+    {
+      const int itn = (int)nb + lane;
+      st_shared_u32(my_slot + kMisc + 12, (uint32_t)itn);
+      if (itn < i1) issue(itn);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (it < i1) {
+      float q[8];
+      uint32_t dmax = 0u;
+      if constexpr (REV >= 0)
+        group_sum<NS, REV & ((1 << NS) - 1)>(w, true, q, dmax);
+      else
+        group_sum<NS, 0>(w, true, q, dmax);
+      const int y_ = (int)__umulhi((uint32_t)it, a.g_ipr_magic);
+      finish_item<true, BINS ? 2 : 0>(
+          a, q, dmax, g, slot, plane, it,
+          plane_off + (size_t)y_ * W + (size_t)(it - y_ * ipr) * 8);
+    }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  // the W % 8 pixels at the end of every row of this slice: exact, one pixel
+  // per thread and turn
+  const int nv = W & 7;
+  if (nv) {
+    const int r0 = (int)((long long)H * sub / upp),
+              r1 = (int)((long long)H * (sub + 1) / upp);
+    const uint32_t thr_sa = (slot & ~16383u) + (a.B + 1) * 128u;
+    for (int t = r0 * nv + (int)threadIdx.x; t < r1 * nv; t += NT) {
+      const int y_ = t / nv, x_ = ipr * 8 + (t - y_ * nv);
+      const uint32_t bin =
+          guarded_exact_bin(a, plane, -y_ - 1, x_, true, thr_sa, 0u, 0u);
+      const size_t px = plane_off + (size_t)y_ * W + x_;
+      red_shared_add((bin << 7) | slot, a.gt[px] ? 0x10000u : 1u);
+      if (BINS) a.bins[px] = (uint8_t)bin;
+    }
+  }
+}
+
+template <int NS, int NT, bool BINS>
+__global__ void __launch_bounds__(NT, 1024 / NT)
+seg_hist_guarded_un(const __grid_constant__ HistArgs a) {
+  extern __shared__ __align__(16) uint32_t gsm[];
+  const int B = a.B, nbins = B + 1;
+  const uint32_t gsm_sa = (uint32_t)__cvta_generic_to_shared(gsm);
+  const uint32_t cnt_sa = (gsm_sa + 16383u) & ~16383u;
+  uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
+  float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
+  for (int i = threadIdx.x; i < nbins * 32; i += NT) cnt[i] = 0;
+  for (int i = threadIdx.x; i < B; i += NT) thr[i] = a.thr.v[i];
+  const uint32_t upp = gridDim.y;
+  const uint32_t plane = blockIdx.x, sub = blockIdx.y;
+  if (threadIdx.x == 0) {
+    const uint32_t full = (uint32_t)a.full_items;
+    s_next_item = sub * ((full + upp - 1) / upp) + NT;
+  }
+  __syncthreads();
+  const uint32_t slot = cnt_sa | ((threadIdx.x & 31) * 4);
+  const uint32_t st_sa = (cnt_sa + nbins * 128 + B * 4 + 15u) & ~15u;
+  const uint32_t my_slot = st_sa + threadIdx.x * 16u;
+  constexpr int kAll = (1 << NS) - 1;
+  const int rev = (int)(a.g_rev & kAll);
+  if (rev == 0)
+    un_unit<NS, NT, BINS, 0>(a, plane, sub, upp, slot, my_slot);
+  else if (rev == (0xA & kAll))
+    un_unit<NS, NT, BINS, 0xA & kAll>(a, plane, sub, upp, slot, my_slot);
+  else if (rev == (0x5 & kAll))
+    un_unit<NS, NT, BINS, 0x5 & kAll>(a, plane, sub, upp, slot, my_slot);
+  else if (rev == kAll)
+    un_unit<NS, NT, BINS, kAll>(a, plane, sub, upp, slot, my_slot);
+  else
+    un_unit<NS, NT, BINS, -1>(a, plane, sub, upp, slot, my_slot);
+  uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
+  flush_bins(cnt, nbins, out, upp > 1);
+}
+
 template <int NS>
 static void (*pick_guarded(bool rows, bool bins))(HistArgs) {
   return bins ? (rows ? seg_hist_guarded<NS, true, true>
@@ -591,27 +786,12 @@ static void (*pick_guarded(bool rows, bool bins))(HistArgs) {
                       : seg_hist_guarded<NS, false, false>);
 }
 
-bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
-  *rc = MLC_OK;
-#ifdef MLC_BOUNDS_CHECK
-  {
-    BoundsList bl;
-    for (int k = 0; k < a.src.n; ++k)
-      bl.add(a.src.ptr[k], (size_t)a.n_planes * a.plane_px * 2);
-    bl.add(a.gt, (size_t)a.n_planes * a.plane_px);
-    const cudaError_t e = bounds_commit(bl, st);
-    if (e != cudaSuccess) {
-      *rc = cuda_fail(e, "bounds_commit");
-      return true;
-    }
-  }
-#endif
+// The threshold grid must be uniform over the unit interval; fills the
+// constants of the estimate.  False: this grid stays on the exact kernels.
+static bool guarded_grid(HistArgs &a) {
   const int B = a.B, S = a.src.n;
   if (B < 2 || B > 120 || S < 1) return false;
-  if (a.plane_px % 8 != 0 || a.items_per_plane != a.plane_px / 8) return false;
-  if (a.plane_px / 8 >= (1ll << 31) - 2 * kGThreads) return false;
-  // the grid must be uniform over the unit interval: f(p) = p*scale + bias
-  // puts thr[k] at k + 1, p = 0 at >= 0 and p = 1 at <= B + 1
+  // f(p) = p*scale + bias puts thr[k] at k + 1, p = 0 at >= 0, p = 1 at <= B+1
   const double sc = (double)a.scale, bi = (double)a.bias;
   if (!(sc > 0.0) || bi < 0.0 || sc + bi > (double)B + 1.0 + 1e-6) return false;
   double g = 0.0;
@@ -633,6 +813,94 @@ bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
   a.g_kq = (float)(sc / (double)S);
   a.g_fb_lo = (float)(bi + 128.0 - e);
   a.g_fb_hi = (float)(bi + 128.0 + e);
+  return true;
+}
+
+// Rows of any width / alignment (no transpose): see seg_hist_guarded_un.
+bool seg_hist_guarded_un_launch(HistArgs &a, cudaStream_t st, int *rc) {
+  *rc = MLC_OK;
+  const int S = a.src.n, W = a.W, H = a.H;
+  const int ipr = W / 8;
+  if (S < 2 || S > 4 || ipr < 2) return false;
+  if (a.src.any_xf & MLC_XF_TRANSPOSE) return false;
+  for (int k = 0; k < S; ++k)
+    if (((uintptr_t)a.src.ptr[k] % 16) != 0) return false;
+  const long long full = (long long)ipr * H;
+  if (full * ipr >= (1ll << 32) || a.n_planes >= (1ll << 31) ||
+      a.units_per_plane >= 65536)
+    return false;
+  if (!guarded_grid(a)) return false;
+#ifdef MLC_BOUNDS_CHECK
+  {
+    BoundsList bl;
+    for (int k = 0; k < S; ++k)
+      bl.add(a.src.ptr[k], ((size_t)a.n_planes * a.plane_px * 2 + 15) / 16 * 16);
+    bl.add(a.gt, ((size_t)a.n_planes * a.plane_px + 3) / 4 * 4);
+    const cudaError_t e = bounds_commit(bl, st);
+    if (e != cudaSuccess) {
+      *rc = cuda_fail(e, "bounds_commit");
+      return true;
+    }
+  }
+#endif
+  a.items_per_row = ipr;
+  a.full_items = full;
+  a.g_ipr_magic = (uint32_t)((1ull << 32) / (unsigned)ipr + 1);
+  a.g_rev = 0u;
+  for (int k = 0; k < S; ++k) {
+    const int xf = a.src.xf[k];
+    const int vy = (xf & MLC_XF_VFLIP) ? 1 : 0, hx = (xf & MLC_XF_HFLIP) ? 1 : 0;
+    // element index of output pixel (y, x0): first of the 8 source elements
+    // that hold output pixels x0 .. x0 + 7 (in reverse order when flipped)
+    a.g_cy[k] = vy ? -W : W;
+    a.g_cx[k] = hx ? -1 : 1;
+    a.g_b[k] = (vy ? (H - 1) * W : 0) + (hx ? W - 8 : 0);
+    if (hx) a.g_rev |= 1u << k;
+  }
+  const int B = a.B;
+  constexpr int NT = 512;
+  const size_t smem = 16384 + (size_t)(B + 1) * 32 * 4 + (size_t)B * 4 + 16 +
+                      (size_t)NT * (2 * S + 1) * 16;
+  const bool bins = a.bins != nullptr;
+  void (*k)(HistArgs) =
+      S == 2   ? (bins ? seg_hist_guarded_un<2, NT, true>
+                       : seg_hist_guarded_un<2, NT, false>)
+      : S == 3 ? (bins ? seg_hist_guarded_un<3, NT, true>
+                       : seg_hist_guarded_un<3, NT, false>)
+               : (bins ? seg_hist_guarded_un<4, NT, true>
+                       : seg_hist_guarded_un<4, NT, false>);
+  const cudaError_t ea = cudaFuncSetAttribute(
+      k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (ea != cudaSuccess) {
+    *rc = cuda_fail(ea, "cudaFuncSetAttribute(seg_hist_guarded_un)");
+    return true;
+  }
+  k<<<dim3((unsigned)a.n_planes, (unsigned)a.units_per_plane), NT, smem, st>>>(
+      a);
+  const cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) *rc = cuda_fail(err, "seg_hist_guarded_un");
+  return true;
+}
+
+bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {
+  *rc = MLC_OK;
+#ifdef MLC_BOUNDS_CHECK
+  {
+    BoundsList bl;
+    for (int k = 0; k < a.src.n; ++k)
+      bl.add(a.src.ptr[k], (size_t)a.n_planes * a.plane_px * 2);
+    bl.add(a.gt, (size_t)a.n_planes * a.plane_px);
+    const cudaError_t e = bounds_commit(bl, st);
+    if (e != cudaSuccess) {
+      *rc = cuda_fail(e, "bounds_commit");
+      return true;
+    }
+  }
+#endif
+  const int B = a.B, S = a.src.n;
+  if (a.plane_px % 8 != 0 || a.items_per_plane != a.plane_px / 8) return false;
+  if (a.plane_px / 8 >= (1ll << 31) - 2 * kGThreads) return false;
+  if (!guarded_grid(a)) return false;
   // item index of output item (y, xi) in source k
   const int ipr = a.items_per_row;
   a.g_rev = 0u;

@@ -267,3 +267,36 @@ def test_valid_segment_prepare_submit_from_host_arrays(ops, tmp_path):
         assert [r['EncodedPixels'] for r in ex.rows] == want_strings
         assert ex.rows[3]['ImageId'] == '1_2'
         assert ex.d2h_bytes > 0
+
+
+# ------------------------------------------- rows of any width / alignment
+@pytest.mark.parametrize('shape', [(3, 2, 35, 53), (2, 4, 350, 525),
+                                   (2, 1, 9, 16), (1, 2, 40, 23),
+                                   (5, 3, 7, 100)])
+@pytest.mark.parametrize('n_src,flips', [(4, True), (2, True), (3, False),
+                                         (4, False)])
+def test_guarded_unaligned_rows(ops, shape, n_src, flips):
+    """350 x 525-like planes (rows that are no multiple of 16 bytes, planes
+    that start at any element offset): enclosing-vector copies + exact row
+    tails give the exact binning."""
+    n, c, h, w = shape
+    srcs, gt = synth_seg(n, c, h, w, seed=h + w + n_src, n_src=n_src)
+    tags = [FLIPS[k % 4] if flips else [] for k in range(n_src)]
+    seen = [forward_tta(s, t).to(DEV) for s, t in zip(srcs, tags)]
+    check(ops, seen, tags, gt.to(DEV), oracle.threshold_grid(100))
+
+
+def test_guarded_unaligned_special_values(ops):
+    """NaN / inf / huge values in windows that straddle vectors and rows."""
+    g = torch.Generator().manual_seed(3)
+    n, c, h, w = 1, 2, 21, 37
+    base = torch.randn((n, c, h, w), generator=g) * 4
+    base[0, 0, 3, 5] = float('nan')
+    base[0, 0, 4, 36] = float('inf')
+    base[0, 1, 0, 0] = float('-inf')
+    base[0, 1, 20, 36] = 65504.0
+    base[0, 1, 10, 8:16] = -30.0
+    srcs = [(base + 0.25 * k).half() for k in range(4)]
+    seen = [forward_tta(s, t).to(DEV) for s, t in zip(srcs, FLIPS)]
+    gt = (torch.rand((n, c, h, w), generator=g) < 0.3).to(torch.uint8)
+    check(ops, seen, FLIPS, gt.to(DEV), oracle.threshold_grid(100))
