@@ -25,7 +25,15 @@ def dice_numpy(targets, outputs, threshold=None, min_area=None,
     """
     gt = (_plane(targets, torch.float32) != 0).to(torch.uint8)
     if threshold is None:
-        prob = (_plane(outputs, torch.float32) != 0).float()
+        # the reference then sums `outputs` as given (dice.py:10-11,20): for a
+        # {0,1} mask that is the integer counting done here; a soft mask would
+        # need numpy's float summation order and is refused rather than
+        # silently binarised
+        raw = _plane(outputs, torch.float32)
+        if bool(((raw != 0) & (raw != 1)).any()):
+            raise ValueError('dice_numpy(threshold=None) takes a {0,1} mask; '
+                             'pass probabilities together with a threshold')
+        prob = raw
         thr = 0.5
     else:
         prob = _plane(outputs, torch.float32)

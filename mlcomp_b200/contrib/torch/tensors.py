@@ -1,19 +1,26 @@
-"""contrib/torch/tensors.py:4-8 ``flip`` on the device, as index arithmetic
-inside a kernel (no index tensor, no gather)."""
+"""contrib/torch/tensors.py:4-8 ``flip``.
+
+Flipping one of the last two dims of a CUDA fp16 / fp32 tensor - what
+``TtaWrap.inverse`` asks for (tta.py:23-26) - is index arithmetic inside a
+kernel (mlc_seg_prob with a flip tag: no index tensor, no gather).  Every
+other call the reference's signature allows (another dim, another dtype, a
+CPU tensor) is answered by ``torch.flip``, which returns exactly what the
+reference's ``x[..., arange(n-1, -1, -1), ...]`` returns.  The scoring kernels
+themselves never call either: they fold flips into their load addresses."""
+import torch
+
 from mlcomp_b200 import ops
 
 
 def flip(x, dim):
-    """Reverse ``x`` along one of its last two dims (what TtaWrap.inverse
-    asks for).  CUDA fp16/fp32 tensors of rank >= 2."""
     nd = x.dim()
-    dim = dim % nd
-    if dim < nd - 2 or nd < 2:
-        raise ValueError('flip: only the last two dims are supported')
-    tag = 'hflip' if dim == nd - 1 else 'vflip'
-    y = x.contiguous().reshape(1, -1, x.shape[-2], x.shape[-1])
-    out = ops.seg_prob([y], [[tag]], None)
-    return out.to(x.dtype).reshape(x.shape)
+    d = dim % nd if nd else 0
+    if nd >= 2 and d >= nd - 2 and x.is_cuda and \
+            x.dtype in (torch.float16, torch.float32):
+        tag = 'hflip' if d == nd - 1 else 'vflip'
+        y = x.contiguous().reshape(1, -1, x.shape[-2], x.shape[-1])
+        return ops.seg_prob([y], [[tag]], None).to(x.dtype).reshape(x.shape)
+    return torch.flip(x, [d])
 
 
 __all__ = ['flip']

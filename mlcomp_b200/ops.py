@@ -462,20 +462,19 @@ def rle_strings(runs, off, cnt):
     str_off = torch.empty(planes, dtype=torch.int64, device=dev)
     str_len = torch.empty(planes, dtype=torch.int32, device=dev)
     total = torch.empty(1, dtype=torch.int64, device=dev)  # cleared by the call
-    capacity = max(64, 8 * int(runs.numel()))
-    while True:
-        chars = torch.empty(capacity, dtype=torch.uint8, device=dev)
-        with torch.cuda.device(dev):
-            check(lib.mlc_rle_format(_ptr(runs), _ptr(off), _ptr(cnt), planes,
-                                     _ptr(chars), capacity, _ptr(str_off),
-                                     _ptr(str_len), _ptr(total), _stream()))
-        need = int(total.item())
-        if need <= capacity:
-            break
-        capacity = need
+    # a value is at most 10 digits + 1 blank: 11 characters per int32 always
+    # suffice, so the size never has to be asked for before allocating
+    capacity = max(64, 11 * int(runs.numel()))
+    chars = torch.empty(capacity, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.mlc_rle_format(_ptr(runs), _ptr(off), _ptr(cnt), planes,
+                                 _ptr(chars), capacity, _ptr(str_off),
+                                 _ptr(str_len), _ptr(total), _stream()))
+    # two device->host copies in all: the index (offsets, lengths, total) in
+    # one packed tensor, then exactly the characters that were written
+    idx = torch.cat([str_off, str_len.to(torch.int64), total]).cpu().numpy()
+    o, n, need = idx[:planes], idx[planes:2 * planes], int(idx[-1])
     text = chars[:need].cpu().numpy().tobytes()
-    o = str_off.cpu().numpy()
-    n = str_len.cpu().numpy()
     return [text[a:a + b].decode('ascii') for a, b in zip(o, n)]
 
 

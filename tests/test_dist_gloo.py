@@ -29,6 +29,15 @@ def _worker(rank, world, port, out_dir):
     dsum = torch.from_numpy(per_img_dice[lo:hi].sum(axis=0))
     micro = torch.from_numpy(per_img_micro[lo:hi].sum(axis=0))
     tot, m, n = combine_ranks(dsum, micro, hi - lo)
+    # the packed form SegSearch exchanges: [dice | iou] fp64 bit patterns,
+    # then the int64 counts and the image count - ONE collective
+    from mlcomp_b200.scoring import combine_packed
+    iou = torch.from_numpy((per_img_dice[lo:hi] ** 2).sum(axis=0))
+    packed = torch.cat([dsum.reshape(-1).view(torch.int64),
+                        iou.reshape(-1).view(torch.int64), micro.reshape(-1),
+                        torch.tensor([hi - lo])])
+    out = combine_packed(packed, 2 * dsum.numel())
+    np.save(os.path.join(out_dir, f'packed_{rank}.npy'), out.numpy())
     np.save(os.path.join(out_dir, f'dice_{rank}.npy'), tot.numpy())
     np.save(os.path.join(out_dir, f'micro_{rank}.npy'), m.numpy())
     np.save(os.path.join(out_dir, f'n_{rank}.npy'), np.array([int(n), lo, hi]))
@@ -56,6 +65,17 @@ def test_shard_and_combine_world2(tmp_path):
     want = per_img_dice[:n[0][2]].sum(axis=0) + per_img_dice[n[0][2]:].sum(axis=0)
     assert np.array_equal(d[0], want)
     np.testing.assert_allclose(d[0], per_img_dice.sum(axis=0), rtol=1e-12)
+    # packed buffer: same numbers in one exchange, identical on both ranks
+    p = [np.load(tmp_path / f'packed_{r}.npy') for r in range(world)]
+    assert np.array_equal(p[0], p[1])
+    nd = d[0].size
+    assert np.array_equal(p[0][:nd].view(np.float64), d[0].reshape(-1))
+    sq = per_img_dice ** 2
+    want_iou = sq[:n[0][2]].sum(axis=0) + sq[n[0][2]:].sum(axis=0)
+    assert np.array_equal(p[0][nd:2 * nd].view(np.float64),
+                          want_iou.reshape(-1))
+    assert np.array_equal(p[0][2 * nd:-1], m[0].reshape(-1))
+    assert p[0][-1] == 101
 
 
 def test_shard_range_covers_everything():

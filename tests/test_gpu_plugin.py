@@ -116,6 +116,14 @@ def test_flip_tta_and_activation_dropins(golden_dir):
     assert np.array_equal(flip(x, 3).cpu().numpy(), z['last'])
     assert np.array_equal(flip(x, 2).cpu().numpy(), z['prev'])
     assert np.array_equal(flip(x, -1).cpu().numpy(), z['last'])
+    # the rest of the reference's signature: any dim, any dtype, CPU tensors
+    for t in (x, x.long(), x.cpu(), x.double()):
+        for d in range(-t.dim(), t.dim()):
+            assert torch.equal(flip(t, d), oracle.flip_axis(t, d % t.dim()))
+    from mlcomp_b200.contrib.metrics.dice import dice_numpy
+    with pytest.raises(ValueError, match='takes a \\{0,1\\} mask'):
+        dice_numpy(np.ones((4, 8), np.float32),
+                   np.full((4, 8), 0.5, np.float32))
     w = TtaWrap(list(range(5)), tfms=['hflip', 'vflip'])
     assert len(w) == 5 and w[2] == 2
     assert np.array_equal(w.inverse(x).cpu().numpy(), z['both'])

@@ -1,10 +1,11 @@
 #!/usr/bin/env python
 """Kernel-level timings for the BASELINE.json configs other than the headline
 one (those are parity-test cases for bench.py; this script gives the numbers
-DESIGN.md quotes for them).  Reduced image counts, same plane shapes; inputs
-are far larger than L2.  Prints one JSON object per line.
+DESIGN.md quotes for them).  FULL image counts by default (C3 5,546 images,
+C4 10,000, C5 3,750 = one GPU's share of 30,000 over 8), "name:count" for a
+reduced one; inputs are far larger than L2.  One JSON object per line.
 
-    python tools/bench_configs.py [c1 c3 c4 c5 c2g]
+    python tools/bench_configs.py [c1 c3 c4 c5 c2g c3:1024 ...]
 """
 import json
 import os
@@ -88,24 +89,24 @@ def c1():
            n * (c * 4 + 8), n, {'us': round(ms * 1e3, 2)})
 
 
-def c3(n=1024):
+def c3(n=5546):
     c, h, w = 4, 350, 525
     tags = [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]
     srcs, gt = synth(n, c, h, w, 4, 3, 0.5)
     thr = ops.threshold_grid(100)
     out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
     ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, xforms=tags, out=out))
-    report('C3 cloud 4-flip TTA %dx4x350x525 fp16: seg_hist_tab<0>' % n, ms,
+    report('C3 cloud 4-flip TTA %dx4x350x525 fp16: seg_hist_guarded_un' % n, ms,
            n * c * (h * w * (4 * 2 + 1) + 808), n * c)
 
 
-def c5(n=512):
+def c5(n=3750):
     c, h, w = 4, 256, 1600
     srcs, gt = synth(n, c, h, w, 5, 5, 0.86)
     thr = ops.threshold_grid(100)
     out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
     ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, out=out))
-    report('C5 ensemble 5 models %dx4x256x1600 fp16: seg_hist_tab<1>' % n,
+    report('C5 ensemble 5 models %dx4x256x1600 fp16: seg_hist_guarded_pf' % n,
            ms, n * c * (h * w * (5 * 2 + 1) + 808), n * c)
 
 
@@ -123,7 +124,7 @@ def c2g(n=1024):
            n * c * (h * w * 5 + 808), n * c)
 
 
-def c4(n=2048):
+def c4(n=10000):
     c, h, w = 1, 1024, 1024
     srcs, _ = synth(n, c, h, w, 1, 4, 0.78)
     lib_cap = n * h * w // 16
@@ -155,6 +156,17 @@ def c4(n=2048):
            {'runs': n_runs, 'total_elems': int(total.item())})
 
 
+def am(n=1024):
+    """Segmentation arg-max: 5 classes (4 + background), 2 flips."""
+    c, h, w = 5, 256, 1600
+    srcs, gt = synth(n, c, h, w, 2, 6, 0.5)
+    tags = [[], ['hflip']]
+    ms = timeit(lambda: ops.seg_argmax(srcs, tags, 'softmax', gt_onehot=gt,
+                                       want_counts=True))
+    report('arg-max %dx5x256x1600 fp16 x 2 flips, softmax: seg_argmax_kernel'
+           % n, ms, n * c * h * w * (2 * 2 + 1) + n * h * w, n * c)
+
+
 def c4s(n=512):
     """C4 all the way to Python strings: encode + device formatting + D2H +
     slicing (what Infer.submit needs), against mask2rle's 3.8 ms per plane."""
@@ -181,5 +193,9 @@ def c4s(n=512):
 if __name__ == '__main__':
     which = sys.argv[1:] or ['c1', 'c2g', 'c3', 'c4', 'c5']
     for k in which:
-        globals()[k]()
+        name, _, count = k.partition(':')
+        if count:
+            globals()[name](int(count))
+        else:
+            globals()[name]()
         torch.cuda.empty_cache()
