@@ -215,6 +215,13 @@ extern "C" int mlc_confusion(const void *preds_dev, int dtype, int64_t n,
   a.n = n;
   a.C = n_cls;
   cudaStream_t st = (cudaStream_t)stream;
+#ifdef MLC_BOUNDS_CHECK
+  {
+    BoundsList bl;
+    bl.add(preds_dev, (size_t)n * n_cls * (dtype == MLC_F16 ? 2 : 4));
+    MLC_CUDA(bounds_commit(bl, st));
+  }
+#endif
   const int sms = sm_count();
   if (n_cls <= kRowsMaxC) {
     const bool cmem = n_cls <= kSmallMaxC;
