@@ -20,6 +20,7 @@ namespace mlc {
 
 constexpr int kAmThreads = 256;
 constexpr int kAmMaxSmemClasses = 64;  // C x C table in shared memory
+constexpr int kAmRegClasses = 8;       // class values of a pixel in registers
 
 struct ArgmaxArgs {
   SrcSet src;
@@ -53,6 +54,79 @@ __device__ __forceinline__ float am_fetch(const ArgmaxArgs &a, int k,
   return to_f32<T>(p[(size_t)ys * a.H + xs]);
 }
 
+// offset of output pixel (y, x) inside a class plane of source k
+__device__ __forceinline__ size_t am_offset(const ArgmaxArgs &a, int k, int y,
+                                            int x) {
+  const int xf = a.src.xf[k];
+  if (!(xf & MLC_XF_TRANSPOSE)) {
+    const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+    const int xs = (xf & MLC_XF_HFLIP) ? a.W - 1 - x : x;
+    return (size_t)ys * a.W + xs;
+  }
+  const int ys = (xf & MLC_XF_VFLIP) ? a.W - 1 - x : x;
+  const int xs = (xf & MLC_XF_HFLIP) ? a.H - 1 - y : y;
+  return (size_t)ys * a.H + xs;
+}
+
+// Class scores of one pixel for exactly CT classes (CT <= kAmRegClasses):
+// the pixel's class values of one source live in registers - every logit is
+// loaded once, every exponential taken once (soft-max steps in torch's order:
+// maximum, sum of expf(x - max) in class order, divide); sum over the sources
+// left to right.
+// numpy arg-max order over mean scores: a NaN beats everything, otherwise
+// larger wins, ties (and NaN vs NaN) go to the lower index
+struct AmBest {
+  float best = 0.f;
+  int best_c = 0;
+  bool best_nan = false;
+  __device__ __forceinline__ void consider(int c, float v, int S) {
+    float w[8] = {v, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    mean8(w, S);
+    v = w[0];
+    const bool is_nan = !(v == v);
+    if (c == 0 || (!best_nan && (is_nan || v > best))) {
+      best = v;
+      best_c = c;
+      best_nan = is_nan;
+    }
+  }
+};
+
+template <typename T, int CT>
+__device__ __forceinline__ int am_scores(const ArgmaxArgs &a, long long pl0,
+                                         size_t px, int y, int x) {
+  float acc[CT];
+  const int S = a.src.n;
+  for (int k = 0; k < S; ++k) {
+    const T *p = static_cast<const T *>(a.src.ptr[k]) + (size_t)pl0 * px +
+                 am_offset(a, k, y, x);
+    float v[CT];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) v[c] = to_f32<T>(p[(size_t)c * px]);
+    if (a.act == MLC_ACT_SOFTMAX) {
+      float m = -3.402823466e+38f, sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < CT; ++c) m = m < v[c] ? v[c] : m;
+#pragma unroll
+      for (int c = 0; c < CT; ++c) {
+        v[c] = expf(v[c] - m);
+        sum += v[c];
+      }
+#pragma unroll
+      for (int c = 0; c < CT; ++c) v[c] = v[c] / sum;
+    } else {
+#pragma unroll
+      for (int c = 0; c < CT; ++c) v[c] = activate(v[c], a.act);
+    }
+#pragma unroll
+    for (int c = 0; c < CT; ++c) acc[c] = k == 0 ? v[c] : acc[c] + v[c];
+  }
+  AmBest b;
+#pragma unroll
+  for (int c = 0; c < CT; ++c) b.consider(c, acc[c], S);
+  return b.best_c;
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kAmThreads)
 seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
@@ -77,71 +151,91 @@ seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
     for (long long p = p0 + threadIdx.x; p < p1; p += blockDim.x) {
       const int y = (int)(p / a.W), x = (int)(p - (long long)y * a.W);
       const long long pl0 = img * C;  // class-0 plane of this image
-      // soft-max: per source the running maximum over the classes and the
-      // sum of expf(x - max) in class order (torch's spatial soft-max)
-      float mk[MLC_MAX_SOURCES], zk[MLC_MAX_SOURCES];
-      if (a.act == MLC_ACT_SOFTMAX) {
-        for (int k = 0; k < S; ++k) {
-          float m = -3.402823466e+38f;
-          for (int j = 0; j < C; ++j) {
-            const float t = am_fetch<T>(a, k, pl0 + j, y, x);
-            m = m < t ? t : m;
-          }
-          float sum = 0.f;
-          for (int j = 0; j < C; ++j)
-            sum += expf(am_fetch<T>(a, k, pl0 + j, y, x) - m);
-          mk[k] = m;
-          zk[k] = sum;
-        }
-      }
-      // arg-max over the classes of mean_k act_k(c); numpy order
-      float best = 0.f;
       int best_c = 0;
-      bool best_nan = false;
-      for (int c = 0; c < C; ++c) {
-        float v = 0.f;
-        for (int k = 0; k < S; ++k) {
-          const float t = am_fetch<T>(a, k, pl0 + c, y, x);
-          const float q = a.act == MLC_ACT_SOFTMAX ? expf(t - mk[k]) / zk[k]
-                                                   : activate(t, a.act);
-          v = k == 0 ? q : v + q;
+      if (C <= kAmRegClasses) {
+        switch (C) {
+          case 1: best_c = am_scores<T, 1>(a, pl0, (size_t)px, y, x); break;
+          case 2: best_c = am_scores<T, 2>(a, pl0, (size_t)px, y, x); break;
+          case 3: best_c = am_scores<T, 3>(a, pl0, (size_t)px, y, x); break;
+          case 4: best_c = am_scores<T, 4>(a, pl0, (size_t)px, y, x); break;
+          case 5: best_c = am_scores<T, 5>(a, pl0, (size_t)px, y, x); break;
+          case 6: best_c = am_scores<T, 6>(a, pl0, (size_t)px, y, x); break;
+          case 7: best_c = am_scores<T, 7>(a, pl0, (size_t)px, y, x); break;
+          default: best_c = am_scores<T, 8>(a, pl0, (size_t)px, y, x); break;
         }
-        float w[8] = {v, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        mean8(w, S);
-        v = w[0];
-        const bool is_nan = !(v == v);
-        if (c == 0 || (!best_nan && (is_nan || v > best))) {
-          best = v;
-          best_c = c;
-          best_nan = is_nan;
+      } else {
+        // many classes: per source the running maximum and the sum first,
+        // then class by class (the class values are re-read from L1)
+        float mk[MLC_MAX_SOURCES], zk[MLC_MAX_SOURCES];
+        if (a.act == MLC_ACT_SOFTMAX) {
+          for (int k = 0; k < S; ++k) {
+            float m = -3.402823466e+38f;
+            for (int j = 0; j < C; ++j) {
+              const float t = am_fetch<T>(a, k, pl0 + j, y, x);
+              m = m < t ? t : m;
+            }
+            float sum = 0.f;
+            for (int j = 0; j < C; ++j)
+              sum += expf(am_fetch<T>(a, k, pl0 + j, y, x) - m);
+            mk[k] = m;
+            zk[k] = sum;
+          }
         }
+        AmBest b;
+        for (int c = 0; c < C; ++c) {
+          float v = 0.f;
+          for (int k = 0; k < S; ++k) {
+            const float t = am_fetch<T>(a, k, pl0 + c, y, x);
+            const float q = a.act == MLC_ACT_SOFTMAX
+                                ? expf(t - mk[k]) / zk[k]
+                                : activate(t, a.act);
+            v = k == 0 ? q : v + q;
+          }
+          b.consider(c, v, S);
+        }
+        best_c = b.best_c;
       }
       if (a.label) a.label[img * px + p] = (uint8_t)best_c;
       if (a.onehot)
         for (int c = 0; c < C; ++c)
           a.onehot[(img * C + c) * px + p] = c == best_c ? 1 : 0;
+      // Counting: the lanes of a warp that agree on a key elect one lane,
+      // which adds their number - a plain atomic per pixel would put 256
+      // threads on a dozen shared-memory words (measured: 30x slower).
+      const unsigned active = __activemask();
+      const int lane = threadIdx.x & 31;
+      auto add_by_key = [&](bool valid, int key, unsigned int *table) {
+        const unsigned voters = __ballot_sync(active, valid);
+        if (valid) {
+          const unsigned peers = __match_any_sync(voters, key);
+          if (lane == __ffs(peers) - 1) atomicAdd(&table[key], __popc(peers));
+        }
+      };
       if (a.counts) {
-        atomicAdd(&s_cnt[best_c * 3 + 1], 1u);  // P
+        add_by_key(true, best_c * 3 + 1, s_cnt);  // P
         if (a.gt_onehot) {
           for (int c = 0; c < C; ++c) {
-            if (a.gt_onehot[(img * C + c) * px + p]) {
-              atomicAdd(&s_cnt[c * 3 + 0], 1u);  // T
-              if (c == best_c) atomicAdd(&s_cnt[c * 3 + 2], 1u);  // I
+            const bool g = a.gt_onehot[(img * C + c) * px + p] != 0;
+            const unsigned bt = __ballot_sync(active, g);
+            const unsigned bi = __ballot_sync(active, g && c == best_c);
+            if (lane == __ffs(active) - 1) {
+              if (bt) atomicAdd(&s_cnt[c * 3 + 0], __popc(bt));  // T
+              if (bi) atomicAdd(&s_cnt[c * 3 + 2], __popc(bi));  // I
             }
           }
         } else if (a.gt_label) {
           const int g = a.gt_label[img * px + p];
-          if (g < C) {
-            atomicAdd(&s_cnt[g * 3 + 0], 1u);
-            if (g == best_c) atomicAdd(&s_cnt[g * 3 + 2], 1u);
-          }
+          add_by_key(g < C, g * 3 + 0, s_cnt);
+          add_by_key(g < C && g == best_c, g * 3 + 2, s_cnt);
         }
       }
       if (a.cm && a.gt_label) {
         const int g = a.gt_label[img * px + p];
-        if (g < C) {  // labels outside [0, C) are dropped (sklearn's rule)
-          if (cm_smem) atomicAdd(&s_cm[g * C + best_c], 1u);
-          else atomicAdd(&a.cm[(size_t)g * C + best_c], 1ull);
+        // labels outside [0, C) are dropped (sklearn's rule)
+        if (cm_smem) {
+          add_by_key(g < C, g * C + best_c, s_cm);
+        } else if (g < C) {
+          atomicAdd(&a.cm[(size_t)g * C + best_c], 1ull);
         }
       }
     }

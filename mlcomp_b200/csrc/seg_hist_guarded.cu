@@ -618,13 +618,34 @@ __device__ __forceinline__ void cp_async4(uint32_t dst, const void *src) {
                : "memory");
 }
 
+// The eight halves that start `off` halves (0..7) into the eight words t[]:
+// two levels of selects move the window to the front word by word, four funnel
+// shifts move it by the odd half.  Branch-free: lanes of a warp that sit in
+// different rows have different offsets, and the eight-way switch of
+// window8_from_enclosing cost 30 % of the kernel's stall samples in branches.
+__device__ __forceinline__ void window8_select(const uint32_t (&t)[8],
+                                               uint32_t off,
+                                               uint32_t (&w)[4]) {
+  const bool b2 = off & 4u, b1 = off & 2u;
+  uint32_t a[6], b[5];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) a[j] = b2 ? t[j + 2] : t[j];
+#pragma unroll
+  for (int j = 0; j < 5; ++j) b[j] = b1 ? a[j + 1] : a[j];
+  const uint32_t sh = (off & 1u) * 16u;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) w[j] = __funnelshift_r(b[j], b[j + 1], sh);
+}
+
 template <int NS, int NT, bool BINS, int REV>
 __device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
                                         uint32_t sub, uint32_t upp,
                                         uint32_t slot, uint32_t my_slot) {
   // per thread: source j's two vectors at (2j, 2j + 1) * NT * 16, then 16 bytes
-  // of truth words (3) + the index of the item the slots hold
+  // of truth words (3) + the index of the item the slots hold, then a word
+  // with the window offsets (3 bits per source) and the truth shift
   constexpr uint32_t kMisc = 2u * NS * NT * 16u;
+  constexpr uint32_t kMeta = kMisc + NT * 16u;
   const int ipr = a.items_per_row, W = a.W, H = a.H;
   const size_t plane_off = (size_t)plane * a.plane_px;
   const uint32_t full = (uint32_t)a.full_items;
@@ -640,12 +661,14 @@ __device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
   auto issue = [&](int it_) {
     const int y_ = (int)__umulhi((uint32_t)it_, a.g_ipr_magic);
     const int x0 = (it_ - y_ * ipr) * 8;
+    uint32_t meta = 0u;
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
       const uintptr_t p = reinterpret_cast<uintptr_t>(
           static_cast<const __half *>(a.src.ptr[j]) + plane_off +
           elem(j, y_, x0));
       const uintptr_t v0 = p & ~(uintptr_t)15;
+      meta |= ((uint32_t)(p & 15) >> 1) << (3 * j);
       cp_async16(my_slot + (2 * j) * NT * 16u,
                  reinterpret_cast<const void *>(v0));
       if (p & 15)
@@ -655,6 +678,8 @@ __device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
     const uintptr_t g = reinterpret_cast<uintptr_t>(a.gt + plane_off +
                                                     (size_t)y_ * W + x0);
     const uintptr_t g0 = g & ~(uintptr_t)3;
+    meta |= (uint32_t)(g & 3) << 12;
+    st_shared_u32(my_slot + kMeta, meta);
     cp_async4(my_slot + kMisc, reinterpret_cast<const void *>(g0));
     cp_async4(my_slot + kMisc + 4, reinterpret_cast<const void *>(g0 + 4));
     if (g & 3)
@@ -673,23 +698,17 @@ __device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
     uint32_t w[4][4];
     uint2 g = make_uint2(0u, 0u);
     if (it < i1) {
-      const int y_ = (int)__umulhi((uint32_t)it, a.g_ipr_magic);
-      const int x0 = (it - y_ * ipr) * 8;
+      const uint32_t meta = lds_u32(my_slot + kMeta);
 #pragma unroll
       for (int j = 0; j < NS; ++j) {
-        // (sources are 16-byte aligned: the offset inside the first vector
-        // is that of the element index)
-        const uint32_t off =
-            (uint32_t)((plane_off + (size_t)elem(j, y_, x0)) & 7);
         const uint4 lo4 = lds_u4(my_slot + (2 * j) * NT * 16u);
         const uint4 hi4 = lds_u4(my_slot + (2 * j + 1) * NT * 16u);
         const uint32_t t[8] = {lo4.x, lo4.y, lo4.z, lo4.w,
                                hi4.x, hi4.y, hi4.z, hi4.w};
-        window8_from_enclosing(t, off,
-                               REV < 0 && ((a.g_rev >> j) & 1) != 0, w[j]);
+        window8_select(t, (meta >> (3 * j)) & 7u, w[j]);
+        if (REV < 0 && ((a.g_rev >> j) & 1)) reverse8(w[j]);
       }
-      const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(
-                              a.gt + plane_off + (size_t)y_ * W + x0) & 3) * 8;
+      const uint32_t sh = ((meta >> 12) & 3u) * 8u;
       const uint32_t t0 = lds_u32(my_slot + kMisc),
                      t1 = lds_u32(my_slot + kMisc + 4),
                      t2 = lds_u32(my_slot + kMisc + 8);
@@ -860,7 +879,7 @@ bool seg_hist_guarded_un_launch(HistArgs &a, cudaStream_t st, int *rc) {
   const int B = a.B;
   constexpr int NT = 512;
   const size_t smem = 16384 + (size_t)(B + 1) * 32 * 4 + (size_t)B * 4 + 16 +
-                      (size_t)NT * (2 * S + 1) * 16;
+                      (size_t)NT * (2 * S + 2) * 16;
   const bool bins = a.bins != nullptr;
   void (*k)(HistArgs) =
       S == 2   ? (bins ? seg_hist_guarded_un<2, NT, true>

@@ -1,8 +1,10 @@
 #!/bin/bash
-# Launch list of the bench's timed region + full capture of its top kernel.
+# Launch list of the bench's timed region + full capture of its top kernel,
+# at the bench's full size (IMAGES=0) unless IMAGES says otherwise.
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --no-cpu --no-side --images ${IMAGES:-1024} --e2e-images 64 --e2e-steps 1"
+IM=${IMAGES:-0}
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu --no-side --images $IM --e2e-images 64 --e2e-steps 1"
 $CMD > gpurun_out/p_plain.json 2> gpurun_out/p_plain.err &&
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/r02_launches_pipeline.csv $CMD > gpurun_out/p_ncu1.log 2>&1
 echo "launch list rc=$?"
