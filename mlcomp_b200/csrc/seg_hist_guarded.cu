@@ -499,13 +499,16 @@ __device__ __forceinline__ void pf_unit(const HistArgs &a, uint32_t plane,
     const uint32_t cur = odd ? my_slot + kStage : my_slot;
     const int it = (int)lds_u32(cur + kIdxOff);
     if (it - lane >= i1) break;  // the same for all lanes of the warp
-    // (inline PTX: atomicAdd() on a uniform address makes the compiler build
-    // its warp-aggregation sequence, ~20 instructions, around one lane)
+    // One lane takes the warp's next 32 items.  The address is offset by a
+    // term that is always zero but not provably so (it >= 0): for an atomic
+    // on a provably uniform address ptxas builds its warp-aggregation
+    // sequence (vote, find-leader, popc, shuffles: ~20 instructions, 11 % of
+    // the kernel's stall samples) around this single lane.
     uint32_t nb = 0;
     if (lane == 0)
       asm volatile("atom.shared.add.u32 %0, [%1], 32;"
                    : "=r"(nb)
-                   : "r"(next_sa)
+                   : "r"(next_sa + (((uint32_t)it >> 31) << 2))
                    : "memory");
     nb = __shfl_sync(0xffffffffu, nb, 0);
     {
@@ -715,11 +718,12 @@ __device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
       g = make_uint2(__funnelshift_r(t0, t1, sh), __funnelshift_r(t1, t2, sh));
     }
     // the slots are free: fetch this thread's next item into them
+    // (address offset by an always-zero term: see pf_unit)
     uint32_t nb = 0;
     if (lane == 0)
       asm volatile("atom.shared.add.u32 %0, [%1], 32;"
                    : "=r"(nb)
-                   : "r"(next_sa)
+                   : "r"(next_sa + (((uint32_t)it >> 31) << 2))
                    : "memory");
     nb = __shfl_sync(0xffffffffu, nb, 0);
     {
