@@ -127,8 +127,11 @@ __device__ __forceinline__ int am_scores(const ArgmaxArgs &a, long long pl0,
   return b.best_c;
 }
 
-template <typename T>
-__global__ void __launch_bounds__(kAmThreads)
+// CT: the class count when it is 2..8 (scores in registers, see am_scores),
+// 0 = any.  A kernel per count: one kernel holding all eight variants needed
+// 128 registers and ran latency-bound at 16 warps per SM.
+template <typename T, int CT>
+__global__ void __launch_bounds__(kAmThreads, 4)
 seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
   extern __shared__ unsigned int am_smem[];  // [C][3] (+ [C][C])
   const int C = a.C;
@@ -152,17 +155,8 @@ seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
       const int y = (int)(p / a.W), x = (int)(p - (long long)y * a.W);
       const long long pl0 = img * C;  // class-0 plane of this image
       int best_c = 0;
-      if (C <= kAmRegClasses) {
-        switch (C) {
-          case 1: best_c = am_scores<T, 1>(a, pl0, (size_t)px, y, x); break;
-          case 2: best_c = am_scores<T, 2>(a, pl0, (size_t)px, y, x); break;
-          case 3: best_c = am_scores<T, 3>(a, pl0, (size_t)px, y, x); break;
-          case 4: best_c = am_scores<T, 4>(a, pl0, (size_t)px, y, x); break;
-          case 5: best_c = am_scores<T, 5>(a, pl0, (size_t)px, y, x); break;
-          case 6: best_c = am_scores<T, 6>(a, pl0, (size_t)px, y, x); break;
-          case 7: best_c = am_scores<T, 7>(a, pl0, (size_t)px, y, x); break;
-          default: best_c = am_scores<T, 8>(a, pl0, (size_t)px, y, x); break;
-        }
+      if constexpr (CT > 0) {
+        best_c = am_scores<T, CT>(a, pl0, (size_t)px, y, x);
       } else {
         // many classes: per source the running maximum and the sum first,
         // then class by class (the class values are re-read from L1)
@@ -311,10 +305,20 @@ extern "C" int mlc_seg_argmax(const void *const *src_dev_ptrs,
                                 ? n_cls * n_cls : 0)) * 4;
   const long long n_chunks = n_img * a.chunks_per_img;
   const int grid = (int)min(n_chunks, 16ll * sm_count());
-  if (dtype == MLC_F16)
-    seg_argmax_kernel<__half><<<grid, kAmThreads, smem, st>>>(a);
-  else
-    seg_argmax_kernel<float><<<grid, kAmThreads, smem, st>>>(a);
+  void (*k)(ArgmaxArgs);
+#define MLC_AM(T)                                                      \
+  (n_cls == 2   ? seg_argmax_kernel<T, 2>                               \
+   : n_cls == 3 ? seg_argmax_kernel<T, 3>                               \
+   : n_cls == 4 ? seg_argmax_kernel<T, 4>                               \
+   : n_cls == 5 ? seg_argmax_kernel<T, 5>                               \
+   : n_cls == 6 ? seg_argmax_kernel<T, 6>                               \
+   : n_cls == 7 ? seg_argmax_kernel<T, 7>                               \
+   : n_cls == 8 ? seg_argmax_kernel<T, 8>                               \
+                : seg_argmax_kernel<T, 0>)
+  if (dtype == MLC_F16) k = MLC_AM(__half);
+  else k = MLC_AM(float);
+#undef MLC_AM
+  k<<<grid, kAmThreads, smem, st>>>(a);
   MLC_LAUNCH_CHECK("seg_argmax_kernel");
   return MLC_OK;
 }
