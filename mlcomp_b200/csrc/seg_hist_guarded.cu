@@ -225,7 +225,13 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
                                             long long plane, int it,
                                             size_t bins_item,
                                             uint32_t stage_sa = 0u,
-                                            uint32_t stage_stride = 0u) {
+                                            uint32_t stage_stride = 0u,
+                                            int skip = 0, int ex_it = 0,
+                                            int ex_i0 = 0) {
+  // skip > 0 (row-tail items of the unaligned kernel): the first `skip`
+  // pixels of the window belong to the previous item and are not counted;
+  // the exact path is then addressed as pixel (y, x) = (-ex_it - 1, ex_i0 + i)
+  const bool tail = skip > 0 || ex_it < 0;
   const float kq = a.g_kq, fb_lo = a.g_fb_lo, fb_hi = a.g_fb_hi;
   uint32_t fx[8], differ = 0;
 #pragma unroll
@@ -244,14 +250,22 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
       const uint32_t hi = __float_as_uint(fmaf(q[i], kq, fb_hi));
       if (all || ((fx[i] ^ hi) >> 16) != 0u)
         fx[i] = 0x43008000u |
-                (guarded_exact_bin(a, plane, it, i, ROWS,
+                (guarded_exact_bin(a, plane, tail ? ex_it : it,
+                                   tail ? ex_i0 + i : i, ROWS,
                                    (slot & ~16383u) + (a.B + 1) * 128u,
                                    stage_sa, stage_stride)
                  << 16);
     }
   }
   // bin = bits 16..22 of fx (the exponent field reads 0x4300 + bin)
-  if ((g.x | g.y) == 0u) {  // all background: the increment is 1
+  if (skip > 0) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint32_t gb = ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
+      if (i >= skip)
+        red_shared_add(((fx[i] >> 9) & 0x3F80u) | slot, gb ? 0x10000u : 1u);
+    }
+  } else if ((g.x | g.y) == 0u) {  // all background: the increment is 1
 #pragma unroll
     for (int i = 0; i < 8; ++i)
       red_shared_add(((fx[i] >> 9) & 0x3F80u) | slot, 1u);
@@ -611,8 +625,9 @@ static void (*pick_guarded_pf(bool rows, bool bins))(HistArgs) {
 // (window8_from_enclosing).  ONE stage: the words of the current item are
 // taken into registers first, then the copies of the thread's next item go
 // into the same slots and are in flight while the current item is computed.
-// Full items of the rows go through this path; the W % 8 pixels at the end of
-// each row are few (1.5 % at W = 525) and are evaluated exactly, one by one.
+// The W % 8 pixels at the end of a row are served by one more item whose window
+// is the row's last eight pixels (the ones it shares with its neighbour are
+// not counted again).
 // Requires 16-byte aligned source tensors (every vector that is read then
 // contains at least one byte of the window it is read for) and no transpose.
 __device__ __forceinline__ void cp_async4(uint32_t dst, const void *src) {
@@ -661,9 +676,14 @@ __device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
   auto elem = [&](int j, int y_, int x0) {
     return a.g_b[j] + a.g_cy[j] * y_ + a.g_cx[j] * x0;
   };
+  // items of a row: its W / 8 full items, then (W % 8 != 0) one more whose
+  // window is the row's LAST eight pixels - it overlaps its neighbour, and
+  // only its last W % 8 pixels are counted
+  const int ipt = ipr + ((W & 7) ? 1 : 0);
   auto issue = [&](int it_) {
     const int y_ = (int)__umulhi((uint32_t)it_, a.g_ipr_magic);
-    const int x0 = (it_ - y_ * ipr) * 8;
+    const int xi_ = it_ - y_ * ipt;
+    const int x0 = xi_ < ipr ? xi_ * 8 : W - 8;
     uint32_t meta = 0u;
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
@@ -740,28 +760,15 @@ __device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
       else
         group_sum<NS, 0>(w, true, q, dmax);
       const int y_ = (int)__umulhi((uint32_t)it, a.g_ipr_magic);
+      const int xi_ = it - y_ * ipt;
+      const int x0 = xi_ < ipr ? xi_ * 8 : W - 8;
       finish_item<true, BINS ? 2 : 0>(
           a, q, dmax, g, slot, plane, it,
-          plane_off + (size_t)y_ * W + (size_t)(it - y_ * ipr) * 8);
+          plane_off + (size_t)y_ * W + (size_t)x0, 0u, 0u,
+          xi_ < ipr ? 0 : 8 - (W & 7), -y_ - 1, x0);
     }
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
-  // the W % 8 pixels at the end of every row of this slice: exact, one pixel
-  // per thread and turn
-  const int nv = W & 7;
-  if (nv) {
-    const int r0 = (int)((long long)H * sub / upp),
-              r1 = (int)((long long)H * (sub + 1) / upp);
-    const uint32_t thr_sa = (slot & ~16383u) + (a.B + 1) * 128u;
-    for (int t = r0 * nv + (int)threadIdx.x; t < r1 * nv; t += NT) {
-      const int y_ = t / nv, x_ = ipr * 8 + (t - y_ * nv);
-      const uint32_t bin =
-          guarded_exact_bin(a, plane, -y_ - 1, x_, true, thr_sa, 0u, 0u);
-      const size_t px = plane_off + (size_t)y_ * W + x_;
-      red_shared_add((bin << 7) | slot, a.gt[px] ? 0x10000u : 1u);
-      if (BINS) a.bins[px] = (uint8_t)bin;
-    }
-  }
 }
 
 template <int NS, int NT, bool BINS>
@@ -848,8 +855,9 @@ bool seg_hist_guarded_un_launch(HistArgs &a, cudaStream_t st, int *rc) {
   if (a.src.any_xf & MLC_XF_TRANSPOSE) return false;
   for (int k = 0; k < S; ++k)
     if (((uintptr_t)a.src.ptr[k] % 16) != 0) return false;
-  const long long full = (long long)ipr * H;
-  if (full * ipr >= (1ll << 32) || a.n_planes >= (1ll << 31) ||
+  const int ipt = ipr + ((W & 7) ? 1 : 0);  // + the row's tail item
+  const long long full = (long long)ipt * H;
+  if (full * ipt >= (1ll << 32) || a.n_planes >= (1ll << 31) ||
       a.units_per_plane >= 65536)
     return false;
   if (!guarded_grid(a)) return false;
@@ -868,7 +876,7 @@ bool seg_hist_guarded_un_launch(HistArgs &a, cudaStream_t st, int *rc) {
 #endif
   a.items_per_row = ipr;
   a.full_items = full;
-  a.g_ipr_magic = (uint32_t)((1ull << 32) / (unsigned)ipr + 1);
+  a.g_ipr_magic = (uint32_t)((1ull << 32) / (unsigned)ipt + 1);
   a.g_rev = 0u;
   for (int k = 0; k < S; ++k) {
     const int xf = a.src.xf[k];
