@@ -208,14 +208,26 @@ seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
       if (a.counts) {
         add_by_key(true, best_c * 3 + 1, s_cnt);  // P
         if (a.gt_onehot) {
-          for (int c = 0; c < C; ++c) {
-            const bool g = a.gt_onehot[(img * C + c) * px + p] != 0;
+          // all class bytes first (independent loads), then the votes: a load
+          // followed by its vote per class serialised C memory latencies
+          auto vote = [&](int c, bool g) {
             const unsigned bt = __ballot_sync(active, g);
             const unsigned bi = __ballot_sync(active, g && c == best_c);
             if (lane == __ffs(active) - 1) {
               if (bt) atomicAdd(&s_cnt[c * 3 + 0], __popc(bt));  // T
               if (bi) atomicAdd(&s_cnt[c * 3 + 2], __popc(bi));  // I
             }
+          };
+          if constexpr (CT > 0) {
+            uint8_t gv[CT];
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+              gv[c] = a.gt_onehot[(img * C + c) * px + p];
+#pragma unroll
+            for (int c = 0; c < CT; ++c) vote(c, gv[c] != 0);
+          } else {
+            for (int c = 0; c < C; ++c)
+              vote(c, a.gt_onehot[(img * C + c) * px + p] != 0);
           }
         } else if (a.gt_label) {
           const int g = a.gt_label[img * px + p];
