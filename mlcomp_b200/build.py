@@ -54,19 +54,37 @@ def _headers():
     return deps
 
 
-def needs_build(variant=''):
+def _digest(flag_text=''):
+    """Content hash of everything the library is built from (not mtimes: a
+    snapshot copied to another machine must not look stale)."""
+    import hashlib
+    h = hashlib.sha256(flag_text.encode())
+    for d in sorted([os.path.join(CSRC, s) for s in SOURCES] + _headers()):
+        h.update(os.path.basename(d).encode())
+        with open(d, 'rb') as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+def _base_flags(defines=()):
+    return ' '.join(['-O3', '-std=c++17', '-lineinfo', '-gencode',
+                     'arch=compute_100a,code=sm_100a'] +
+                    ['-D' + d for d in defines] +
+                    os.environ.get('MLC_EXTRA_NVCC', '').split())
+
+
+def needs_build(variant='', defines=()):
     lib = lib_for(variant)
-    if not os.path.exists(lib):
+    stamp = lib + '.stamp'
+    if not os.path.exists(lib) or not os.path.exists(stamp):
         return True
-    t = os.path.getmtime(lib)
-    deps = [os.path.join(CSRC, s) for s in SOURCES] + _headers()
-    return any(os.path.getmtime(d) > t for d in deps)
+    return open(stamp).read().strip() != _digest(_base_flags(defines))
 
 
 def build(verbose=False, force=False, variant='', defines=()):
     """Compile what is stale and link.  Returns the library path."""
     lib = lib_for(variant)
-    if not force and not needs_build(variant):
+    if not force and not needs_build(variant, defines):
         return lib
     os.makedirs(LIB_DIR, exist_ok=True)
     obj_dir = os.path.join(HERE, 'build', variant or 'default')
@@ -115,6 +133,8 @@ def build(verbose=False, force=False, variant='', defines=()):
         sys.stderr.write(res.stdout + res.stderr)
     if res.returncode:
         raise RuntimeError('nvcc failed linking libmlcomp_b200.so')
+    with open(lib + '.stamp', 'w') as f:
+        f.write(_digest(_base_flags(defines)))
     return lib
 
 

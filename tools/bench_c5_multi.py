@@ -5,9 +5,9 @@ sharded over the ranks, one exchange of the packed score tables) at N GPUs:
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N \\
         --master-addr 127.0.0.1 --master-port 29544 tools/bench_c5_multi.py [images_per_rank]
 
-Each rank owns its shard in HBM (synthetic, SURVEY.md 8(d): members = base +
-N(0, 0.7)); a step = SegSearch.add over the shard + result() (the all_gather
-of 22 KB per rank).  Prints one JSON line on rank 0; time = max over ranks.
+Each rank owns its shard in HBM (synthetic, SURVEY.md 8(d): members = shared
+logits + their own noise per pixel); a step = SegSearch.add over the shard + result() (the all_gather
+of 16.5 KB per rank + the fold kernel).  Prints one JSON line on rank 0; time = max over ranks.
 """
 import datetime
 import json
@@ -33,15 +33,17 @@ def main():
     if world > 1:
         dist.init_process_group('nccl', device_id=dev,
                                 timeout=datetime.timedelta(seconds=300))
-    n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
-    cfg = dict(bench.C2)
+    # BASELINE config 5 at full size: 30 000 images over 8 GPUs = 3 750 each
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 3750
+    cfg = dict(bench.CFG)
     c, h, w = cfg['n_cls'], cfg['H'], cfg['W']
-    base, gt = bench.synth(cfg, n, 5000 + rank, dev)
-    g = torch.Generator(device=dev).manual_seed(50 + rank)
-    members = [(base + 0.7 * torch.randn(base.shape, generator=g, device=dev,
-                                         dtype=torch.float16))
-               for _ in range(5)]
-    del base
+    members, gt = bench.synth_tta(cfg, n, 5000 + rank, dev, n_var=5)
+    # ensemble members are not flipped: undo the storage flips of synth_tta
+    for k in range(5):
+        dims = bench.FLIP_DIMS[k % 4]
+        if dims:
+            for lo in range(0, n, 256):
+                members[k][lo:lo + 256] = members[k][lo:lo + 256].flip(*dims)
     thr = ops.threshold_grid(cfg['bins'])
     search = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev)
 
