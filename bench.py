@@ -58,6 +58,25 @@ def workload_name(cfg, n_img=None):
                cfg['H'], cfg['W']))
 
 
+def config_dict(cfg, n_img, e2e_images, e2e_chunk):
+    """The `config` object - identical in both arms (the reference arm's
+    bounded sample is described under `cpu_baseline.sample`)."""
+    planes = n_img * cfg['n_cls']
+    px = cfg['H'] * cfg['W']
+    return {
+        'workload': workload_name(cfg, n_img),
+        'planes_per_gpu': planes,
+        'arithmetic': 'fp16 logits, fp32 sigmoid / mean / compares, '
+                      'integer counts, fp64 dice',
+        'cache': 'inputs %.1f GB per GPU per step, far larger than the '
+                 '126 MB L2; no flush needed' % (planes * px * 9 / 1e9),
+        'e2e': '%d images x 4 variants per GPU per step from pinned host '
+               'memory in parts of %d images, copies double-buffered against '
+               'the kernels; scores, run pairs and RLE text read back' %
+               (min(n_img, e2e_images), e2e_chunk),
+    }
+
+
 def hist_bytes_per_plane(cfg, n_src, elem=2):
     """logits once + 1 B/px ground truth + histogram out."""
     px = cfg['H'] * cfg['W']
@@ -316,7 +335,8 @@ def run_reference(args, cfg):
         'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16',
         'data': 'synthetic',
-        'config': {'workload': workload_name(cfg), 'sample': sample},
+        'config': config_dict(cfg, args.images or cfg['n_img'],
+                              args.e2e_images, args.e2e_chunk),
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores,
                          'kind': kind, 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0,
@@ -633,6 +653,7 @@ def run_ours(args, cfg):
     # ---- end to end through the executor plugin -----------------------------
     e2e = e2e_through_executor(args, cfg, srcs, gt, dev, world, barrier)
     validated &= e2e.pop('ok')
+    e2e.pop('how', None)
 
     if rank != 0:
         if world > 1:
@@ -650,15 +671,7 @@ def run_ours(args, cfg):
         'ms_per_step': step_ms, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16',
         'data': 'synthetic',
-        'config': {
-            'workload': workload_name(cfg, n_img),
-            'planes_per_gpu': planes,
-            'arithmetic': 'fp16 logits, fp32 sigmoid / mean / compares, '
-                          'integer counts, fp64 dice',
-            'cache': 'inputs %.1f GB per GPU per step, far larger than the '
-                     '126 MB L2; no flush needed' % (planes * px * 9 / 1e9),
-            'e2e': e2e.pop('how'),
-        },
+        'config': config_dict(cfg, n_img, args.e2e_images, args.e2e_chunk),
         'validated': bool(validated),
         'parity': dict(parity or {}, best=best,
                        same_best_every_step=same_best),
