@@ -82,6 +82,10 @@ class _SegInputs:
             size = max(hi - lo for lo, hi in self._parts) if self._parts \
                 else self.part[1] - self.part[0]
             self._stager = scoring.HostStager(arrays, 'cuda', size)
+        # whatever was enqueued on the previous part's buffers so far is what
+        # must finish before they are overwritten (a no-op when score() has
+        # released them already)
+        self._stager.release()
         dev = self._stager.fetch(*self.part)
         if self.part in self._parts:
             i = self._parts.index(self.part)
