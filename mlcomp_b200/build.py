@@ -30,7 +30,7 @@ CSRC = os.path.join(HERE, 'csrc')
 LIB_DIR = os.path.join(HERE, 'lib')
 LIB = os.path.join(LIB_DIR, 'libmlcomp_b200.so')
 SOURCES = ['common.cu', 'confusion.cu', 'seg_hist.cu', 'seg_hist_guarded.cu',
-           'seg_argmax.cu', 'dice_scan.cu', 'rle.cu', 'rle_format.cu', 'rle_decode.cu',
+           'seg_hist_guarded_rows.cu', 'seg_argmax.cu', 'dice_scan.cu', 'rle.cu', 'rle_format.cu', 'rle_decode.cu',
            'composite.cu', 'exchange.cu']
 
 

@@ -1378,8 +1378,12 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
       // rows of any width / alignment: the same estimate fed through
       // enclosing-vector copies (declines transposes, unaligned tensors,
       // irregular grids)
-      HistArgs b = a;
       int rc = MLC_OK;
+      {
+        HistArgs b = a;
+        if (seg_hist_guarded_rows_launch(b, st, &rc)) return rc;
+      }
+      HistArgs b = a;
       if (seg_hist_guarded_un_launch(b, st, &rc)) return rc;
     }
     if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID && hist_variant() != 4) {

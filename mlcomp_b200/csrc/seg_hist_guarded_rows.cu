@@ -1,0 +1,383 @@
+// K1, guarded estimate (seg_hist_guarded.cuh), for rows of ANY width and
+// alignment (350 x 525 ...): the rows are staged in shared memory by the bulk
+// copy engine (TMA unit, 1-D cp.async.bulk) instead of by the threads.
+//
+// Why: a row of W fp16 values that is no multiple of 16 bytes starts at a
+// different offset inside its 16-byte vectors in every row, and flipped
+// sources add their own.  seg_hist_guarded_un pays for that per item and per
+// source with two cp.async of the enclosing vectors and 64-bit address
+// arithmetic (70 instructions per pixel against 49 of the aligned kernel), in
+// a single stage, and reads most 32-byte sectors twice (ncu: 5.5 of 32 bytes
+// used per request).  Here ONE thread of the CTA asks the copy engine for
+// "the 16-byte vectors that enclose source row ys" - one copy per row and
+// source, every sector once - into a ring of row slots that is many rows
+// deep; the other threads never form a global address.
+//
+// (A tensor map cannot do the realignment itself: measured on B200, a tiled
+// copy whose innermost start coordinate is not a multiple of 16 bytes raises
+// "illegal instruction" - tools/_probe/tma_probe.cu - so the copy preserves
+// the address modulo 16 and the residual offset, 0..7 elements, uniform per
+// row and source, is resolved at the read: two LDS.128 and window8_select.)
+//
+// A bulk copy costs the copy engine a fixed ~129 ns per CTA whatever its size
+// up to 2 KiB (tools/_probe/bulk_rate.cu: 512 B .. 2 KiB copies all take
+// 128.8 ns, 4 KiB 182 ns, from 8 KiB on the HBM rate), and a row of 525 fp16
+// values is 1 KiB: one copy per row and source ran at 0.33 of the HBM peak
+// with the producer never idle.  Rows of a plane are contiguous, so a copy
+// takes a BAND of R consecutive rows of one source (>= 4 KiB) and the rows
+// are told apart at the read.
+//
+// One ring slot = one band of R (a power of two) output rows of the plane:
+//   [0, 16)   one word per source: element position, in the source's area, of
+//             the window of output item 0 of the band's first row.  Row rr of
+//             the band lies rr * W elements further on (further back in a
+//             vertically flipped source); output item xi begins xi chunks of
+//             16 bytes further on or, in a horizontally flipped source,
+//             further back (its eight pixels then in reverse order: register
+//             naming).  Position >> 3 is the chunk, & 7 the window's offset.
+//   [16, 20)  byte position of the band's first truth byte in the truth area
+//   then per source: 16 bytes of headroom (a flipped row's partial item begins
+//             before the row), the copied vectors, 16 bytes spare
+//   then the truth bytes' vectors + 32 bytes spare
+// The last item of a row with W % 8 != 0 holds W % 8 real pixels and then
+// whatever lies behind (or, flipped, before) the row: not counted
+// (finish_item nvalid).
+//
+// Pipeline: a full / empty mbarrier pair per slot, four slots.  Lanes 0 .. NS
+// of the last warp are the producer (wait for a slot to be empty, write its
+// header, issue one copy each: the sources and the truth bytes); the other
+// warps take 32 consecutive items of the unit at a time from a shared
+// counter, wait for the (at most two) bands they lie in, read their words and
+// release the bands (one arrive per warp and band, counted in items).
+#include "seg_hist_guarded.cuh"
+
+namespace mlc {
+
+constexpr int kRowsSlots = 4;
+constexpr int kRowsThreads = 512;
+constexpr uint32_t kRowsSmem = 112u * 1024u;  // dynamic, two CTAs per SM
+constexpr uint32_t kRowsRing = 80u * 1024u;   // of which the ring may take
+
+struct RowGeom {
+  int ipt;              // items per row, the partial last one included
+  int nvalid_tail;      // pixels of a row's last item (8: it is a full one)
+  uint32_t ipt_magic;   // floor(2^32 / ipt) + 1
+  int log_r;            // rows per band = 1 << log_r
+  uint32_t pitch;       // bytes of one source's area in a slot
+  uint32_t gt_off;      // byte offset of the truth area in a slot
+  uint32_t slot_bytes;
+  int rows_per_unit;
+  uint32_t smem_bytes;  // dynamic shared memory of the launch
+};
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_n(uint32_t bar, uint32_t n) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(n)
+               : "memory");
+}
+// (the time hint lets the hardware park the warp until the phase completes:
+// without it the waiting warps polled at full rate - ncu: half of all issued
+// instructions - and starved the producer warp of issue slots)
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+      "@!p bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity), "r"(100000u)
+      : "memory");
+}
+// `bytes` (a multiple of 16) from 16-byte aligned global memory to shared
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src,
+                                         uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1], %2, [%3];" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void st_shared_u4(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+__shared__ unsigned int s_rows_next;  // next unassigned item of the CTA's unit
+
+struct RowRing {
+  uint32_t bar_sa;  // full[s] at + 16 s, empty[s] at + 16 s + 8
+  uint32_t a_sa;    // slot s at + s * slot_bytes
+};
+
+template <int NS>
+__device__ __forceinline__ void rows_produce(const HistArgs &a,
+                                             const RowGeom &g,
+                                             const RowRing &ring, uint32_t plane,
+                                             int row0, int nrows) {
+  constexpr unsigned kMask = (2u << NS) - 1u;  // lanes 0 .. NS
+  const int j = threadIdx.x & 31;
+  if (j > NS) return;
+  const int H = a.H, W = a.W, R = 1 << g.log_r;
+  const size_t plane_off = (size_t)plane * a.plane_px;
+  // lane j < NS: source j; lane NS: the truth bytes
+  const int xf = j < NS ? a.src.xf[j] : 0;
+  const bool vf = xf & MLC_XF_VFLIP;
+  const uint32_t esz = j < NS ? 2u : 1u;
+  const uintptr_t base =
+      j < NS ? reinterpret_cast<uintptr_t>(
+                   static_cast<const __half *>(a.src.ptr[j]) + plane_off)
+             : reinterpret_cast<uintptr_t>(a.gt + plane_off);
+  const uint32_t dst_off = j < NS ? 32u + (uint32_t)j * g.pitch + 16u : g.gt_off;
+  const uint32_t pos0 = (xf & MLC_XF_HFLIP) ? (uint32_t)(W - 8) : 0u;
+  int slot = 0;
+  uint32_t round = 0;
+  for (int r = 0; r < nrows; r += R) {
+    const int nr = min(R, nrows - r), yb = row0 + r;
+    const uint32_t slot_sa = ring.a_sa + slot * g.slot_bytes;
+    const uint32_t full = ring.bar_sa + slot * 16u;
+    if (round > 0) mbar_wait(full + 8u, (round - 1u) & 1u);
+    // the band's rows of this source are contiguous; the lowest one is
+    const int ys_lo = vf ? H - yb - nr : yb;
+    const uintptr_t p = base + (size_t)ys_lo * W * esz;
+    const uintptr_t from = p & ~(uintptr_t)15;
+    const uint32_t bytes =
+        (uint32_t)(((p + (uint32_t)(nr * W) * esz + 15u) & ~(uintptr_t)15) - from);
+    uint32_t total = bytes;
+#pragma unroll
+    for (int d = 1; d <= 4; d <<= 1) {
+      const uint32_t o = __shfl_xor_sync(kMask, total, d, 8);
+      total += (j ^ d) <= NS ? o : 0u;
+    }
+    if (j < NS)
+      st_shared_u32(slot_sa + 4u * j, (uint32_t)(p & 15) / 2u + pos0 +
+                                          (vf ? (uint32_t)((nr - 1) * W) : 0u));
+    else
+      st_shared_u32(slot_sa + 16u, (uint32_t)(p & 15));
+    __syncwarp(kMask);  // the header is written before the barrier is armed
+    if (j == 0) mbar_expect_tx(full, total);
+    bulk_g2s(slot_sa + dst_off, reinterpret_cast<const void *>(from), bytes,
+             full);
+    if (++slot == kRowsSlots) {
+      slot = 0;
+      ++round;
+    }
+  }
+}
+
+template <int NS, bool BINS, int REV>
+__device__ __forceinline__ void rows_consume(const HistArgs &a,
+                                             const RowGeom &g,
+                                             const RowRing &ring, uint32_t plane,
+                                             int row0, int nrows,
+                                             uint32_t slot) {
+  const int lane = threadIdx.x & 31;
+  const int ipt = g.ipt, W = a.W;
+  const int n_items = nrows * ipt;
+  const uint32_t next_sa = (uint32_t)__cvta_generic_to_shared(&s_rows_next);
+  const size_t plane_off = (size_t)plane * a.plane_px;
+  int guard = 0;  // always >= 0, not provably so (see pf_unit)
+  while (true) {
+    uint32_t nb = 0;
+    if (lane == 0)
+      asm volatile("atom.shared.add.u32 %0, [%1], 32;"
+                   : "=r"(nb)
+                   : "r"(next_sa + (((uint32_t)guard >> 31) << 2))
+                   : "memory");
+    nb = __shfl_sync(0xffffffffu, nb, 0);
+    if ((int)nb >= n_items) break;
+    const int it = (int)nb + lane;
+    guard = it;
+    const bool active = it < n_items;
+    const int itc = active ? it : n_items - 1;
+    const int r = (int)__umulhi((uint32_t)itc, g.ipt_magic);
+    const int xi = itc - r * ipt;
+    const int band = r >> g.log_r, rr = r & ((1 << g.log_r) - 1);
+    const int sl = band & (kRowsSlots - 1);
+    const uint32_t full = ring.bar_sa + sl * 16u;
+    mbar_wait(full, (uint32_t)(band / kRowsSlots) & 1u);
+    const uint32_t slot_sa = ring.a_sa + sl * g.slot_bytes;
+    uint32_t w[4][4];
+    const uint4 head = lds_u4(slot_sa);
+    const uint32_t hw[4] = {head.x, head.y, head.z, head.w};
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      const bool rev = REV >= 0 ? ((REV >> j) & 1) : ((a.g_rev >> j) & 1u);
+      // g_cy: +W, or -W in a vertically flipped source
+      const uint32_t pos = hw[j] + (uint32_t)(rr * a.g_cy[j]);
+      const uint32_t lo_sa = slot_sa + 48u + j * g.pitch + (pos >> 3) * 16u +
+                             (rev ? -(uint32_t)xi * 16u : (uint32_t)xi * 16u);
+      const uint4 lo4 = lds_u4(lo_sa), hi4 = lds_u4(lo_sa + 16u);
+      const uint32_t t[8] = {lo4.x, lo4.y, lo4.z, lo4.w,
+                             hi4.x, hi4.y, hi4.z, hi4.w};
+      window8_select(t, pos & 7u, w[j]);
+      if (REV < 0 && rev) reverse8(w[j]);
+    }
+    uint2 gt;
+    {
+      const uint32_t gb = lds_u32(slot_sa + 16u) + (uint32_t)(rr * W + xi * 8);
+      const uint32_t ga = slot_sa + g.gt_off + (gb & ~3u), sh = (gb & 3u) * 8u;
+      const uint32_t t0 = lds_u32(ga), t1 = lds_u32(ga + 4u),
+                     t2 = lds_u32(ga + 8u);
+      gt = make_uint2(__funnelshift_r(t0, t1, sh), __funnelshift_r(t1, t2, sh));
+    }
+    // release the bands: one arrive per warp and band, counted in items (a
+    // chunk of 32 items lies in at most two rows: ipt >= 32)
+    __syncwarp();
+    {
+      const int b_first = __shfl_sync(0xffffffffu, band, 0);
+      const unsigned in_a =
+          __ballot_sync(0xffffffffu, active && band == b_first);
+      const unsigned in_b =
+          __ballot_sync(0xffffffffu, active && band != b_first);
+      if (lane == 0) mbar_arrive_n(full + 8u, (uint32_t)__popc(in_a));
+      if (in_b && lane == 31 - __clz((int)in_b))
+        mbar_arrive_n(full + 8u, (uint32_t)__popc(in_b));
+    }
+    if (active) {
+      float q[8];
+      uint32_t dmax = 0u;
+      if constexpr (REV >= 0)
+        group_sum<NS, REV & ((1 << NS) - 1)>(w, true, q, dmax);
+      else
+        group_sum<NS, 0>(w, true, q, dmax);
+      const int y = row0 + r, x0 = xi * 8;
+      finish_item<true, BINS ? 2 : 0>(
+          a, q, dmax, gt, slot, plane, it, plane_off + (size_t)y * W + (size_t)x0,
+          0u, 0u, 0, -y - 1, x0, xi == ipt - 1 ? g.nvalid_tail : 8);
+    }
+  }
+}
+
+template <int NS, bool BINS>
+__global__ void __launch_bounds__(kRowsThreads, 1024 / kRowsThreads)
+seg_hist_guarded_rows(const __grid_constant__ HistArgs a,
+                      const __grid_constant__ RowGeom g) {
+  extern __shared__ __align__(128) uint32_t gsm[];
+  constexpr int NT = kRowsThreads;
+  const int B = a.B, nbins = B + 1;
+  const uint32_t gsm_sa = (uint32_t)__cvta_generic_to_shared(gsm);
+  const uint32_t end_sa = gsm_sa + g.smem_bytes;
+  const uint32_t cnt_bytes = (uint32_t)nbins * 128u + (uint32_t)B * 4u;
+  // counters + thresholds on the last 16 KiB boundary that leaves room for
+  // them; barriers and ring slots before them (the host sized the slots for
+  // the 80 KiB that are there at least)
+  const uint32_t cnt_sa = (end_sa - cnt_bytes) & ~16383u;
+  RowRing ring;
+  ring.bar_sa = (gsm_sa + 15u) & ~15u;
+  ring.a_sa = (ring.bar_sa + kRowsSlots * 16u + 127u) & ~127u;
+  uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
+  float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
+  for (int i = threadIdx.x; i < nbins * 32; i += NT) cnt[i] = 0;
+  for (int i = threadIdx.x; i < B; i += NT) thr[i] = a.thr.v[i];
+  if (threadIdx.x == 0) {
+    s_rows_next = 0u;
+    for (int s = 0; s < kRowsSlots; ++s) {
+      mbar_init(ring.bar_sa + s * 16u, 1u);
+      mbar_init(ring.bar_sa + s * 16u + 8u, (uint32_t)(g.ipt << g.log_r));
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const uint32_t plane = blockIdx.x, sub = blockIdx.y, upp = gridDim.y;
+  const int row0 = (int)sub * g.rows_per_unit;
+  const int nrows = max(0, min(a.H, row0 + g.rows_per_unit) - row0);
+  const bool fits = ring.a_sa + kRowsSlots * g.slot_bytes <= cnt_sa;
+  if (!fits) __trap();
+  if (threadIdx.x >= NT - 32) {
+    rows_produce<NS>(a, g, ring, plane, row0, nrows);
+  } else {
+    const uint32_t slot = cnt_sa | ((threadIdx.x & 31) * 4);
+    constexpr int kAll = (1 << NS) - 1;
+    const int rev = (int)(a.g_rev & kAll);
+    if (rev == 0)
+      rows_consume<NS, BINS, 0>(a, g, ring, plane, row0, nrows, slot);
+    else if (rev == (0xA & kAll))
+      rows_consume<NS, BINS, 0xA & kAll>(a, g, ring, plane, row0, nrows, slot);
+    else if (rev == (0x5 & kAll))
+      rows_consume<NS, BINS, 0x5 & kAll>(a, g, ring, plane, row0, nrows, slot);
+    else if (rev == kAll)
+      rows_consume<NS, BINS, kAll>(a, g, ring, plane, row0, nrows, slot);
+    else
+      rows_consume<NS, BINS, -1>(a, g, ring, plane, row0, nrows, slot);
+  }
+  uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
+  flush_bins(cnt, nbins, out, upp > 1);
+}
+
+// Requires 16-byte aligned source tensors (every vector that is copied then
+// contains at least one byte of its tensor), W >= 249 (a chunk of 32 items
+// lies in at most two rows), no transpose.
+bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
+  *rc = MLC_OK;
+  const int S = a.src.n, W = a.W, H = a.H;
+  if (S < 2 || S > 4) return false;
+  if (a.src.any_xf & MLC_XF_TRANSPOSE) return false;
+  for (int k = 0; k < S; ++k)
+    if (((uintptr_t)a.src.ptr[k] % 16) != 0) return false;
+  RowGeom g;
+  g.ipt = (W + 7) / 8;
+  if (g.ipt < 32) return false;
+  if ((long long)H * g.ipt * g.ipt >= (1ll << 32) || a.n_planes >= (1ll << 31) ||
+      a.units_per_plane >= 65536)
+    return false;
+  g.nvalid_tail = (W & 7) ? (W & 7) : 8;
+  g.ipt_magic = (uint32_t)((1ull << 32) / (unsigned)g.ipt + 1);
+  // rows per band: the largest power of two whose four slots fit the ring
+  // (a source's area: 16 bytes of headroom, the vectors that enclose the
+  // band's rows, 16 bytes spare for the second vector of the last window)
+  g.log_r = -1;
+  for (int lr = 0; lr <= 6; ++lr) {
+    const uint32_t R = 1u << lr;
+    const uint32_t pitch = 16u * ((2u * W * R + 30u + 15u) / 16u + 2u);
+    const uint32_t gt_off = 32u + (uint32_t)S * pitch;
+    const uint32_t slot =
+        (gt_off + 16u * ((W * R + 15u + 15u) / 16u + 3u) + 127u) / 128u * 128u;
+    if (kRowsSlots * slot > kRowsRing) break;
+    g.log_r = lr;
+    g.pitch = pitch;
+    g.gt_off = gt_off;
+    g.slot_bytes = slot;
+  }
+  if (g.log_r < 0) return false;
+  g.smem_bytes = kRowsSmem;
+  g.rows_per_unit = (H + a.units_per_plane - 1) / a.units_per_plane;
+  if (!guarded_grid(a)) return false;
+  a.g_rev = 0u;
+  for (int k = 0; k < S; ++k) {
+    if (a.src.xf[k] & MLC_XF_HFLIP) a.g_rev |= 1u << k;
+    a.g_cy[k] = (a.src.xf[k] & MLC_XF_VFLIP) ? -W : W;
+  }
+  const bool bins = a.bins != nullptr;
+  void (*k)(HistArgs, RowGeom) =
+      S == 2   ? (bins ? seg_hist_guarded_rows<2, true>
+                       : seg_hist_guarded_rows<2, false>)
+      : S == 3 ? (bins ? seg_hist_guarded_rows<3, true>
+                       : seg_hist_guarded_rows<3, false>)
+               : (bins ? seg_hist_guarded_rows<4, true>
+                       : seg_hist_guarded_rows<4, false>);
+  const cudaError_t ea = cudaFuncSetAttribute(
+      k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem_bytes);
+  if (ea != cudaSuccess) {
+    *rc = cuda_fail(ea, "cudaFuncSetAttribute(seg_hist_guarded_rows)");
+    return true;
+  }
+  k<<<dim3((unsigned)a.n_planes, (unsigned)a.units_per_plane), kRowsThreads,
+      g.smem_bytes, st>>>(a, g);
+  const cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) *rc = cuda_fail(err, "seg_hist_guarded_rows");
+  return true;
+}
+
+}  // namespace mlc

@@ -286,6 +286,54 @@ def test_guarded_unaligned_rows(ops, shape, n_src, flips):
     check(ops, seen, tags, gt.to(DEV), oracle.threshold_grid(100))
 
 
+@pytest.mark.parametrize('shape', [(3, 3, 9, 263), (5, 4, 4, 250),
+                                   (2, 9, 3, 257), (1, 1, 6, 249),
+                                   (1, 2, 3, 601), (1, 1, 2, 1001),
+                                   (2, 2, 40, 525), (1, 33, 2, 255)])
+@pytest.mark.parametrize('n_src,flips', [(4, True), (2, True), (3, False)])
+def test_guarded_tma_rows(ops, shape, n_src, flips):
+    """Rows of >= 249 pixels of any width (csrc/seg_hist_guarded_rows.cu: rows
+    staged by tensor-map copies): partial last items, planes in the full
+    8 / 16-plane groups and in the last, shorter group, 1 - 4 copies per row,
+    more rows than ring slots."""
+    n, c, h, w = shape
+    srcs, gt = synth_seg(n, c, h, w, seed=h + w + n_src, n_src=n_src)
+    tags = [FLIPS[k % 4] if flips else [] for k in range(n_src)]
+    seen = [forward_tta(s, t).to(DEV) for s, t in zip(srcs, tags)]
+    check(ops, seen, tags, gt.to(DEV), oracle.threshold_grid(100))
+
+
+def test_guarded_tma_rows_special_values_and_tensor_ends(ops):
+    """NaN / inf / huge values next to row ends, and tensors that end exactly
+    where their allocation ends (a copy that runs over the end of the tensor
+    must be zero-filled by the copy engine, not read)."""
+    g = torch.Generator().manual_seed(5)
+    n, c, h, w = 1, 3, 11, 253
+    base = torch.randn((n, c, h, w), generator=g) * 4
+    base[0, 0, 3, 252] = float('nan')
+    base[0, 0, 4, 0] = float('inf')
+    base[0, 1, 0, 0] = float('-inf')
+    base[0, 2, 10, 252] = 65504.0
+    base[0, 2, 10, 248] = float('nan')
+    base[0, 1, 10, 240:248] = -30.0
+    srcs = [(base + 0.25 * k).half() for k in range(4)]
+    gt = (torch.rand((n, c, h, w), generator=g) < 0.3).to(torch.uint8)
+    seen = []
+    for s, t in zip(srcs, FLIPS):
+        f = forward_tta(s, t)
+        # the tensor's last byte is the allocation's last byte (512-byte
+        # granules of the caching allocator: pick the offset accordingly)
+        numel = f.numel()
+        granule = 256
+        total = (numel + granule - 1) // granule * granule
+        buf = torch.empty(total, dtype=torch.float16, device=DEV)
+        off = (total - numel) // 8 * 8
+        view = buf[off:off + numel].view(f.shape)
+        view.copy_(f)
+        seen.append(view)
+    check(ops, seen, FLIPS, gt.to(DEV), oracle.threshold_grid(100))
+
+
 def test_guarded_unaligned_special_values(ops):
     """NaN / inf / huge values in windows that straddle vectors and rows."""
     g = torch.Generator().manual_seed(3)
