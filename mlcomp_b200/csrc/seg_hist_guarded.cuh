@@ -223,6 +223,19 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
     }
   }
   // bin = bits 16..22 of fx (the exponent field reads 0x4300 + bin)
+  if (!BINS && nvalid < 8) {
+    // pixels beyond the row go to bin 127: a row of counters that the caller
+    // provides and never flushes (a few instructions for the lanes that hold a
+    // row's last item, instead of a second counting path: that one was taken,
+    // divergently, by every second warp)
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i >= nvalid) fx[i] = 0x437F0000u;
+    const uint64_t keep = ~0ull >> (64 - 8 * nvalid);  // nvalid >= 1
+    g.x &= (uint32_t)keep;
+    g.y &= (uint32_t)(keep >> 32);
+    nvalid = 8;
+  }
   if (skip > 0 || nvalid < 8) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {

@@ -28,14 +28,13 @@
 // are told apart at the read.
 //
 // One ring slot = one band of R (a power of two) output rows of the plane:
-//   [0, 16)   one word per source: element position, in the source's area, of
-//             the window of output item 0 of the band's first row.  Row rr of
-//             the band lies rr * W elements further on (further back in a
-//             vertically flipped source); output item xi begins xi chunks of
-//             16 bytes further on or, in a horizontally flipped source,
-//             further back (its eight pixels then in reverse order: register
-//             naming).  Position >> 3 is the chunk, & 7 the window's offset.
-//   [16, 20)  byte position of the band's first truth byte in the truth area
+//   32 bytes per row of the band: one word per source - (byte offset, from
+//             the slot, of the 16-byte chunk in which the window of the row's
+//             output item 0 begins) << 3 | element offset of the window in
+//             it - and the byte offset of the row's first truth byte.  Output
+//             item xi begins xi chunks further on or, in a horizontally
+//             flipped source, further back (its eight pixels then in reverse
+//             order: register naming).
 //   then per source: 16 bytes of headroom (a flipped row's partial item begins
 //             before the row), the copied vectors, 16 bytes spare
 //   then the truth bytes' vectors + 32 bytes spare
@@ -56,7 +55,7 @@ namespace mlc {
 constexpr int kRowsSlots = 4;
 constexpr int kRowsThreads = 512;
 constexpr uint32_t kRowsSmem = 112u * 1024u;  // dynamic, two CTAs per SM
-constexpr uint32_t kRowsRing = 80u * 1024u;   // of which the ring may take
+constexpr uint32_t kRowsRing = 78u * 1024u;   // of which the ring may take
 
 struct RowGeom {
   int ipt;              // items per row, the partial last one included
@@ -121,25 +120,30 @@ struct RowRing {
   uint32_t a_sa;    // slot s at + s * slot_bytes
 };
 
+// All 32 lanes of the producer warp take part: lane = 8 * q + j serves copy j
+// (j < NS: source j; j == NS: the truth bytes; j > NS: idle) - the lanes with
+// q == 0 issue the copies, lane (q, j) writes the header words of the band's
+// rows q, q + 4, ...  (The warp shares its scheduler's issue slots with seven
+// busy consumer warps: a version whose copy lanes also looped over the rows'
+// header words fell behind the consumers.)
 template <int NS>
 __device__ __forceinline__ void rows_produce(const HistArgs &a,
                                              const RowGeom &g,
                                              const RowRing &ring, uint32_t plane,
                                              int row0, int nrows) {
-  constexpr unsigned kMask = (2u << NS) - 1u;  // lanes 0 .. NS
-  const int j = threadIdx.x & 31;
-  if (j > NS) return;
+  const int lane = threadIdx.x & 31, j = lane & 7, q = lane >> 3;
   const int H = a.H, W = a.W, R = 1 << g.log_r;
   const size_t plane_off = (size_t)plane * a.plane_px;
-  // lane j < NS: source j; lane NS: the truth bytes
-  const int xf = j < NS ? a.src.xf[j] : 0;
+  const bool src = j < NS, used = j <= NS;
+  const int xf = src ? a.src.xf[j] : 0;
   const bool vf = xf & MLC_XF_VFLIP;
-  const uint32_t esz = j < NS ? 2u : 1u;
+  const uint32_t esz = src ? 2u : 1u;
   const uintptr_t base =
-      j < NS ? reinterpret_cast<uintptr_t>(
-                   static_cast<const __half *>(a.src.ptr[j]) + plane_off)
-             : reinterpret_cast<uintptr_t>(a.gt + plane_off);
-  const uint32_t dst_off = j < NS ? 32u + (uint32_t)j * g.pitch + 16u : g.gt_off;
+      src ? reinterpret_cast<uintptr_t>(
+                static_cast<const __half *>(a.src.ptr[j]) + plane_off)
+          : reinterpret_cast<uintptr_t>(a.gt + plane_off);
+  const uint32_t dst_off =
+      src ? (32u << g.log_r) + (uint32_t)j * g.pitch + 16u : g.gt_off;
   const uint32_t pos0 = (xf & MLC_XF_HFLIP) ? (uint32_t)(W - 8) : 0u;
   int slot = 0;
   uint32_t round = 0;
@@ -153,22 +157,29 @@ __device__ __forceinline__ void rows_produce(const HistArgs &a,
     const uintptr_t p = base + (size_t)ys_lo * W * esz;
     const uintptr_t from = p & ~(uintptr_t)15;
     const uint32_t bytes =
-        (uint32_t)(((p + (uint32_t)(nr * W) * esz + 15u) & ~(uintptr_t)15) - from);
+        used ? (uint32_t)(((p + (uint32_t)(nr * W) * esz + 15u) & ~(uintptr_t)15) -
+                          from)
+             : 0u;
     uint32_t total = bytes;
 #pragma unroll
-    for (int d = 1; d <= 4; d <<= 1) {
-      const uint32_t o = __shfl_xor_sync(kMask, total, d, 8);
-      total += (j ^ d) <= NS ? o : 0u;
+    for (int d = 1; d <= 4; d <<= 1)
+      total += __shfl_xor_sync(0xffffffffu, total, d, 8);
+    for (int rr = q; rr < nr; rr += 4) {
+      // row rr of the band is the (nr - 1 - rr)-th of the copy when flipped
+      const uint32_t at = (uint32_t)((vf ? nr - 1 - rr : rr) * W);
+      if (src) {
+        const uint32_t pos = (uint32_t)(p & 15) / 2u + pos0 + at;
+        st_shared_u32(slot_sa + 32u * rr + 4u * j,
+                      ((dst_off + (pos >> 3) * 16u) << 3) | (pos & 7u));
+      } else if (used) {
+        st_shared_u32(slot_sa + 32u * rr + 16u, dst_off + (uint32_t)(p & 15) + at);
+      }
     }
-    if (j < NS)
-      st_shared_u32(slot_sa + 4u * j, (uint32_t)(p & 15) / 2u + pos0 +
-                                          (vf ? (uint32_t)((nr - 1) * W) : 0u));
-    else
-      st_shared_u32(slot_sa + 16u, (uint32_t)(p & 15));
-    __syncwarp(kMask);  // the header is written before the barrier is armed
-    if (j == 0) mbar_expect_tx(full, total);
-    bulk_g2s(slot_sa + dst_off, reinterpret_cast<const void *>(from), bytes,
-             full);
+    __syncwarp();  // the header is written before the barrier is armed
+    if (lane == 0) mbar_expect_tx(full, total);
+    if (q == 0 && used)
+      bulk_g2s(slot_sa + dst_off, reinterpret_cast<const void *>(from), bytes,
+               full);
     if (++slot == kRowsSlots) {
       slot = 0;
       ++round;
@@ -209,41 +220,39 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
     mbar_wait(full, (uint32_t)(band / kRowsSlots) & 1u);
     const uint32_t slot_sa = ring.a_sa + sl * g.slot_bytes;
     uint32_t w[4][4];
-    const uint4 head = lds_u4(slot_sa);
+    const uint32_t row_sa = slot_sa + 32u * rr;
+    const uint4 head = lds_u4(row_sa);
     const uint32_t hw[4] = {head.x, head.y, head.z, head.w};
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
       const bool rev = REV >= 0 ? ((REV >> j) & 1) : ((a.g_rev >> j) & 1u);
-      // g_cy: +W, or -W in a vertically flipped source
-      const uint32_t pos = hw[j] + (uint32_t)(rr * a.g_cy[j]);
-      const uint32_t lo_sa = slot_sa + 48u + j * g.pitch + (pos >> 3) * 16u +
+      const uint32_t lo_sa = slot_sa + (hw[j] >> 3) +
                              (rev ? -(uint32_t)xi * 16u : (uint32_t)xi * 16u);
       const uint4 lo4 = lds_u4(lo_sa), hi4 = lds_u4(lo_sa + 16u);
       const uint32_t t[8] = {lo4.x, lo4.y, lo4.z, lo4.w,
                              hi4.x, hi4.y, hi4.z, hi4.w};
-      window8_select(t, pos & 7u, w[j]);
+      window8_select(t, hw[j] & 7u, w[j]);
       if (REV < 0 && rev) reverse8(w[j]);
     }
     uint2 gt;
     {
-      const uint32_t gb = lds_u32(slot_sa + 16u) + (uint32_t)(rr * W + xi * 8);
-      const uint32_t ga = slot_sa + g.gt_off + (gb & ~3u), sh = (gb & 3u) * 8u;
+      const uint32_t gb = lds_u32(row_sa + 16u) + (uint32_t)xi * 8u;
+      const uint32_t ga = slot_sa + (gb & ~3u), sh = (gb & 3u) * 8u;
       const uint32_t t0 = lds_u32(ga), t1 = lds_u32(ga + 4u),
                      t2 = lds_u32(ga + 8u);
       gt = make_uint2(__funnelshift_r(t0, t1, sh), __funnelshift_r(t1, t2, sh));
     }
     // release the bands: one arrive per warp and band, counted in items (a
-    // chunk of 32 items lies in at most two rows: ipt >= 32)
+    // chunk of 32 items lies in at most two rows: ipt >= 32, so in at most
+    // two bands; nb is the same in all lanes)
     __syncwarp();
-    {
-      const int b_first = __shfl_sync(0xffffffffu, band, 0);
-      const unsigned in_a =
-          __ballot_sync(0xffffffffu, active && band == b_first);
-      const unsigned in_b =
-          __ballot_sync(0xffffffffu, active && band != b_first);
-      if (lane == 0) mbar_arrive_n(full + 8u, (uint32_t)__popc(in_a));
-      if (in_b && lane == 31 - __clz((int)in_b))
-        mbar_arrive_n(full + 8u, (uint32_t)__popc(in_b));
+    if (lane == 0) {
+      const int tot = min(32, n_items - (int)nb);
+      const int n_a = min(tot, ((band + 1) << g.log_r) * ipt - (int)nb);
+      mbar_arrive_n(full + 8u, (uint32_t)n_a);
+      if (tot > n_a)
+        mbar_arrive_n(ring.bar_sa + ((band + 1) & (kRowsSlots - 1)) * 16u + 8u,
+                      (uint32_t)(tot - n_a));
     }
     if (active) {
       float q[8];
@@ -269,11 +278,11 @@ seg_hist_guarded_rows(const __grid_constant__ HistArgs a,
   const int B = a.B, nbins = B + 1;
   const uint32_t gsm_sa = (uint32_t)__cvta_generic_to_shared(gsm);
   const uint32_t end_sa = gsm_sa + g.smem_bytes;
-  const uint32_t cnt_bytes = (uint32_t)nbins * 128u + (uint32_t)B * 4u;
-  // counters + thresholds on the last 16 KiB boundary that leaves room for
-  // them; barriers and ring slots before them (the host sized the slots for
-  // the 80 KiB that are there at least)
-  const uint32_t cnt_sa = (end_sa - cnt_bytes) & ~16383u;
+  // counters + thresholds on the last 16 KiB boundary that leaves room for a
+  // full window of 128 rows of counters (row 127 takes the pixels beyond a
+  // row's end: finish_item); barriers and ring slots before them (the host
+  // sized the slots for the 78 KiB that are there at least)
+  const uint32_t cnt_sa = (end_sa - 16384u) & ~16383u;
   RowRing ring;
   ring.bar_sa = (gsm_sa + 15u) & ~15u;
   ring.a_sa = (ring.bar_sa + kRowsSlots * 16u + 127u) & ~127u;
@@ -341,7 +350,7 @@ bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
   for (int lr = 0; lr <= 6; ++lr) {
     const uint32_t R = 1u << lr;
     const uint32_t pitch = 16u * ((2u * W * R + 30u + 15u) / 16u + 2u);
-    const uint32_t gt_off = 32u + (uint32_t)S * pitch;
+    const uint32_t gt_off = 32u * R + (uint32_t)S * pitch;
     const uint32_t slot =
         (gt_off + 16u * ((W * R + 15u + 15u) / 16u + 3u) + 127u) / 128u * 128u;
     if (kRowsSlots * slot > kRowsRing) break;
@@ -355,10 +364,8 @@ bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
   g.rows_per_unit = (H + a.units_per_plane - 1) / a.units_per_plane;
   if (!guarded_grid(a)) return false;
   a.g_rev = 0u;
-  for (int k = 0; k < S; ++k) {
+  for (int k = 0; k < S; ++k)
     if (a.src.xf[k] & MLC_XF_HFLIP) a.g_rev |= 1u << k;
-    a.g_cy[k] = (a.src.xf[k] & MLC_XF_VFLIP) ? -W : W;
-  }
   const bool bins = a.bins != nullptr;
   void (*k)(HistArgs, RowGeom) =
       S == 2   ? (bins ? seg_hist_guarded_rows<2, true>
