@@ -160,8 +160,7 @@ __device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
 // The eight halves that start `off` halves (0..7) into the eight words t[]:
 // two levels of selects move the window to the front word by word, four funnel
 // shifts move it by the odd half.  Branch-free: lanes of a warp that sit in
-// different rows have different offsets, and the eight-way switch of
-// an eight-way switch cost 30 % of the kernel's stall samples in branches.
+// different rows have different offsets, and an eight-way switch cost 30 % of the kernel's stall samples in branches.
 __device__ __forceinline__ void window8_select(const uint32_t (&t)[8],
                                                uint32_t off,
                                                uint32_t (&w)[4]) {

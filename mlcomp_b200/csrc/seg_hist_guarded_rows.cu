@@ -17,7 +17,8 @@
 // copy whose innermost start coordinate is not a multiple of 16 bytes raises
 // "illegal instruction" - tools/_probe/tma_probe.cu - so the copy preserves
 // the address modulo 16 and the residual offset, 0..7 elements, uniform per
-// row and source, is resolved at the read: two LDS.128 and window8_select.)
+// row and source, is resolved at the read: three LDS.64, five selects and
+// four funnel shifts per source.)
 //
 // A bulk copy costs the copy engine a fixed ~129 ns per CTA whatever its size
 // up to 2 KiB (tools/_probe/bulk_rate.cu: 512 B .. 2 KiB copies all take
@@ -28,13 +29,13 @@
 // are told apart at the read.
 //
 // One ring slot = one band of R (a power of two) output rows of the plane:
-//   32 bytes per row of the band: one word per source - (byte offset, from
-//             the slot, of the 16-byte chunk in which the window of the row's
-//             output item 0 begins) << 3 | element offset of the window in
-//             it - and the byte offset of the row's first truth byte.  Output
-//             item xi begins xi chunks further on or, in a horizontally
-//             flipped source, further back (its eight pixels then in reverse
-//             order: register naming).
+//   32 bytes per row of the band: one word per source - byte offset, from
+//             the slot, of the 8-byte granule in which the window of the
+//             row's output item 0 begins | element offset (0..3) of the window
+//             in it - and the byte offset of the row's first truth byte.
+//             Output item xi begins 16 xi bytes further on or, in a
+//             horizontally flipped source, further back (its eight pixels then
+//             in reverse order: register naming).
 //   then per source: 16 bytes of headroom (a flipped row's partial item begins
 //             before the row), the copied vectors, 16 bytes spare
 //   then the truth bytes' vectors + 32 bytes spare
@@ -46,8 +47,8 @@
 // of the last warp are the producer (wait for a slot to be empty, write its
 // header, issue one copy each: the sources and the truth bytes); the other
 // warps take 32 consecutive items of the unit at a time from a shared
-// counter, wait for the (at most two) bands they lie in, read their words and
-// release the bands (one arrive per warp and band, counted in items).
+// counter; a lane waits for the band its item lies in, reads its words and
+// arrives on the band's empty barrier (which counts items).
 #include "seg_hist_guarded.cuh"
 
 namespace mlc {
@@ -170,7 +171,7 @@ __device__ __forceinline__ void rows_produce(const HistArgs &a,
       if (src) {
         const uint32_t pos = (uint32_t)(p & 15) / 2u + pos0 + at;
         st_shared_u32(slot_sa + 32u * rr + 4u * j,
-                      ((dst_off + (pos >> 3) * 16u) << 3) | (pos & 7u));
+                      (dst_off + (pos >> 2) * 8u) | (pos & 3u));
       } else if (used) {
         st_shared_u32(slot_sa + 32u * rr + 16u, dst_off + (uint32_t)(p & 15) + at);
       }
@@ -200,6 +201,9 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
   const size_t plane_off = (size_t)plane * a.plane_px;
   int guard = 0;  // always >= 0, not provably so (see pf_unit)
   while (true) {
+    // (32 items per counter update: with 64 a band's last items were held
+    // longer before their turn and its slot was released later - 0.56
+    // against 0.64 of the HBM peak)
     uint32_t nb = 0;
     if (lane == 0)
       asm volatile("atom.shared.add.u32 %0, [%1], 32;"
@@ -226,12 +230,22 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
       const bool rev = REV >= 0 ? ((REV >> j) & 1) : ((a.g_rev >> j) & 1u);
-      const uint32_t lo_sa = slot_sa + (hw[j] >> 3) +
-                             (rev ? -(uint32_t)xi * 16u : (uint32_t)xi * 16u);
-      const uint4 lo4 = lds_u4(lo_sa), hi4 = lds_u4(lo_sa + 16u);
-      const uint32_t t[8] = {lo4.x, lo4.y, lo4.z, lo4.w,
-                             hi4.x, hi4.y, hi4.z, hi4.w};
-      window8_select(t, hw[j] & 7u, w[j]);
+      // three 8-byte loads from the 8-byte granule the window begins in (a
+      // lane stride of 16 bytes makes them 4 wavefronts each, 12 against the
+      // 8 of two LDS.128 of the enclosing vectors; what is saved is one of
+      // two levels of selects: +2.4 %)
+      const uint32_t off = hw[j] & 3u;
+      const uint32_t q_sa = slot_sa + (hw[j] & ~7u) +
+                            (rev ? -(uint32_t)xi * 16u : (uint32_t)xi * 16u);
+      const uint2 q0 = lds_u2(q_sa), q1 = lds_u2(q_sa + 8u),
+                  q2 = lds_u2(q_sa + 16u);
+      const bool b1 = off & 2u;
+      const uint32_t b[5] = {b1 ? q0.y : q0.x, b1 ? q1.x : q0.y,
+                             b1 ? q1.y : q1.x, b1 ? q2.x : q1.y,
+                             b1 ? q2.y : q2.x};
+      const uint32_t sh = (off & 1u) * 16u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) w[j][k] = __funnelshift_r(b[k], b[k + 1], sh);
       if (REV < 0 && rev) reverse8(w[j]);
     }
     uint2 gt;
@@ -242,18 +256,10 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
                      t2 = lds_u32(ga + 8u);
       gt = make_uint2(__funnelshift_r(t0, t1, sh), __funnelshift_r(t1, t2, sh));
     }
-    // release the bands: one arrive per warp and band, counted in items (a
-    // chunk of 32 items lies in at most two rows: ipt >= 32, so in at most
-    // two bands; nb is the same in all lanes)
-    __syncwarp();
-    if (lane == 0) {
-      const int tot = min(32, n_items - (int)nb);
-      const int n_a = min(tot, ((band + 1) << g.log_r) * ipt - (int)nb);
-      mbar_arrive_n(full + 8u, (uint32_t)n_a);
-      if (tot > n_a)
-        mbar_arrive_n(ring.bar_sa + ((band + 1) & (kRowsSlots - 1)) * 16u + 8u,
-                      (uint32_t)(tot - n_a));
-    }
+    // release the band: every lane for its own item, after its own loads (one
+    // arrive per warp and band, its count computed by lane 0 behind a
+    // __syncwarp, cost 18 issue slots per item against this one: +4.5 %)
+    if (active) mbar_arrive_n(full + 8u, 1u);
     if (active) {
       float q[8];
       uint32_t dmax = 0u;
