@@ -114,10 +114,9 @@ __device__ __forceinline__ void st_shared_u4(uint32_t addr, uint4 v) {
                : "memory");
 }
 
-__shared__ unsigned int s_rows_next;  // next unassigned item of the CTA's unit
-
 struct RowRing {
-  uint32_t bar_sa;  // full[s] at + 16 s, empty[s] at + 16 s + 8
+  uint32_t bar_sa;  // full[s] at + 16 s, empty[s] at + 16 s + 8; behind them
+                    // the next unassigned item of the CTA's unit
   uint32_t a_sa;    // slot s at + s * slot_bytes
 };
 
@@ -197,7 +196,7 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
   const int lane = threadIdx.x & 31;
   const int ipt = g.ipt, W = a.W;
   const int n_items = nrows * ipt;
-  const uint32_t next_sa = (uint32_t)__cvta_generic_to_shared(&s_rows_next);
+  const uint32_t next_sa = ring.bar_sa + kRowsSlots * 16u;
   const size_t plane_off = (size_t)plane * a.plane_px;
   int guard = 0;  // always >= 0, not provably so (see pf_unit)
   while (true) {
@@ -214,10 +213,9 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
     if ((int)nb >= n_items) break;
     const int it = (int)nb + lane;
     guard = it;
-    const bool active = it < n_items;
-    const int itc = active ? it : n_items - 1;
-    const int r = (int)__umulhi((uint32_t)itc, g.ipt_magic);
-    const int xi = itc - r * ipt;
+    if (it >= n_items) continue;  // (the last chunk of a unit)
+    const int r = (int)__umulhi((uint32_t)it, g.ipt_magic);
+    const int xi = it - r * ipt;
     const int band = r >> g.log_r, rr = r & ((1 << g.log_r) - 1);
     const int sl = band & (kRowsSlots - 1);
     const uint32_t full = ring.bar_sa + sl * 16u;
@@ -259,8 +257,8 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
     // release the band: every lane for its own item, after its own loads (one
     // arrive per warp and band, its count computed by lane 0 behind a
     // __syncwarp, cost 18 issue slots per item against this one: +4.5 %)
-    if (active) mbar_arrive_n(full + 8u, 1u);
-    if (active) {
+    mbar_arrive_n(full + 8u, 1u);
+    {
       float q[8];
       uint32_t dmax = 0u;
       if constexpr (REV >= 0)
@@ -291,13 +289,13 @@ seg_hist_guarded_rows(const __grid_constant__ HistArgs a,
   const uint32_t cnt_sa = (end_sa - 16384u) & ~16383u;
   RowRing ring;
   ring.bar_sa = (gsm_sa + 15u) & ~15u;
-  ring.a_sa = (ring.bar_sa + kRowsSlots * 16u + 127u) & ~127u;
+  ring.a_sa = (ring.bar_sa + kRowsSlots * 16u + 16u + 127u) & ~127u;
   uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
   float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
   for (int i = threadIdx.x; i < nbins * 32; i += NT) cnt[i] = 0;
   for (int i = threadIdx.x; i < B; i += NT) thr[i] = a.thr.v[i];
   if (threadIdx.x == 0) {
-    s_rows_next = 0u;
+    st_shared_u32(ring.bar_sa + kRowsSlots * 16u, 0u);
     for (int s = 0; s < kRowsSlots; ++s) {
       mbar_init(ring.bar_sa + s * 16u, 1u);
       mbar_init(ring.bar_sa + s * 16u + 8u, (uint32_t)(g.ipt << g.log_r));

@@ -96,7 +96,7 @@ def c3(n=5546):
     thr = ops.threshold_grid(100)
     out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
     ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, xforms=tags, out=out))
-    report('C3 cloud 4-flip TTA %dx4x350x525 fp16: seg_hist_guarded_un' % n, ms,
+    report('C3 cloud 4-flip TTA %dx4x350x525 fp16: seg_hist_guarded_rows' % n, ms,
            n * c * (h * w * (4 * 2 + 1) + 808), n * c)
 
 
