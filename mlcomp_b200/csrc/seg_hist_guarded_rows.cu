@@ -177,9 +177,11 @@ __device__ __forceinline__ void rows_produce(const HistArgs &a,
     }
     __syncwarp();  // the header is written before the barrier is armed
     if (lane == 0) mbar_expect_tx(full, total);
-    if (q == 0 && used)
+    if (q == 0 && used) {
+      MLC_CHECK_LOAD(reinterpret_cast<const void *>(from), bytes);
       bulk_g2s(slot_sa + dst_off, reinterpret_cast<const void *>(from), bytes,
                full);
+    }
     if (++slot == kRowsSlots) {
       slot = 0;
       ++round;
@@ -367,6 +369,21 @@ bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
   g.smem_bytes = kRowsSmem;
   g.rows_per_unit = (H + a.units_per_plane - 1) / a.units_per_plane;
   if (!guarded_grid(a)) return false;
+#ifdef MLC_BOUNDS_CHECK
+  {  // the copies may take the 16-byte vectors that enclose a tensor's ends
+    BoundsList bl;
+    for (int k = 0; k < S; ++k)
+      bl.add(a.src.ptr[k], ((size_t)a.n_planes * a.plane_px * 2 + 15) / 16 * 16);
+    const uintptr_t g0 = (uintptr_t)a.gt & ~(uintptr_t)15;
+    bl.add(reinterpret_cast<const void *>(g0),
+           ((uintptr_t)a.gt + (size_t)a.n_planes * a.plane_px + 15) / 16 * 16 - g0);
+    const cudaError_t e = bounds_commit(bl, st);
+    if (e != cudaSuccess) {
+      *rc = cuda_fail(e, "bounds_commit");
+      return true;
+    }
+  }
+#endif
   a.g_rev = 0u;
   for (int k = 0; k < S; ++k)
     if (a.src.xf[k] & MLC_XF_HFLIP) a.g_rev |= 1u << k;
