@@ -10,10 +10,29 @@
 // scores are computed exactly as mlc_seg_prob computes them (same max / sum /
 // divide order, same mean rule), so label == argmax(mlc_seg_prob) bit for bit.
 //
-// One thread per pixel.  Per source the three steps of the soft-max (running
-// maximum over the classes, sum of expf(x - max) in class order, the divide)
-// re-read the pixel's class values; they stay in L1 (the working set of a CTA
-// is 256 px x S x C values), so DRAM sees every logit once.
+// Two kernels.  seg_argmax_kernel: one thread per pixel, any geometry, dtype,
+// activation and class count - the exact arithmetic throughout (one accurate
+// expf and one IEEE divide per logit), thread-per-pixel 2-byte loads; 0.15 of
+// the HBM peak.  seg_argmax_items (fp16, 2..8 classes, soft-max or no
+// activation, rows of whole 16-byte items, no transpose): a thread takes an
+// 8-pixel item with one 128-bit load per class and source and decides the
+// arg-max from a GUARDED ESTIMATE of the class scores, as seg_hist_guarded does
+// for the threshold bins:
+//   per source   d_c = x_c - max_c x    (the reference's own fp32 subtraction)
+//                t_c = ex2.approx(d_c * log2 e),  p_c = t_c * rcp.approx(sum t)
+//   score_c = sum over the sources of p_c
+// |score_c - reference sum| < 2^-18 per source for C <= 8 (ex2.approx 2^-22
+// relative, the rounding of d * log2 e at most |d| 2^-23 relative on a term
+// e^d <= 1, C + 1 such terms in p_c, rcp.approx 1 ulp; the reference's expf /
+// sum / divide add 2^-21), and the mean is a monotone map of the sum.  So
+// when the largest estimated score exceeds the second largest by more than
+// S * 2^-15 (an 8-fold margin), the reference's arg-max is that class.  Every
+// other pixel - near-ties, exact ties (which go to the lowest index), NaN /
+// inf anywhere (the estimated scores then do not sum to S) - is evaluated by
+// the exact code of the first kernel (am_scores).  With no activation the
+// scores are plain fp32 sums: computed exactly, no estimate.
+// Counts: per class, the item's eight labels are compared as packed bytes and
+// the T / P / I counts of a thread stay in registers until its chunk ends.
 #include "mlc_common.cuh"
 
 namespace mlc {
@@ -34,6 +53,8 @@ struct ArgmaxArgs {
   int C, H, W;
   int act;
   int chunks_per_img;
+  int items_per_row;  // seg_argmax_items: W / 8
+  float margin;       // seg_argmax_items: S * 2^-15
 };
 
 // element (class plane `pl`, output pixel (y, x)) of source k, un-transformed
@@ -256,6 +277,249 @@ seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
   }
 }
 
+// ---- the item kernel ---------------------------------------------------------
+// exact arg-max of one pixel (the arithmetic of seg_argmax_kernel)
+template <int CT>
+__device__ __noinline__ int am_exact_pixel(const ArgmaxArgs &a, long long pl0,
+                                           size_t px, int y, int x) {
+  return am_scores<__half, CT>(a, pl0, px, y, x);
+}
+
+// 0x80 in every byte of v that is not zero
+__device__ __forceinline__ uint32_t nonzero_bytes(uint32_t v) {
+  return (((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v) & 0x80808080u;
+}
+
+constexpr float kAmLog2e = 1.4426950408889634f;
+
+template <int CT, int ACT>
+__global__ void __launch_bounds__(kAmThreads, 2)
+seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
+  extern __shared__ unsigned int am_smem[];  // [C][3], then [C * C][32]
+  constexpr int C = CT;
+  unsigned int *s_cnt = am_smem;
+  unsigned int *s_cm = am_smem + 3 * C;  // per-lane columns
+  const long long px = (long long)a.H * a.W;
+  const int ipr = a.items_per_row;
+  const long long items = px / 8;
+  const long long n_chunks = a.n_img * a.chunks_per_img;
+  const long long per = (items + a.chunks_per_img - 1) / a.chunks_per_img;
+  const int S = a.src.n;
+  const int lane = threadIdx.x & 31;
+  const bool want_cm = a.cm && a.gt_label;
+
+  for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+    const long long img = chunk / a.chunks_per_img;
+    const long long i0 = (chunk - img * a.chunks_per_img) * per;
+    const long long i1 = min(items, i0 + per);
+    const long long pl0 = img * C;  // class-0 plane of this image
+    for (int i = threadIdx.x; i < 3 * C + (want_cm ? C * C * 32 : 0);
+         i += blockDim.x)
+      am_smem[i] = 0;
+    __syncthreads();
+    uint32_t nT[C], nP[C], nI[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) nT[c] = nP[c] = nI[c] = 0u;
+    for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x) {
+      // (32-bit: a plane has fewer than 2^31 pixels)
+      const int y = (int)((uint32_t)it / (uint32_t)ipr),
+                xi = (int)((uint32_t)it - (uint32_t)y * (uint32_t)ipr);
+      float acc[8][C];
+      for (int k = 0; k < S; ++k) {
+        const int xf = a.src.xf[k];
+        const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
+        const bool hf = xf & MLC_XF_HFLIP;
+        const int xs = hf ? ipr - 1 - xi : xi;
+        const uint4 *p = reinterpret_cast<const uint4 *>(
+                             static_cast<const __half *>(a.src.ptr[k]) +
+                             (size_t)pl0 * px) +
+                         ((size_t)ys * ipr + xs);
+        uint32_t w[C][4];
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const uint4 r = ldg_stream16(p + (size_t)c * (px / 8));
+          w[c][0] = r.x; w[c][1] = r.y; w[c][2] = r.z; w[c][3] = r.w;
+        }
+        if (hf) {  // the item's pixels come in reverse order
+#pragma unroll
+          for (int c = 0; c < C; ++c) {
+            const uint32_t t0 = prmt32(w[c][3], 0u, 0x1032u),
+                           t1 = prmt32(w[c][2], 0u, 0x1032u),
+                           t2 = prmt32(w[c][1], 0u, 0x1032u),
+                           t3 = prmt32(w[c][0], 0u, 0x1032u);
+            w[c][0] = t0; w[c][1] = t1; w[c][2] = t2; w[c][3] = t3;
+          }
+        }
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          float v[2][C];
+#pragma unroll
+          for (int c = 0; c < C; ++c) {
+            const float2 f = __half22float2(
+                *reinterpret_cast<const __half2 *>(&w[c][h]));
+            v[0][c] = f.x;
+            v[1][c] = f.y;
+          }
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            if (ACT == MLC_ACT_SOFTMAX) {
+              float m = v[e][0];
+#pragma unroll
+              for (int c = 1; c < C; ++c) m = fmaxf(m, v[e][c]);
+              float z = 0.f;
+#pragma unroll
+              for (int c = 0; c < C; ++c) {
+                float t;
+                asm("ex2.approx.ftz.f32 %0, %1;"
+                    : "=f"(t)
+                    : "f"((v[e][c] - m) * kAmLog2e));
+                v[e][c] = t;
+                z += t;
+              }
+              float r;
+              asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(z));
+#pragma unroll
+              for (int c = 0; c < C; ++c) v[e][c] *= r;
+            }
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+              acc[2 * h + e][c] = k == 0 ? v[e][c] : acc[2 * h + e][c] + v[e][c];
+          }
+        }
+      }
+      // labels of the eight pixels, one per byte
+      uint32_t lab[2] = {0u, 0u};
+      if (ACT == MLC_ACT_SOFTMAX) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float best = acc[i][0], second = -1.f, tot = acc[i][0];
+          int bc = 0;
+#pragma unroll
+          for (int c = 1; c < C; ++c) {
+            const float v = acc[i][c];
+            tot += v;
+            const bool up = v > best;
+            second = up ? best : fmaxf(second, v);
+            bc = up ? c : bc;
+            best = up ? v : best;
+          }
+          // NaN anywhere makes tot NaN and the test false
+          const bool sane = fabsf(tot - (float)S) < 1e-3f * (float)S;
+          if (!(sane && best - second > a.margin))
+            bc = am_exact_pixel<CT>(a, pl0, (size_t)px, y, xi * 8 + i);
+          lab[i >> 2] |= (uint32_t)bc << (8 * (i & 3));
+        }
+      } else {
+        // plain sums: the reference's own arithmetic (mean8, then numpy's
+        // arg-max order)
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          float wv[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) wv[i] = acc[i][c];
+          mean8(wv, S);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i][c] = wv[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float best = acc[i][0];
+          int bc = 0;
+          bool best_nan = !(best == best);
+#pragma unroll
+          for (int c = 1; c < C; ++c) {
+            const float v = acc[i][c];
+            const bool is_nan = !(v == v);
+            const bool up = !best_nan && (is_nan || v > best);
+            bc = up ? c : bc;
+            best = up ? v : best;
+            best_nan = best_nan || (up && is_nan);
+          }
+          lab[i >> 2] |= (uint32_t)bc << (8 * (i & 3));
+        }
+      }
+      const size_t at = (size_t)img * px + (size_t)it * 8;
+      if (a.label)
+        *reinterpret_cast<uint2 *>(a.label + at) = make_uint2(lab[0], lab[1]);
+      uint2 gl = make_uint2(0u, 0u);
+      if (a.gt_label) gl = ldg_stream8(a.gt_label + at);
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        // bytes equal to c: x ^ c has a zero byte there (labels are < 128)
+        const uint32_t pat = 0x01010101u * (uint32_t)c;
+        const uint32_t e0 = ~nonzero_bytes(lab[0] ^ pat) & 0x80808080u,
+                       e1 = ~nonzero_bytes(lab[1] ^ pat) & 0x80808080u;
+        if (a.onehot)
+          *reinterpret_cast<uint2 *>(a.onehot + (size_t)(pl0 + c) * px +
+                                     (size_t)it * 8) =
+              make_uint2(e0 >> 7, e1 >> 7);
+        if (a.counts) {
+          nP[c] += __popc(e0 | (e1 >> 1));
+          uint32_t t0 = 0u, t1 = 0u;
+          if (a.gt_onehot) {
+            const uint2 g = ldg_stream8(a.gt_onehot + (size_t)(pl0 + c) * px +
+                                        (size_t)it * 8);
+            t0 = nonzero_bytes(g.x);
+            t1 = nonzero_bytes(g.y);
+          } else if (a.gt_label) {
+            t0 = ~nonzero_bytes(gl.x ^ pat) & 0x80808080u;
+            t1 = ~nonzero_bytes(gl.y ^ pat) & 0x80808080u;
+          }
+          nT[c] += __popc(t0 | (t1 >> 1));
+          nI[c] += __popc((t0 & e0) | ((t1 & e1) >> 1));
+        }
+      }
+      if (want_cm) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t g = ((i < 4 ? gl.x : gl.y) >> (8 * (i & 3))) & 0xFFu;
+          const uint32_t b = (lab[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+          // labels outside [0, C) are dropped (sklearn's rule)
+          if (g < (uint32_t)C) atomicAdd(&s_cm[(g * C + b) * 32 + lane], 1u);
+        }
+      }
+    }
+    if (a.counts) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        uint32_t t = nT[c], p = nP[c], q = nI[c];
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) {
+          t += __shfl_xor_sync(0xffffffffu, t, d);
+          p += __shfl_xor_sync(0xffffffffu, p, d);
+          q += __shfl_xor_sync(0xffffffffu, q, d);
+        }
+        if (lane == 0) {
+          if (t) atomicAdd(&s_cnt[c * 3 + 0], t);
+          if (p) atomicAdd(&s_cnt[c * 3 + 1], p);
+          if (q) atomicAdd(&s_cnt[c * 3 + 2], q);
+        }
+      }
+    }
+    __syncthreads();
+    if (a.counts)
+      for (int i = threadIdx.x; i < 3 * C; i += blockDim.x)
+        if (s_cnt[i])
+          atomicAdd(&a.counts[img * 3 * C + i], (unsigned long long)s_cnt[i]);
+    if (want_cm)
+      for (int i = threadIdx.x; i < C * C; i += blockDim.x) {
+        unsigned int v = 0;
+        for (int l = 0; l < 32; ++l) v += s_cm[i * 32 + ((l + i) & 31)];
+        if (v) atomicAdd(&a.cm[i], (unsigned long long)v);
+      }
+    __syncthreads();
+  }
+}
+
+template <int CT>
+static void launch_items(const ArgmaxArgs &a, int grid, size_t smem,
+                         cudaStream_t st) {
+  if (a.act == MLC_ACT_SOFTMAX)
+    seg_argmax_items<CT, MLC_ACT_SOFTMAX><<<grid, kAmThreads, smem, st>>>(a);
+  else
+    seg_argmax_items<CT, MLC_ACT_NONE><<<grid, kAmThreads, smem, st>>>(a);
+}
+
 }  // namespace mlc
 
 using namespace mlc;
@@ -317,6 +581,33 @@ extern "C" int mlc_seg_argmax(const void *const *src_dev_ptrs,
                                 ? n_cls * n_cls : 0)) * 4;
   const long long n_chunks = n_img * a.chunks_per_img;
   const int grid = (int)min(n_chunks, 16ll * sm_count());
+  // the item kernel: fp16, 2..8 classes, rows of whole aligned items
+  bool items = dtype == MLC_F16 && n_cls >= 2 && n_cls <= 8 &&
+               (act == MLC_ACT_SOFTMAX || act == MLC_ACT_NONE) && (W % 8) == 0 &&
+               !(a.src.any_xf & MLC_XF_TRANSPOSE) &&
+               ((uintptr_t)gt_onehot_dev % 8) == 0 &&
+               ((uintptr_t)gt_label_dev % 8) == 0 &&
+               ((uintptr_t)label_dev % 8) == 0 && ((uintptr_t)onehot_dev % 8) == 0;
+  for (int i = 0; i < n_src; ++i)
+    items = items && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
+  if (items) {
+    a.items_per_row = W / 8;
+    a.margin = (float)n_src * 3.0517578125e-5f;  // S * 2^-15
+    const size_t ismem =
+        (size_t)(3 * n_cls + (cm_dev ? n_cls * n_cls * 32 : 0)) * 4;
+    const int igrid = (int)min(n_chunks, 2ll * sm_count());
+    switch (n_cls) {
+      case 2: launch_items<2>(a, igrid, ismem, st); break;
+      case 3: launch_items<3>(a, igrid, ismem, st); break;
+      case 4: launch_items<4>(a, igrid, ismem, st); break;
+      case 5: launch_items<5>(a, igrid, ismem, st); break;
+      case 6: launch_items<6>(a, igrid, ismem, st); break;
+      case 7: launch_items<7>(a, igrid, ismem, st); break;
+      default: launch_items<8>(a, igrid, ismem, st); break;
+    }
+    MLC_LAUNCH_CHECK("seg_argmax_items");
+    return MLC_OK;
+  }
   void (*k)(ArgmaxArgs);
 #define MLC_AM(T)                                                      \
   (n_cls == 2   ? seg_argmax_kernel<T, 2>                               \

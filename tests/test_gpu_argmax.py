@@ -81,6 +81,51 @@ def test_argmax_matches_oracle(ops, dtype, c, shape, tags):
         assert torch.equal(out2['counts'], out['counts'])
 
 
+@pytest.mark.parametrize('c', [2, 3, 5, 6, 7, 8])
+@pytest.mark.parametrize('n_src', [1, 2, 3])
+def test_argmax_item_kernel_ties_and_near_ties(ops, c, n_src):
+    """seg_argmax_items (fp16, rows of whole items, 2..8 classes): logits on a
+    coarse grid make exact ties and near-ties frequent, so both the decided
+    and the exactly evaluated pixels are exercised; labels must equal the
+    arg-max of the device's exact scores, counts and confusion the oracle's."""
+    rng = np.random.default_rng(100 * c + n_src)
+    n, h, w = 2, 12, 64
+    tags = [[], ['hflip'], ['hflip', 'vflip']][:n_src]
+    base = rng.integers(-3, 4, (n, c, h, w)).astype(np.float32) * 0.5
+    base[0, :, 0, :8] = 0.0                      # all classes equal
+    base[0, :, 1, :8] = 11.0                     # ... and saturated
+    base[1, 0, 2, 3] = np.float32('nan')
+    base[1, c - 1, 2, 4] = np.float32('inf')
+    base[1, :, 2, 5] = np.float32('-inf')
+    base[1, 1, 3, :] += 2.0 ** -10               # one fp16 ulp at 1.0 or less
+    srcs = [torch.from_numpy(base + (rng.integers(0, 2, base.shape) * 2.0 ** -9
+                                     if k else 0)).half()
+            for k in range(n_src)]
+    seen = [forward_tta(s_, t) for s_, t in zip(srcs, tags)]
+    dev = [s_.to(DEV) for s_ in seen]
+    gt_label = torch.from_numpy(rng.integers(0, c + 1, (n, h, w)).astype(np.uint8))
+    for act in ('softmax', None):
+        own = ops.seg_prob(dev, xforms=tags, activation=act).cpu().numpy()
+        want = np.zeros((n, h, w), np.int64)
+        # numpy's order on the device's exact scores: first NaN, else first max
+        want = np.argmax(own, axis=1)
+        out = ops.seg_argmax(dev, tags, act, gt_label=gt_label.to(DEV),
+                             want_onehot=True, want_counts=True,
+                             want_confusion=True)
+        label = out['label'].cpu().numpy()
+        assert np.array_equal(label, want), int((label != want).sum())
+        onehot = out['onehot'].cpu().numpy()
+        for j in range(c):
+            assert np.array_equal(onehot[:, j], (label == j).astype(np.uint8))
+        g1 = np.stack([(gt_label.numpy() == j) for j in range(c)], axis=1)
+        assert np.array_equal(out['counts'].cpu().numpy(),
+                              oracle.onehot_counts(label, g1))
+        keep = gt_label.numpy() < c
+        cm = np.bincount(gt_label.numpy()[keep].astype(np.int64) * c +
+                         label[keep], minlength=c * c).reshape(c, c)
+        assert np.array_equal(out['confusion'].cpu().numpy(), cm)
+
+
 def test_argmax_nan_and_ties(ops):
     """numpy order: first NaN wins, else first maximum."""
     x = torch.zeros((1, 4, 1, 8), dtype=torch.float32)

@@ -163,7 +163,7 @@ def am(n=1024):
     tags = [[], ['hflip']]
     ms = timeit(lambda: ops.seg_argmax(srcs, tags, 'softmax', gt_onehot=gt,
                                        want_counts=True))
-    report('arg-max %dx5x256x1600 fp16 x 2 flips, softmax: seg_argmax_kernel'
+    report('arg-max %dx5x256x1600 fp16 x 2 flips, softmax: seg_argmax_items'
            % n, ms, n * c * h * w * (2 * 2 + 1) + n * h * w, n * c)
 
 
