@@ -292,11 +292,42 @@ __device__ __forceinline__ uint32_t nonzero_bytes(uint32_t v) {
 
 constexpr float kAmLog2e = 1.4426950408889634f;
 
+__device__ __forceinline__ void am_cp16(uint32_t dst, const void *src) {
+  MLC_CHECK_LOAD(src, 16);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src)
+               : "memory");
+}
+__device__ __forceinline__ void am_cp8(uint32_t dst, const void *src) {
+  MLC_CHECK_LOAD(src, 8);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src)
+               : "memory");
+}
+__device__ __forceinline__ uint4 am_lds16(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 am_lds8(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y)
+               : "r"(addr));
+  return v;
+}
+
+// Every thread copies its NEXT item - one 16-byte vector per class and source,
+// the truth bytes - with cp.async into its own shared-memory slots while it
+// works on the current one (two stages; no registers are held by loads in
+// flight: with direct loads the kernel ran at 4 warps per scheduler, 128
+// registers each, and 60 % of the issue slots had no eligible warp).
 template <int CT, int ACT>
 __global__ void __launch_bounds__(kAmThreads, 2)
 seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
-  extern __shared__ unsigned int am_smem[];  // [C][3], then [C * C][32]
+  extern __shared__ __align__(16) unsigned int am_smem[];
+  // [C][3], then [C * C][32] (with a confusion matrix), then the stages
   constexpr int C = CT;
+  constexpr int NT = kAmThreads;
   unsigned int *s_cnt = am_smem;
   unsigned int *s_cm = am_smem + 3 * C;  // per-lane columns
   const long long px = (long long)a.H * a.W;
@@ -307,37 +338,69 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
   const int S = a.src.n;
   const int lane = threadIdx.x & 31;
   const bool want_cm = a.cm && a.gt_label;
+  // a thread's slots of one stage: S x C vectors at a stride of NT x 16 bytes,
+  // then the truth bytes (C x 8 one-hot, or 8 of the label map) at NT x 8
+  const uint32_t n_head = 3 * C + (want_cm ? C * C * 32 : 0);
+  const uint32_t stage_sa =
+      ((uint32_t)__cvta_generic_to_shared(am_smem) + n_head * 4u + 15u) & ~15u;
+  const uint32_t gt_words = a.gt_onehot ? C : (a.gt_label ? 1 : 0);
+  const uint32_t gt_base = (uint32_t)(S * C) * NT * 16u;
+  const uint32_t stage_bytes = gt_base + gt_words * NT * 8u;
+  const uint32_t my16 = stage_sa + threadIdx.x * 16u;
+  const uint32_t my8 = stage_sa + gt_base + threadIdx.x * 8u;
 
   for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
     const long long img = chunk / a.chunks_per_img;
     const long long i0 = (chunk - img * a.chunks_per_img) * per;
     const long long i1 = min(items, i0 + per);
     const long long pl0 = img * C;  // class-0 plane of this image
-    for (int i = threadIdx.x; i < 3 * C + (want_cm ? C * C * 32 : 0);
-         i += blockDim.x)
-      am_smem[i] = 0;
+    for (int i = threadIdx.x; i < (int)n_head; i += blockDim.x) am_smem[i] = 0;
     __syncthreads();
     uint32_t nT[C], nP[C], nI[C];
 #pragma unroll
     for (int c = 0; c < C; ++c) nT[c] = nP[c] = nI[c] = 0u;
-    for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x) {
+    auto issue = [&](long long it_, uint32_t st) {
       // (32-bit: a plane has fewer than 2^31 pixels)
-      const int y = (int)((uint32_t)it / (uint32_t)ipr),
-                xi = (int)((uint32_t)it - (uint32_t)y * (uint32_t)ipr);
-      float acc[8][C];
+      const int y_ = (int)((uint32_t)it_ / (uint32_t)ipr),
+                xi_ = (int)((uint32_t)it_ - (uint32_t)y_ * (uint32_t)ipr);
       for (int k = 0; k < S; ++k) {
         const int xf = a.src.xf[k];
-        const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y : y;
-        const bool hf = xf & MLC_XF_HFLIP;
-        const int xs = hf ? ipr - 1 - xi : xi;
+        const int ys = (xf & MLC_XF_VFLIP) ? a.H - 1 - y_ : y_;
+        const int xs = (xf & MLC_XF_HFLIP) ? ipr - 1 - xi_ : xi_;
         const uint4 *p = reinterpret_cast<const uint4 *>(
                              static_cast<const __half *>(a.src.ptr[k]) +
                              (size_t)pl0 * px) +
                          ((size_t)ys * ipr + xs);
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+          am_cp16(my16 + st + (uint32_t)(k * C + c) * NT * 16u,
+                  p + (size_t)c * (px / 8));
+      }
+      if (a.gt_onehot) {
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+          am_cp8(my8 + st + (uint32_t)c * NT * 8u,
+                 a.gt_onehot + (size_t)(pl0 + c) * px + (size_t)it_ * 8);
+      } else if (a.gt_label) {
+        am_cp8(my8 + st, a.gt_label + (size_t)img * px + (size_t)it_ * 8);
+      }
+    };
+    uint32_t cur = 0u;  // byte offset of the stage that holds the current item
+    if (i0 + threadIdx.x < i1) issue(i0 + threadIdx.x, cur);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (long long it = i0 + threadIdx.x; it < i1; it += blockDim.x) {
+      if (it + blockDim.x < i1) issue(it + blockDim.x, cur ^ stage_bytes);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      const int y = (int)((uint32_t)it / (uint32_t)ipr),
+                xi = (int)((uint32_t)it - (uint32_t)y * (uint32_t)ipr);
+      float acc[8][C];
+      for (int k = 0; k < S; ++k) {
+        const bool hf = a.src.xf[k] & MLC_XF_HFLIP;
         uint32_t w[C][4];
 #pragma unroll
         for (int c = 0; c < C; ++c) {
-          const uint4 r = ldg_stream16(p + (size_t)c * (px / 8));
+          const uint4 r = am_lds16(my16 + cur + (uint32_t)(k * C + c) * NT * 16u);
           w[c][0] = r.x; w[c][1] = r.y; w[c][2] = r.z; w[c][3] = r.w;
         }
         if (hf) {  // the item's pixels come in reverse order
@@ -442,7 +505,7 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
       if (a.label)
         *reinterpret_cast<uint2 *>(a.label + at) = make_uint2(lab[0], lab[1]);
       uint2 gl = make_uint2(0u, 0u);
-      if (a.gt_label) gl = ldg_stream8(a.gt_label + at);
+      if (a.gt_label) gl = am_lds8(my8 + cur);
 #pragma unroll
       for (int c = 0; c < C; ++c) {
         // bytes equal to c: x ^ c has a zero byte there (labels are < 128)
@@ -457,8 +520,7 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
           nP[c] += __popc(e0 | (e1 >> 1));
           uint32_t t0 = 0u, t1 = 0u;
           if (a.gt_onehot) {
-            const uint2 g = ldg_stream8(a.gt_onehot + (size_t)(pl0 + c) * px +
-                                        (size_t)it * 8);
+            const uint2 g = am_lds8(my8 + cur + (uint32_t)c * NT * 8u);
             t0 = nonzero_bytes(g.x);
             t1 = nonzero_bytes(g.y);
           } else if (a.gt_label) {
@@ -478,7 +540,9 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
           if (g < (uint32_t)C) atomicAdd(&s_cm[(g * C + b) * 32 + lane], 1u);
         }
       }
+      cur ^= stage_bytes;
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (a.counts) {
 #pragma unroll
       for (int c = 0; c < C; ++c) {
@@ -512,12 +576,16 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
 }
 
 template <int CT>
-static void launch_items(const ArgmaxArgs &a, int grid, size_t smem,
-                         cudaStream_t st) {
-  if (a.act == MLC_ACT_SOFTMAX)
-    seg_argmax_items<CT, MLC_ACT_SOFTMAX><<<grid, kAmThreads, smem, st>>>(a);
-  else
-    seg_argmax_items<CT, MLC_ACT_NONE><<<grid, kAmThreads, smem, st>>>(a);
+static cudaError_t launch_items(const ArgmaxArgs &a, int grid, size_t smem,
+                                cudaStream_t st) {
+  void (*k)(ArgmaxArgs) = a.act == MLC_ACT_SOFTMAX
+                              ? seg_argmax_items<CT, MLC_ACT_SOFTMAX>
+                              : seg_argmax_items<CT, MLC_ACT_NONE>;
+  const cudaError_t e = cudaFuncSetAttribute(
+      k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  k<<<grid, kAmThreads, smem, st>>>(a);
+  return cudaGetLastError();
 }
 
 }  // namespace mlc
@@ -593,20 +661,27 @@ extern "C" int mlc_seg_argmax(const void *const *src_dev_ptrs,
   if (items) {
     a.items_per_row = W / 8;
     a.margin = (float)n_src * 3.0517578125e-5f;  // S * 2^-15
+    // counters, then two stages of (S x C x 16 + truth bytes) per thread
+    const size_t gt_words = gt_onehot_dev ? n_cls : (gt_label_dev ? 1 : 0);
     const size_t ismem =
-        (size_t)(3 * n_cls + (cm_dev ? n_cls * n_cls * 32 : 0)) * 4;
-    const int igrid = (int)min(n_chunks, 2ll * sm_count());
-    switch (n_cls) {
-      case 2: launch_items<2>(a, igrid, ismem, st); break;
-      case 3: launch_items<3>(a, igrid, ismem, st); break;
-      case 4: launch_items<4>(a, igrid, ismem, st); break;
-      case 5: launch_items<5>(a, igrid, ismem, st); break;
-      case 6: launch_items<6>(a, igrid, ismem, st); break;
-      case 7: launch_items<7>(a, igrid, ismem, st); break;
-      default: launch_items<8>(a, igrid, ismem, st); break;
+        (size_t)(3 * n_cls + (cm_dev ? n_cls * n_cls * 32 : 0)) * 4 + 16 +
+        2 * ((size_t)n_src * n_cls * 16 + gt_words * 8) * kAmThreads;
+    items = ismem <= 227 * 1024;
+    if (items) {
+      const int igrid = (int)min(n_chunks, 2ll * sm_count());
+      cudaError_t e;
+      switch (n_cls) {
+        case 2: e = launch_items<2>(a, igrid, ismem, st); break;
+        case 3: e = launch_items<3>(a, igrid, ismem, st); break;
+        case 4: e = launch_items<4>(a, igrid, ismem, st); break;
+        case 5: e = launch_items<5>(a, igrid, ismem, st); break;
+        case 6: e = launch_items<6>(a, igrid, ismem, st); break;
+        case 7: e = launch_items<7>(a, igrid, ismem, st); break;
+        default: e = launch_items<8>(a, igrid, ismem, st); break;
+      }
+      MLC_CUDA(e);
+      return MLC_OK;
     }
-    MLC_LAUNCH_CHECK("seg_argmax_items");
-    return MLC_OK;
   }
   void (*k)(ArgmaxArgs);
 #define MLC_AM(T)                                                      \
