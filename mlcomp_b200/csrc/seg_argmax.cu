@@ -659,6 +659,17 @@ extern "C" int mlc_seg_argmax(const void *const *src_dev_ptrs,
   for (int i = 0; i < n_src; ++i)
     items = items && ((uintptr_t)src_dev_ptrs[i] % 16) == 0;
   if (items) {
+#ifdef MLC_BOUNDS_CHECK
+    {
+      BoundsList bl;
+      const size_t px_all = (size_t)n_img * H * W;
+      for (int i = 0; i < n_src; ++i)
+        bl.add(src_dev_ptrs[i], px_all * n_cls * 2);
+      bl.add(gt_onehot_dev, px_all * n_cls);
+      bl.add(gt_label_dev, px_all);
+      MLC_CUDA(bounds_commit(bl, st));
+    }
+#endif
     a.items_per_row = W / 8;
     a.margin = (float)n_src * 3.0517578125e-5f;  // S * 2^-15
     // counters, then two stages of (S x C x 16 + truth bytes) per thread

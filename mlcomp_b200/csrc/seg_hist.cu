@@ -1375,16 +1375,11 @@ static int seg_hist_impl(const void *const *src_dev_ptrs, const int32_t *xform,
     if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID &&
         ((!vec && !vrows) || (a.plane_px % 8) != 0) &&
         hist_variant() != 4 && hist_variant() != 6) {
-      // rows of any width / alignment: the same estimate fed through
-      // enclosing-vector copies (declines transposes, unaligned tensors,
-      // irregular grids)
+      // rows of any width / alignment: the same estimate, rows staged by
+      // bulk copies (declines transposes, unaligned tensors, irregular grids)
       int rc = MLC_OK;
-      {
-        HistArgs b = a;
-        if (seg_hist_guarded_rows_launch(b, st, &rc)) return rc;
-      }
       HistArgs b = a;
-      if (seg_hist_guarded_un_launch(b, st, &rc)) return rc;
+      if (seg_hist_guarded_rows_launch(b, st, &rc)) return rc;
     }
     if (dtype == MLC_F16 && act == MLC_ACT_SIGMOID && hist_variant() != 4) {
       // activation table in shared memory: one 1024-thread CTA per SM

@@ -86,10 +86,9 @@ __device__ __forceinline__ void store_bins8(uint8_t *dst, const int c[8],
 // Returns true when the job was launched (or failed: *rc), false when the
 // threshold table / layout is outside what the kernel serves.
 bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc);
-// the same for rows of any width / alignment (a.H, a.W as for the fetches)
-bool seg_hist_guarded_un_launch(HistArgs &a, cudaStream_t st, int *rc);
-// the same with the rows staged by the TMA unit (seg_hist_guarded_rows.cu;
-// W >= 249, 16-byte aligned tensors)
+// the same for rows of any width / alignment, staged by the TMA unit
+// (seg_hist_guarded_rows.cu; a.H, a.W as for the fetches; W >= 9, 16-byte
+// aligned source tensors, no transpose)
 bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc);
 
 }  // namespace mlc

@@ -381,252 +381,12 @@ static void (*pick_guarded_pf(bool rows, bool bins))(HistArgs) {
                       : seg_hist_guarded_pf<NS, NT, false, false>);
 }
 
-// ---- rows of any width and alignment (350 x 525 ...) -------------------------
-// Same arithmetic; what changes is how an item's 8 values per source reach the
-// registers.  An 8-element window that starts at an arbitrary element lies in
-// the two 16-byte aligned vectors that enclose it: a thread copies those (one
-// when the window is aligned) with cp.async into its own shared-memory slots,
-// and when they have arrived picks the window with one of eight fixed shuffles
-// (window8_from_enclosing).  ONE stage: the words of the current item are
-// taken into registers first, then the copies of the thread's next item go
-// into the same slots and are in flight while the current item is computed.
-// The W % 8 pixels at the end of a row are served by one more item whose window
-// is the row's last eight pixels (the ones it shares with its neighbour are
-// not counted again).
-// Requires 16-byte aligned source tensors (every vector that is read then
-// contains at least one byte of the window it is read for) and no transpose.
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void *src) {
-  MLC_CHECK_LOAD(src, 4);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src)
-               : "memory");
-}
-
-template <int NS, int NT, bool BINS, int REV>
-__device__ __forceinline__ void un_unit(const HistArgs &a, uint32_t plane,
-                                        uint32_t sub, uint32_t upp,
-                                        uint32_t slot, uint32_t my_slot) {
-  // per thread: source j's two vectors at (2j, 2j + 1) * NT * 16, then 16 bytes
-  // of truth words (3) + the index of the item the slots hold, then a word
-  // with the window offsets (3 bits per source) and the truth shift
-  constexpr uint32_t kMisc = 2u * NS * NT * 16u;
-  constexpr uint32_t kMeta = kMisc + NT * 16u;
-  const int ipr = a.items_per_row, W = a.W, H = a.H;
-  const size_t plane_off = (size_t)plane * a.plane_px;
-  const uint32_t full = (uint32_t)a.full_items;
-  const uint32_t ipu = (full + upp - 1) / upp;
-  const int i0 = (int)(sub * ipu);
-  const int i1 = (int)min(full, (uint32_t)i0 + ipu);
-  const int lane = threadIdx.x & 31;
-  const uint32_t next_sa = (uint32_t)__cvta_generic_to_shared(&s_next_item);
-  // element index of output pixel (y, x0) in source j (x0 = first of 8)
-  auto elem = [&](int j, int y_, int x0) {
-    return a.g_b[j] + a.g_cy[j] * y_ + a.g_cx[j] * x0;
-  };
-  // items of a row: its W / 8 full items, then (W % 8 != 0) one more whose
-  // window is the row's LAST eight pixels - it overlaps its neighbour, and
-  // only its last W % 8 pixels are counted
-  const int ipt = ipr + ((W & 7) ? 1 : 0);
-  auto issue = [&](int it_) {
-    const int y_ = (int)__umulhi((uint32_t)it_, a.g_ipr_magic);
-    const int xi_ = it_ - y_ * ipt;
-    const int x0 = xi_ < ipr ? xi_ * 8 : W - 8;
-    uint32_t meta = 0u;
-#pragma unroll
-    for (int j = 0; j < NS; ++j) {
-      const uintptr_t p = reinterpret_cast<uintptr_t>(
-          static_cast<const __half *>(a.src.ptr[j]) + plane_off +
-          elem(j, y_, x0));
-      const uintptr_t v0 = p & ~(uintptr_t)15;
-      meta |= ((uint32_t)(p & 15) >> 1) << (3 * j);
-      cp_async16(my_slot + (2 * j) * NT * 16u,
-                 reinterpret_cast<const void *>(v0));
-      if (p & 15)
-        cp_async16(my_slot + (2 * j + 1) * NT * 16u,
-                   reinterpret_cast<const void *>(v0 + 16));
-    }
-    const uintptr_t g = reinterpret_cast<uintptr_t>(a.gt + plane_off +
-                                                    (size_t)y_ * W + x0);
-    const uintptr_t g0 = g & ~(uintptr_t)3;
-    meta |= (uint32_t)(g & 3) << 12;
-    st_shared_u32(my_slot + kMeta, meta);
-    cp_async4(my_slot + kMisc, reinterpret_cast<const void *>(g0));
-    cp_async4(my_slot + kMisc + 4, reinterpret_cast<const void *>(g0 + 4));
-    if (g & 3)
-      cp_async4(my_slot + kMisc + 8, reinterpret_cast<const void *>(g0 + 8));
-  };
-  {
-    const int it = i0 + (int)threadIdx.x;  // the first round is static
-    st_shared_u32(my_slot + kMisc + 12, (uint32_t)it);
-    if (it < i1) issue(it);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  }
-  while (true) {
-    const int it = (int)lds_u32(my_slot + kMisc + 12);
-    if (it - lane >= i1) break;  // the same for all lanes of the warp
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    uint32_t w[4][4];
-    uint2 g = make_uint2(0u, 0u);
-    if (it < i1) {
-      const uint32_t meta = lds_u32(my_slot + kMeta);
-#pragma unroll
-      for (int j = 0; j < NS; ++j) {
-        const uint4 lo4 = lds_u4(my_slot + (2 * j) * NT * 16u);
-        const uint4 hi4 = lds_u4(my_slot + (2 * j + 1) * NT * 16u);
-        const uint32_t t[8] = {lo4.x, lo4.y, lo4.z, lo4.w,
-                               hi4.x, hi4.y, hi4.z, hi4.w};
-        window8_select(t, (meta >> (3 * j)) & 7u, w[j]);
-        if (REV < 0 && ((a.g_rev >> j) & 1)) reverse8(w[j]);
-      }
-      const uint32_t sh = ((meta >> 12) & 3u) * 8u;
-      const uint32_t t0 = lds_u32(my_slot + kMisc),
-                     t1 = lds_u32(my_slot + kMisc + 4),
-                     t2 = lds_u32(my_slot + kMisc + 8);
-      g = make_uint2(__funnelshift_r(t0, t1, sh), __funnelshift_r(t1, t2, sh));
-    }
-    // the slots are free: fetch this thread's next item into them
-    // (address offset by an always-zero term: see pf_unit)
-    uint32_t nb = 0;
-    if (lane == 0)
-      asm volatile("atom.shared.add.u32 %0, [%1], 32;"
-                   : "=r"(nb)
-                   : "r"(next_sa + (((uint32_t)it >> 31) << 2))
-                   : "memory");
-    nb = __shfl_sync(0xffffffffu, nb, 0);
-    {
-      const int itn = (int)nb + lane;
-      st_shared_u32(my_slot + kMisc + 12, (uint32_t)itn);
-      if (itn < i1) issue(itn);
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    if (it < i1) {
-      float q[8];
-      uint32_t dmax = 0u;
-      if constexpr (REV >= 0)
-        group_sum<NS, REV & ((1 << NS) - 1)>(w, true, q, dmax);
-      else
-        group_sum<NS, 0>(w, true, q, dmax);
-      const int y_ = (int)__umulhi((uint32_t)it, a.g_ipr_magic);
-      const int xi_ = it - y_ * ipt;
-      const int x0 = xi_ < ipr ? xi_ * 8 : W - 8;
-      finish_item<true, BINS ? 2 : 0>(
-          a, q, dmax, g, slot, plane, it,
-          plane_off + (size_t)y_ * W + (size_t)x0, 0u, 0u,
-          xi_ < ipr ? 0 : 8 - (W & 7), -y_ - 1, x0);
-    }
-  }
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-}
-
-template <int NS, int NT, bool BINS>
-__global__ void __launch_bounds__(NT, 1024 / NT)
-seg_hist_guarded_un(const __grid_constant__ HistArgs a) {
-  extern __shared__ __align__(16) uint32_t gsm[];
-  const int B = a.B, nbins = B + 1;
-  const uint32_t gsm_sa = (uint32_t)__cvta_generic_to_shared(gsm);
-  const uint32_t cnt_sa = (gsm_sa + 16383u) & ~16383u;
-  uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
-  float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
-  for (int i = threadIdx.x; i < nbins * 32; i += NT) cnt[i] = 0;
-  for (int i = threadIdx.x; i < B; i += NT) thr[i] = a.thr.v[i];
-  const uint32_t upp = gridDim.y;
-  const uint32_t plane = blockIdx.x, sub = blockIdx.y;
-  if (threadIdx.x == 0) {
-    const uint32_t full = (uint32_t)a.full_items;
-    s_next_item = sub * ((full + upp - 1) / upp) + NT;
-  }
-  __syncthreads();
-  const uint32_t slot = cnt_sa | ((threadIdx.x & 31) * 4);
-  const uint32_t st_sa = (cnt_sa + nbins * 128 + B * 4 + 15u) & ~15u;
-  const uint32_t my_slot = st_sa + threadIdx.x * 16u;
-  constexpr int kAll = (1 << NS) - 1;
-  const int rev = (int)(a.g_rev & kAll);
-  if (rev == 0)
-    un_unit<NS, NT, BINS, 0>(a, plane, sub, upp, slot, my_slot);
-  else if (rev == (0xA & kAll))
-    un_unit<NS, NT, BINS, 0xA & kAll>(a, plane, sub, upp, slot, my_slot);
-  else if (rev == (0x5 & kAll))
-    un_unit<NS, NT, BINS, 0x5 & kAll>(a, plane, sub, upp, slot, my_slot);
-  else if (rev == kAll)
-    un_unit<NS, NT, BINS, kAll>(a, plane, sub, upp, slot, my_slot);
-  else
-    un_unit<NS, NT, BINS, -1>(a, plane, sub, upp, slot, my_slot);
-  uint32_t *out = a.hist + (size_t)plane * 2 * nbins;
-  flush_bins(cnt, nbins, out, upp > 1);
-}
-
 template <int NS>
 static void (*pick_guarded(bool rows, bool bins))(HistArgs) {
   return bins ? (rows ? seg_hist_guarded<NS, true, true>
                       : seg_hist_guarded<NS, false, true>)
               : (rows ? seg_hist_guarded<NS, true, false>
                       : seg_hist_guarded<NS, false, false>);
-}
-
-// Rows of any width / alignment (no transpose): see seg_hist_guarded_un.
-bool seg_hist_guarded_un_launch(HistArgs &a, cudaStream_t st, int *rc) {
-  *rc = MLC_OK;
-  const int S = a.src.n, W = a.W, H = a.H;
-  const int ipr = W / 8;
-  if (S < 2 || S > 4 || ipr < 2) return false;
-  if (a.src.any_xf & MLC_XF_TRANSPOSE) return false;
-  for (int k = 0; k < S; ++k)
-    if (((uintptr_t)a.src.ptr[k] % 16) != 0) return false;
-  const int ipt = ipr + ((W & 7) ? 1 : 0);  // + the row's tail item
-  const long long full = (long long)ipt * H;
-  if (full * ipt >= (1ll << 32) || a.n_planes >= (1ll << 31) ||
-      a.units_per_plane >= 65536)
-    return false;
-  if (!guarded_grid(a)) return false;
-#ifdef MLC_BOUNDS_CHECK
-  {
-    BoundsList bl;
-    for (int k = 0; k < S; ++k)
-      bl.add(a.src.ptr[k], ((size_t)a.n_planes * a.plane_px * 2 + 15) / 16 * 16);
-    bl.add(a.gt, ((size_t)a.n_planes * a.plane_px + 3) / 4 * 4);
-    const cudaError_t e = bounds_commit(bl, st);
-    if (e != cudaSuccess) {
-      *rc = cuda_fail(e, "bounds_commit");
-      return true;
-    }
-  }
-#endif
-  a.items_per_row = ipr;
-  a.full_items = full;
-  a.g_ipr_magic = (uint32_t)((1ull << 32) / (unsigned)ipt + 1);
-  a.g_rev = 0u;
-  for (int k = 0; k < S; ++k) {
-    const int xf = a.src.xf[k];
-    const int vy = (xf & MLC_XF_VFLIP) ? 1 : 0, hx = (xf & MLC_XF_HFLIP) ? 1 : 0;
-    // element index of output pixel (y, x0): first of the 8 source elements
-    // that hold output pixels x0 .. x0 + 7 (in reverse order when flipped)
-    a.g_cy[k] = vy ? -W : W;
-    a.g_cx[k] = hx ? -1 : 1;
-    a.g_b[k] = (vy ? (H - 1) * W : 0) + (hx ? W - 8 : 0);
-    if (hx) a.g_rev |= 1u << k;
-  }
-  const int B = a.B;
-  constexpr int NT = 512;
-  const size_t smem = 16384 + (size_t)(B + 1) * 32 * 4 + (size_t)B * 4 + 16 +
-                      (size_t)NT * (2 * S + 2) * 16;
-  const bool bins = a.bins != nullptr;
-  void (*k)(HistArgs) =
-      S == 2   ? (bins ? seg_hist_guarded_un<2, NT, true>
-                       : seg_hist_guarded_un<2, NT, false>)
-      : S == 3 ? (bins ? seg_hist_guarded_un<3, NT, true>
-                       : seg_hist_guarded_un<3, NT, false>)
-               : (bins ? seg_hist_guarded_un<4, NT, true>
-                       : seg_hist_guarded_un<4, NT, false>);
-  const cudaError_t ea = cudaFuncSetAttribute(
-      k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (ea != cudaSuccess) {
-    *rc = cuda_fail(ea, "cudaFuncSetAttribute(seg_hist_guarded_un)");
-    return true;
-  }
-  k<<<dim3((unsigned)a.n_planes, (unsigned)a.units_per_plane), NT, smem, st>>>(
-      a);
-  const cudaError_t err = cudaGetLastError();
-  if (err != cudaSuccess) *rc = cuda_fail(err, "seg_hist_guarded_un");
-  return true;
 }
 
 bool seg_hist_guarded_launch(HistArgs &a, bool rows, cudaStream_t st, int *rc) {

@@ -157,24 +157,6 @@ __device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
   return v;
 }
 
-// The eight halves that start `off` halves (0..7) into the eight words t[]:
-// two levels of selects move the window to the front word by word, four funnel
-// shifts move it by the odd half.  Branch-free: lanes of a warp that sit in
-// different rows have different offsets, and an eight-way switch cost 30 % of the kernel's stall samples in branches.
-__device__ __forceinline__ void window8_select(const uint32_t (&t)[8],
-                                               uint32_t off,
-                                               uint32_t (&w)[4]) {
-  const bool b2 = off & 4u, b1 = off & 2u;
-  uint32_t a[6], b[5];
-#pragma unroll
-  for (int j = 0; j < 6; ++j) a[j] = b2 ? t[j + 2] : t[j];
-#pragma unroll
-  for (int j = 0; j < 5; ++j) b[j] = b1 ? a[j + 1] : a[j];
-  const uint32_t sh = (off & 1u) * 16u;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) w[j] = __funnelshift_r(b[j], b[j + 1], sh);
-}
-
 // From the sums of sigmoids of one item to its histogram updates (and bin
 // bytes): grid position moved down / up by the error bound, exact evaluation
 // of the pixels the two disagree on, one shared-memory atomic per pixel.
@@ -188,14 +170,13 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
                                             size_t bins_item,
                                             uint32_t stage_sa = 0u,
                                             uint32_t stage_stride = 0u,
-                                            int skip = 0, int ex_it = 0,
-                                            int ex_i0 = 0, int nvalid = 8) {
-  // skip > 0 (row-tail items of the unaligned kernel): the first `skip`
-  // pixels of the window belong to the previous item and are not counted;
-  // nvalid < 8 (row-tail items of the TMA-fed kernel): only the first
-  // `nvalid` pixels exist, the others lie beyond the row.
-  // The exact path is then addressed as pixel (y, x) = (-ex_it - 1, ex_i0 + i)
-  const bool tail = skip > 0 || ex_it < 0;
+                                            int ex_it = 0, int ex_i0 = 0,
+                                            int nvalid = 8) {
+  // nvalid < 8 (a row's last item in the kernel for rows of any width): only
+  // the first `nvalid` pixels exist, the others lie beyond the row.
+  // ex_it < 0: the exact path is addressed as pixel (y, x) = (-ex_it - 1,
+  // ex_i0 + i) instead of by item index
+  const bool tail = ex_it < 0;
   const float kq = a.g_kq, fb_lo = a.g_fb_lo, fb_hi = a.g_fb_hi;
   uint32_t fx[8], differ = 0;
 #pragma unroll
@@ -235,11 +216,11 @@ __device__ __forceinline__ void finish_item(const HistArgs &a,
     g.y &= (uint32_t)(keep >> 32);
     nvalid = 8;
   }
-  if (skip > 0 || nvalid < 8) {
+  if (nvalid < 8) {  // (with bin planes only)
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const uint32_t gb = ((i < 4 ? g.x : g.y) >> (8 * (i & 3))) & 0xFFu;
-      if (i >= skip && i < nvalid)
+      if (i < nvalid)
         red_shared_add(((fx[i] >> 9) & 0x3F80u) | slot, gb ? 0x10000u : 1u);
     }
   } else if ((g.x | g.y) == 0u) {  // all background: the increment is 1

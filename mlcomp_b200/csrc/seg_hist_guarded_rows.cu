@@ -4,14 +4,16 @@
 //
 // Why: a row of W fp16 values that is no multiple of 16 bytes starts at a
 // different offset inside its 16-byte vectors in every row, and flipped
-// sources add their own.  seg_hist_guarded_un pays for that per item and per
-// source with two cp.async of the enclosing vectors and 64-bit address
-// arithmetic (70 instructions per pixel against 49 of the aligned kernel), in
-// a single stage, and reads most 32-byte sectors twice (ncu: 5.5 of 32 bytes
-// used per request).  Here ONE thread of the CTA asks the copy engine for
-// "the 16-byte vectors that enclose source row ys" - one copy per row and
-// source, every sector once - into a ring of row slots that is many rows
-// deep; the other threads never form a global address.
+// sources add their own.  The kernel this one replaced (seg_hist_guarded_un:
+// every thread copied the two 16-byte vectors that enclose its window, per
+// item and source, with cp.async) paid for that with 64-bit address
+// arithmetic and a 14-instruction window selection per source and item (70
+// instructions per pixel against 49 of the aligned kernel), had room for a
+// single stage, and read most 32-byte sectors twice (ncu: 5.5 of 32 bytes
+// used per request): 0.43 of the HBM peak on 350 x 525 planes.  Here a
+// producer warp asks the copy engine for "the 16-byte vectors that enclose
+// these rows of this source" - every sector once - into a ring of slots that
+// is many rows deep; the other threads never form a global address.
 //
 // (A tensor map cannot do the realignment itself: measured on B200, a tiled
 // copy whose innermost start coordinate is not a multiple of 16 bytes raises
@@ -270,7 +272,7 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
       const int y = row0 + r, x0 = xi * 8;
       finish_item<true, BINS ? 2 : 0>(
           a, q, dmax, gt, slot, plane, it, plane_off + (size_t)y * W + (size_t)x0,
-          0u, 0u, 0, -y - 1, x0, xi == ipt - 1 ? g.nvalid_tail : 8);
+          0u, 0u, -y - 1, x0, xi == ipt - 1 ? g.nvalid_tail : 8);
     }
   }
 }
@@ -332,8 +334,7 @@ seg_hist_guarded_rows(const __grid_constant__ HistArgs a,
 }
 
 // Requires 16-byte aligned source tensors (every vector that is copied then
-// contains at least one byte of its tensor), W >= 249 (a chunk of 32 items
-// lies in at most two rows), no transpose.
+// contains at least one byte of its tensor), W >= 9, no transpose.
 bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
   *rc = MLC_OK;
   const int S = a.src.n, W = a.W, H = a.H;
@@ -343,7 +344,7 @@ bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
     if (((uintptr_t)a.src.ptr[k] % 16) != 0) return false;
   RowGeom g;
   g.ipt = (W + 7) / 8;
-  if (g.ipt < 32) return false;
+  if (g.ipt < 2) return false;  // (the magic of a division by 1 has 33 bits)
   if ((long long)H * g.ipt * g.ipt >= (1ll << 32) || a.n_planes >= (1ll << 31) ||
       a.units_per_plane >= 65536)
     return false;

@@ -277,8 +277,8 @@ def test_valid_segment_prepare_submit_from_host_arrays(ops, tmp_path):
                                          (4, False)])
 def test_guarded_unaligned_rows(ops, shape, n_src, flips):
     """350 x 525-like planes (rows that are no multiple of 16 bytes, planes
-    that start at any element offset): enclosing-vector copies + exact row
-    tails give the exact binning."""
+    that start at any element offset; csrc/seg_hist_guarded_rows.cu also for
+    rows of a few items): the exact binning."""
     n, c, h, w = shape
     srcs, gt = synth_seg(n, c, h, w, seed=h + w + n_src, n_src=n_src)
     tags = [FLIPS[k % 4] if flips else [] for k in range(n_src)]
@@ -292,10 +292,9 @@ def test_guarded_unaligned_rows(ops, shape, n_src, flips):
                                    (2, 2, 40, 525), (1, 33, 2, 255)])
 @pytest.mark.parametrize('n_src,flips', [(4, True), (2, True), (3, False)])
 def test_guarded_tma_rows(ops, shape, n_src, flips):
-    """Rows of >= 249 pixels of any width (csrc/seg_hist_guarded_rows.cu: rows
-    staged by tensor-map copies): partial last items, planes in the full
-    8 / 16-plane groups and in the last, shorter group, 1 - 4 copies per row,
-    more rows than ring slots."""
+    """Wide rows of any width (csrc/seg_hist_guarded_rows.cu: bands of rows
+    staged by bulk copies): partial last items, one to many rows per band,
+    more bands than ring slots, planes at every 16-byte phase."""
     n, c, h, w = shape
     srcs, gt = synth_seg(n, c, h, w, seed=h + w + n_src, n_src=n_src)
     tags = [FLIPS[k % 4] if flips else [] for k in range(n_src)]
