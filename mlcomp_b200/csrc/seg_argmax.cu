@@ -28,11 +28,13 @@
 // when the largest estimated score exceeds the second largest by more than
 // S * 2^-15 (an 8-fold margin), the reference's arg-max is that class.  Every
 // other pixel - near-ties, exact ties (which go to the lowest index), NaN /
-// inf anywhere (the estimated scores then do not sum to S) - is evaluated by
+// inf anywhere (every estimated score of the pixel is then NaN) - is evaluated by
 // the exact code of the first kernel (am_scores).  With no activation the
 // scores are plain fp32 sums: computed exactly, no estimate.
 // Counts: per class, the item's eight labels are compared as packed bytes and
 // the T / P / I counts of a thread stay in registers until its chunk ends.
+#include <type_traits>
+
 #include "mlc_common.cuh"
 
 namespace mlc {
@@ -395,7 +397,10 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
       const int y = (int)((uint32_t)it / (uint32_t)ipr),
                 xi = (int)((uint32_t)it - (uint32_t)y * (uint32_t)ipr);
       float acc[8][C];
-      for (int k = 0; k < S; ++k) {
+      // (the first source assigns, the others add: a compile-time flag - as a
+      // run-time test of k it cost a select per class and pixel)
+      auto do_source = [&](int k, auto first_tag) {
+        constexpr bool kFirst = decltype(first_tag)::value;
         const bool hf = a.src.xf[k] & MLC_XF_HFLIP;
         uint32_t w[C][4];
 #pragma unroll
@@ -446,29 +451,31 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
             }
 #pragma unroll
             for (int c = 0; c < C; ++c)
-              acc[2 * h + e][c] = k == 0 ? v[e][c] : acc[2 * h + e][c] + v[e][c];
+              acc[2 * h + e][c] = kFirst ? v[e][c] : acc[2 * h + e][c] + v[e][c];
           }
         }
-      }
+      };
+      do_source(0, std::true_type{});
+      for (int k = 1; k < S; ++k) do_source(k, std::false_type{});
       // labels of the eight pixels, one per byte
       uint32_t lab[2] = {0u, 0u};
       if (ACT == MLC_ACT_SOFTMAX) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float best = acc[i][0], second = -1.f, tot = acc[i][0];
+          float best = acc[i][0], second = -1.f;
           int bc = 0;
 #pragma unroll
           for (int c = 1; c < C; ++c) {
             const float v = acc[i][c];
-            tot += v;
             const bool up = v > best;
             second = up ? best : fmaxf(second, v);
             bc = up ? c : bc;
             best = up ? v : best;
           }
-          // NaN anywhere makes tot NaN and the test false
-          const bool sane = fabsf(tot - (float)S) < 1e-3f * (float)S;
-          if (!(sane && best - second > a.margin))
+          // A NaN or +inf logit, or a pixel whose logits are all -inf, makes
+          // the sum of a source's exponentials NaN and with it the score of
+          // EVERY class of the pixel: best = NaN, the test is false
+          if (!(best - second > a.margin))
             bc = am_exact_pixel<CT>(a, pl0, (size_t)px, y, xi * 8 + i);
           lab[i >> 2] |= (uint32_t)bc << (8 * (i & 3));
         }
