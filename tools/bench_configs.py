@@ -100,6 +100,19 @@ def c3(n=5546):
            n * c * (h * w * (4 * 2 + 1) + 808), n * c)
 
 
+def c3b(n=1024):
+    """C3 with the per-pixel bin planes as second output (what the pipeline
+    runs when the masks are to be encoded afterwards)."""
+    c, h, w = 4, 350, 525
+    tags = [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]
+    srcs, gt = synth(n, c, h, w, 4, 3, 0.5)
+    thr = ops.threshold_grid(100)
+    out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
+    ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, xforms=tags, bins=True))
+    report('C3 + bin planes %dx4x350x525 fp16: seg_hist_guarded_rows<bins>'
+           % n, ms, n * c * (h * w * (4 * 2 + 1 + 1) + 808), n * c)
+
+
 def c5(n=3750):
     c, h, w = 4, 256, 1600
     srcs, gt = synth(n, c, h, w, 5, 5, 0.86)
@@ -122,6 +135,18 @@ def c2g(n=1024):
     ms = timeit(lambda: ops.seg_hist(x32, gt, thr, out=out))
     report('C2 fp32 logits (seg_hist_logit) %d img' % n, ms,
            n * c * (h * w * 5 + 808), n * c)
+
+
+def c2r(n=1024):
+    """Single-model submission of the Severstal shape: every plane of ONE fp16
+    source to run-length pairs (Infer without TTA): rle_kernel<half, CODE, 512>."""
+    c, h, w = 4, 256, 1600
+    srcs, _ = synth(n, c, h, w, 1, 2, 0.86)
+    runs, off, cnt, area = ops.rle_encode(srcs, 0.5, 0)
+    n_runs = int(cnt.sum().item())
+    ms = timeit(lambda: ops.rle_encode(srcs, 0.5, 0))
+    report('Severstal single source -> RLE %dx4x256x1600 fp16: rle_kernel CODE'
+           % n, ms, n * c * h * w * 2 + 8 * n_runs, n * c, {'runs': n_runs})
 
 
 def c4(n=10000):
