@@ -540,13 +540,17 @@ def run_ours(args, cfg):
     # no-ops unless run under `ncu --profile-from-start off`
     torch.cuda.profiler.start()
     e0.record()
+    marks = [e0]
     for _ in range(args.steps):
         out = step()
+        marks.append(torch.cuda.Event(True))
+        marks[-1].record()
     e1.record()
     barrier()
     torch.cuda.profiler.stop()
     clocks = sampler.stop() if sampler else None
     ms = e0.elapsed_time(e1)
+    each_ms = [a.elapsed_time(b) for a, b in zip(marks[:-1], marks[1:])]
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -669,6 +673,8 @@ def run_ours(args, cfg):
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world,
         'steps': args.steps, 'warmup': max(args.warmup, 3),
         'ms_per_step': step_ms, 'higher_is_better': True,
+        'ms_each_step_rank0': {'min': min(each_ms), 'max': max(each_ms),
+                               'median': float(np.median(each_ms))},
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16',
         'data': 'synthetic',
         'config': config_dict(cfg, n_img, args.e2e_images, args.e2e_chunk),
