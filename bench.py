@@ -470,10 +470,14 @@ def run_ours(args, cfg):
     search = scoring.SegSearch(c, thr, cfg['min_areas'], device=dev,
                                record_events=True)
     cap = max(1 << 20, planes * px // 64)
+    # one buffer for the bin planes of every step (10.9 GB: allocated per step
+    # it alternates between two cached blocks, and whenever the caching
+    # allocator gives one back to the driver the step stalls for 50 - 200 ms)
+    bins_buf = torch.empty((n_img, c, h, w), dtype=torch.uint8, device=dev)
 
     def step():
         search.reset()
-        hist, bins = search.add(srcs, gt, xforms=TAGS, keep_bins=True)
+        hist, bins = search.add(srcs, gt, xforms=TAGS, keep_bins=bins_buf)
         res = search.result()
         k_c = [b['threshold_index'] for b in res['best']]
         a_c = [b['min_area'] for b in res['best']]
@@ -488,6 +492,9 @@ def run_ours(args, cfg):
     res, hist, bins, rle = step()
     best = res['best']
     n_runs = int(rle[0].numel() // 2)
+    # the run buffer of the later steps: twice what this data needs instead
+    # of the size-based first guess (0.7 GB per step)
+    cap = max(1 << 20, 4 * n_runs)
     n_nonempty = int((rle[2] > 0).sum().item())
 
     # ---- CPU path on the first planes of the shard + parity (rank 0) -------
@@ -531,12 +538,17 @@ def run_ours(args, cfg):
     # ---- warm-up + timed region ---------------------------------------------
     for _ in range(max(args.warmup, 3)):
         step()
-    sampler = ClockSampler(local) if rank == 0 else None
+    sampler = ClockSampler(local) if rank == 0 and not os.environ.get('MLC_BENCH_NO_SAMPLER') else None
     search.kernel_events.clear()
     barrier()
     if sampler:
         sampler.start()
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    # no collector pauses inside the timed steps (with several ranks one
+    # rank's pause is everybody's: the ranks meet in every step's exchange)
+    import gc
+    gc.collect()
+    gc.disable()
     # no-ops unless run under `ncu --profile-from-start off`
     torch.cuda.profiler.start()
     e0.record()
@@ -547,6 +559,7 @@ def run_ours(args, cfg):
         marks[-1].record()
     e1.record()
     barrier()
+    gc.enable()
     torch.cuda.profiler.stop()
     clocks = sampler.stop() if sampler else None
     ms = e0.elapsed_time(e1)
@@ -558,6 +571,18 @@ def run_ours(args, cfg):
     value = planes * world * args.steps / (ms * 1e-3)
     kern_ms = [a.elapsed_time(b) for a, b in search.kernel_events]
     kern_avg = float(np.mean(kern_ms))
+    # the slowest step / launch of every rank (a one-off stall on one GPU
+    # shows here and in the max-over-ranks total, not in the medians)
+    worst = torch.tensor([max(each_ms), float(np.median(each_ms)),
+                          max(kern_ms), float(np.median(kern_ms))],
+                         dtype=torch.float64, device=dev)
+    if world > 1:
+        allw = [torch.zeros_like(worst) for _ in range(world)]
+        dist.all_gather(allw, worst)
+        worst = torch.stack(allw)
+    else:
+        worst = worst[None]
+    worst = worst.cpu().numpy().round(3).tolist()
     same_best = [b['threshold_index'] for b in out[0]['best']] == \
         [b['threshold_index'] for b in best]
     validated &= same_best
@@ -573,7 +598,7 @@ def run_ours(args, cfg):
 
         def strong_step():
             search.reset()
-            h_, b_ = search.add(part, gpart, xforms=TAGS, keep_bins=True)
+            h_, b_ = search.add(part, gpart, xforms=TAGS, keep_bins=bins_buf[:m])
             r_ = search.result()
             return ops.rle_from_bins(
                 b_, [b['threshold_index'] for b in r_['best']],
@@ -675,6 +700,9 @@ def run_ours(args, cfg):
         'ms_per_step': step_ms, 'higher_is_better': True,
         'ms_each_step_rank0': {'min': min(each_ms), 'max': max(each_ms),
                                'median': float(np.median(each_ms))},
+        'ms_per_rank': {'columns': ['slowest step', 'median step',
+                                    'slowest launch', 'median launch'],
+                        'rows': worst},
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16',
         'data': 'synthetic',
         'config': config_dict(cfg, n_img, args.e2e_images, args.e2e_chunk),

@@ -182,7 +182,10 @@ def seg_hist(sources, gt, thr, xforms=None, activation='sigmoid', lut=None,
 
     ``bins=True`` (mlc_seg_hist_bins) also returns the bin index of every
     pixel, uint8 [n_img, n_cls, H, W]: ``bins > k`` is the mask at thr[k]
-    (``rle_from_bins``), 1 byte per pixel instead of the sources again."""
+    (``rle_from_bins``), 1 byte per pixel instead of the sources again.
+    ``bins=<uint8 tensor of that shape>`` writes them there (a loop over
+    chunks then allocates nothing: at 10 GB per buffer a cudaMalloc or
+    cudaFree of the caching allocator stalls the step by tens of ms)."""
     lib = _lib.load()
     sources, ptrs, xf, n, c, h, w = _sources(sources, xforms)
     gt = _need_cuda(gt, 'gt', (torch.uint8,))
@@ -200,10 +203,17 @@ def seg_hist(sources, gt, thr, xforms=None, activation='sigmoid', lut=None,
         _need_cuda(lut, 'lut', (torch.uint8,))
         if lut.numel() != _lib.MLC_LUT_BYTES:
             raise ValueError('lut must come from seg_lut()')
-    if bins:
+    if bins is not False and bins is not None:
         if len(thr) > 255:
             raise ValueError('bins need n_thr <= 255')
-        bins_out = torch.empty((n, c, h, w), dtype=torch.uint8, device=dev)
+        if isinstance(bins, torch.Tensor):
+            bins_out = _need_cuda(bins, 'bins', (torch.uint8,))
+            if tuple(bins_out.shape) != (n, c, h, w) or \
+                    not bins_out.is_contiguous():
+                raise ValueError(f'bins has shape {tuple(bins_out.shape)}, '
+                                 f'expected contiguous {(n, c, h, w)} uint8')
+        else:
+            bins_out = torch.empty((n, c, h, w), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             check(lib.mlc_seg_hist_bins(
                 ptrs, xf, len(sources), _dtype_code(sources[0]), _ptr(gt), n,

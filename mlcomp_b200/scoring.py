@@ -252,15 +252,17 @@ class SegSearch:
         """Score one chunk already in HBM; returns its histograms
         [n, C, 2, B+1] (int32) for per-image reporting - with
         ``keep_bins`` the pair (histograms, per-pixel bin indices uint8
-        [n, C, H, W]) for ``ops.rle_from_bins`` at the point the search picks."""
+        [n, C, H, W]) for ``ops.rle_from_bins`` at the point the search picks
+        (``keep_bins=<tensor>``: written into that buffer)."""
         if self.record_events:
             ev = (torch.cuda.Event(enable_timing=True),
                   torch.cuda.Event(enable_timing=True))
             ev[0].record()
         bins = None
-        if keep_bins:
+        if keep_bins is not False and keep_bins is not None:
             hist, bins = ops.seg_hist(sources, gt, self.thr, xforms=xforms,
-                                      activation=self.activation, bins=True)
+                                      activation=self.activation,
+                                      bins=keep_bins)
         else:
             hist = ops.seg_hist(sources, gt, self.thr, xforms=xforms,
                                 activation=self.activation, lut=self.lut)
@@ -289,7 +291,7 @@ class SegSearch:
             self.dice_sum += dsum
             self.micro += micro
         self.n_img += hist.shape[0]
-        return (hist, bins) if keep_bins else hist
+        return (hist, bins) if bins is not None else hist
 
     # -- host-resident chunks: copies overlapped with compute -----------------
     def _stager(self, arrays, chunk):

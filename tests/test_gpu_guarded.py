@@ -149,6 +149,31 @@ def test_guarded_severstal_tta_full_planes(ops):
     check(ops, sharp, FLIPS, gt, thr)
 
 
+def test_bins_into_a_callers_buffer(ops):
+    """seg_hist(bins=<tensor>) / SegSearch.add(keep_bins=<tensor>) write the
+    bin planes into the caller's buffer (no allocation per chunk) and give
+    what bins=True gives; a buffer of another shape or dtype is refused."""
+    from mlcomp_b200 import scoring
+    srcs, gt = synth_seg(3, 2, 16, 64, seed=11, n_src=4)
+    seen = [forward_tta(s, t).to(DEV) for s, t in zip(srcs, FLIPS)]
+    thr = oracle.threshold_grid(100)
+    hist, bins = ops.seg_hist(seen, gt.to(DEV), thr, xforms=FLIPS, bins=True)
+    buf = torch.full((3, 2, 16, 64), 255, dtype=torch.uint8, device=DEV)
+    hist2, bins2 = ops.seg_hist(seen, gt.to(DEV), thr, xforms=FLIPS, bins=buf)
+    assert bins2.data_ptr() == buf.data_ptr()
+    assert torch.equal(bins2, bins) and torch.equal(hist2, hist)
+    s = scoring.SegSearch(2, thr, [0, 8])
+    buf.fill_(255)
+    h3, b3 = s.add(seen, gt.to(DEV), xforms=FLIPS, keep_bins=buf)
+    assert b3.data_ptr() == buf.data_ptr() and torch.equal(b3, bins)
+    assert torch.equal(h3, hist)
+    assert isinstance(s.add(seen, gt.to(DEV), xforms=FLIPS), torch.Tensor)
+    with pytest.raises(ValueError):
+        ops.seg_hist(seen, gt.to(DEV), thr, xforms=FLIPS, bins=buf[:2])
+    with pytest.raises(TypeError):
+        ops.seg_hist(seen, gt.to(DEV), thr, xforms=FLIPS, bins=buf.int())
+
+
 def test_guarded_split_planes_small_job(ops):
     """Few large planes: the host splits planes into units (atomic flush)."""
     g = torch.Generator(device=DEV).manual_seed(9)
