@@ -684,6 +684,28 @@ def run_ours(args, cfg):
     validated &= e2e.pop('ok')
     e2e.pop('how', None)
 
+    # ---- side: the other BASELINE configs, kernel timings (N = 1 only) ------
+    if world == 1 and not args.no_side:
+        del srcs, gt, bins_buf
+        torch.cuda.empty_cache()
+        try:
+            sys.path.insert(0, os.path.join(ROOT, 'tools'))
+            import bench_configs as bc
+            bc.DEV, bc.QUIET = dev, True
+            bc.RESULTS.clear()
+            for name, count in (('c1', None), ('c3', 1024), ('c4', 2048),
+                                ('c5', 512), ('am', 256)):
+                getattr(bc, name)(*([count] if count else []))
+                torch.cuda.empty_cache()
+            side['other_configs'] = {
+                'note': 'kernel timings (median of 10 launches, CUDA events) '
+                        'of the other BASELINE.json configs at reduced image '
+                        'counts; full sizes: tools/bench_configs.py, '
+                        'profiles/r02_kernels.jsonl',
+                'lines': list(bc.RESULTS)}
+        except Exception as e:  # a side key must not cost the headline
+            side['other_configs'] = {'error': repr(e)}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

@@ -67,13 +67,19 @@ def synth(n, c, h, w, n_src, seed, empty):
     return srcs, gt
 
 
+RESULTS = []   # every line reported (bench.py collects them as a side key)
+QUIET = False
+
+
 def report(name, ms, nbytes, planes, extra=None):
     gbs = nbytes / (ms * 1e-3) / 1e9
     out = {'config': name, 'ms': round(ms, 4), 'GB/s': round(gbs, 1),
            'frac_of_measured_peak': round(gbs / PEAK, 3),
            'masks_per_s': round(planes / (ms * 1e-3))}
     out.update(extra or {})
-    print(json.dumps(out), flush=True)
+    RESULTS.append(out)
+    if not QUIET:
+        print(json.dumps(out), flush=True)
 
 
 def c1():
