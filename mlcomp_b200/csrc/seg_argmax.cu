@@ -21,12 +21,19 @@
 //   per source   d_c = x_c - max_c x    (the reference's own fp32 subtraction)
 //                t_c = ex2.approx(d_c * log2 e),  p_c = t_c * rcp.approx(sum t)
 //   score_c = sum over the sources of p_c
-// |score_c - reference sum| < 2^-18 per source for C <= 8 (ex2.approx 2^-22
-// relative, the rounding of d * log2 e at most |d| 2^-23 relative on a term
-// e^d <= 1, C + 1 such terms in p_c, rcp.approx 1 ulp; the reference's expf /
-// sum / divide add 2^-21), and the mean is a monotone map of the sum.  So
+// Error of p_c against the true soft-max, C <= 8: t_c
+// has the relative error |d_c| 2^-23.7 (rounded product with the rounded
+// constant) + 2^-22 (ex2.approx), and since p_c |d_c| <= e^d |d| <= 1 / e the
+// subtraction of the maximum makes that small exactly for the classes that
+// matter; with the sum's roundings (7 x 2^-24), one rcp ulp and the product:
+// |p_c - true| < 2^-19.6, the reference's own expf / sum / divide < 2^-20.3,
+// so |score_c - reference sum| < S * 2^-19 and the difference of two scores
+// is off by less than S * 2^-18.  (An estimate WITHOUT the maximum was tried:
+// 18 instructions per pixel fewer, but its error grows with |x| itself, the
+// margin had to be S * 2^-13 and four times as many pixels took the exact
+// path: 2.73 ms against 2.54.)  The mean is a monotone map of the sum.  So
 // when the largest estimated score exceeds the second largest by more than
-// S * 2^-15 (an 8-fold margin), the reference's arg-max is that class.  Every
+// S * 2^-16 (a 4-fold margin), the reference's arg-max is that class.  Every
 // other pixel - near-ties, exact ties (which go to the lowest index), NaN /
 // inf anywhere (every estimated score of the pixel is then NaN) - is evaluated by
 // the exact code of the first kernel (am_scores).  With no activation the
@@ -56,7 +63,7 @@ struct ArgmaxArgs {
   int act;
   int chunks_per_img;
   int items_per_row;  // seg_argmax_items: W / 8
-  float margin;       // seg_argmax_items: S * 2^-15
+  float margin;       // seg_argmax_items: S * 2^-16
 };
 
 // element (class plane `pl`, output pixel (y, x)) of source k, un-transformed
@@ -280,11 +287,46 @@ seg_argmax_kernel(const __grid_constant__ ArgmaxArgs a) {
 }
 
 // ---- the item kernel ---------------------------------------------------------
-// exact arg-max of one pixel (the arithmetic of seg_argmax_kernel)
+// exact arg-max of pixel i of the item whose raw vectors lie in the calling
+// thread's shared-memory slots (source k, class c at slot_sa + (k * CT + c) *
+// stride, in SOURCE order): the arithmetic of am_scores / seg_argmax_kernel,
+// without going back to global memory
 template <int CT>
-__device__ __noinline__ int am_exact_pixel(const ArgmaxArgs &a, long long pl0,
-                                           size_t px, int y, int x) {
-  return am_scores<__half, CT>(a, pl0, px, y, x);
+__device__ __noinline__ int am_exact_pixel(const ArgmaxArgs &a,
+                                           uint32_t slot_sa, uint32_t stride,
+                                           int i) {
+  float acc[CT];
+  const int S = a.src.n;
+  for (int k = 0; k < S; ++k) {
+    const int e = (a.src.xf[k] & MLC_XF_HFLIP) ? 7 - i : i;
+    float v[CT];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) {
+      unsigned short hbits;
+      asm volatile("ld.shared.u16 %0, [%1];"
+                   : "=h"(hbits)
+                   : "r"(slot_sa + (uint32_t)(k * CT + c) * stride + e * 2u));
+      v[c] = __half2float(__ushort_as_half(hbits));
+    }
+    if (a.act == MLC_ACT_SOFTMAX) {
+      float m = -3.402823466e+38f, sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < CT; ++c) m = m < v[c] ? v[c] : m;
+#pragma unroll
+      for (int c = 0; c < CT; ++c) {
+        v[c] = expf(v[c] - m);
+        sum += v[c];
+      }
+#pragma unroll
+      for (int c = 0; c < CT; ++c) v[c] = v[c] / sum;
+    }
+#pragma unroll
+    for (int c = 0; c < CT; ++c) acc[c] = k == 0 ? v[c] : acc[c] + v[c];
+  }
+  AmBest b;
+#pragma unroll
+  for (int c = 0; c < CT; ++c) b.consider(c, acc[c], S);
+  return b.best_c;
 }
 
 // 0x80 in every byte of v that is not zero
@@ -394,8 +436,6 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
       if (it + blockDim.x < i1) issue(it + blockDim.x, cur ^ stage_bytes);
       asm volatile("cp.async.commit_group;" ::: "memory");
       asm volatile("cp.async.wait_group 1;" ::: "memory");
-      const int y = (int)((uint32_t)it / (uint32_t)ipr),
-                xi = (int)((uint32_t)it - (uint32_t)y * (uint32_t)ipr);
       float acc[8][C];
       // (the first source assigns, the others add: a compile-time flag - as a
       // run-time test of k it cost a select per class and pixel)
@@ -476,7 +516,7 @@ seg_argmax_items(const __grid_constant__ ArgmaxArgs a) {
           // the sum of a source's exponentials NaN and with it the score of
           // EVERY class of the pixel: best = NaN, the test is false
           if (!(best - second > a.margin))
-            bc = am_exact_pixel<CT>(a, pl0, (size_t)px, y, xi * 8 + i);
+            bc = am_exact_pixel<CT>(a, my16 + cur, NT * 16u, i);
           lab[i >> 2] |= (uint32_t)bc << (8 * (i & 3));
         }
       } else {
@@ -678,7 +718,7 @@ extern "C" int mlc_seg_argmax(const void *const *src_dev_ptrs,
     }
 #endif
     a.items_per_row = W / 8;
-    a.margin = (float)n_src * 3.0517578125e-5f;  // S * 2^-15
+    a.margin = (float)n_src * 1.52587890625e-5f;  // S * 2^-16
     // counters, then two stages of (S x C x 16 + truth bytes) per thread
     const size_t gt_words = gt_onehot_dev ? n_cls : (gt_label_dev ? 1 : 0);
     const size_t ismem =

@@ -126,6 +126,37 @@ def test_argmax_item_kernel_ties_and_near_ties(ops, c, n_src):
         assert np.array_equal(out['confusion'].cpu().numpy(), cm)
 
 
+@pytest.mark.parametrize('c', [2, 5, 8])
+def test_argmax_item_kernel_extreme_logits(ops, c):
+    """The estimate takes no maximum off the logits: values whose exponentials
+    overflow, flush to zero or leave the sum outside [2^-100, 2^128) must reach
+    the exact path and give the labels of the exact scores."""
+    rng = np.random.default_rng(31 + c)
+    n, h, w = 2, 8, 64
+    levels = np.array([-120., -100., -88., -87.5, -87.25, -87., -86.5, -70.,
+                       -69., -68.5, 0., 60., 86., 87., 88., 88.5, 89., 100.,
+                       2000.], np.float32)
+    base = levels[rng.integers(0, len(levels), (n, c, h, w))]
+    # the same regime for all classes of a pixel in half of the rows, so that
+    # near-ties inside one regime occur too
+    same = levels[rng.integers(0, len(levels), (n, 1, h // 2, w))]
+    base[:, :, :h // 2] = same + rng.integers(-2, 3, (n, c, h // 2, w)) * 0.25
+    tags = [[], ['hflip']]
+    srcs = [torch.from_numpy(base).half(),
+            torch.from_numpy(base + rng.integers(-1, 2, base.shape) * 0.125)
+            .half()]
+    seen = [forward_tta(s_, t) for s_, t in zip(srcs, tags)]
+    dev = [s_.to(DEV) for s_ in seen]
+    own = ops.seg_prob(dev, xforms=tags, activation='softmax').cpu().numpy()
+    want = np.argmax(own, axis=1)
+    label = ops.seg_argmax(dev, tags, 'softmax')['label'].cpu().numpy()
+    assert np.array_equal(label, want), int((label != want).sum())
+    one = ops.seg_argmax(dev[:1], tags[:1], 'softmax')['label'].cpu().numpy()
+    own1 = ops.seg_prob(dev[:1], xforms=tags[:1],
+                        activation='softmax').cpu().numpy()
+    assert np.array_equal(one, np.argmax(own1, axis=1))
+
+
 def test_argmax_nan_and_ties(ops):
     """numpy order: first NaN wins, else first maximum."""
     x = torch.zeros((1, 4, 1, 8), dtype=torch.float32)
