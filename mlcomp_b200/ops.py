@@ -24,7 +24,14 @@ __all__ = ['MLC_XF_HFLIP', 'MLC_XF_VFLIP', 'MLC_XF_TRANSPOSE',
            'mask_outline']
 
 
+_raw_stream = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+
+
 def _stream():
+    # (torch.cuda.current_stream() builds a Stream object through several
+    # device-index look-ups: 19 us a call, four calls per scoring step)
+    if _raw_stream is not None:
+        return c_void_p(_raw_stream(torch.cuda.current_device()))
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
