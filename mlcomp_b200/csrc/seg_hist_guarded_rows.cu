@@ -110,11 +110,6 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src,
       "l"(src), "r"(bytes), "r"(bar)
       : "memory");
 }
-__device__ __forceinline__ void st_shared_u4(uint32_t addr, uint4 v) {
-  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x),
-               "r"(v.y), "r"(v.z), "r"(v.w)
-               : "memory");
-}
 
 struct RowRing {
   uint32_t bar_sa;  // full[s] at + 16 s, empty[s] at + 16 s + 8; behind them
