@@ -143,6 +143,20 @@ def c2g(n=1024):
            n * c * (h * w * 5 + 808), n * c)
 
 
+def t32(n=512):
+    """4-flip TTA of fp32 logits (the reference's own dtype) on the Severstal
+    shape: the exact multi-source kernel (no guarded estimate for fp32)."""
+    c, h, w = 4, 256, 1600
+    tags = [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]
+    srcs, gt = synth(n, c, h, w, 4, 7, 0.86)
+    srcs = [s.float() for s in srcs]
+    thr = ops.threshold_grid(100)
+    out = torch.empty((n, c, 2, 101), dtype=torch.int32, device=DEV)
+    ms = timeit(lambda: ops.seg_hist(srcs, gt, thr, xforms=tags, out=out))
+    report('4-flip TTA fp32 %dx4x256x1600: seg_hist_generic<float>' % n, ms,
+           n * c * (h * w * (4 * 4 + 1) + 808), n * c)
+
+
 def c2r(n=1024):
     """Single-model submission of the Severstal shape: every plane of ONE fp16
     source to run-length pairs (Infer without TTA): rle_kernel<half, CODE, 512>."""
