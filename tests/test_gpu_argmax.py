@@ -157,6 +157,41 @@ def test_argmax_item_kernel_extreme_logits(ops, c):
     assert np.array_equal(one, np.argmax(own1, axis=1))
 
 
+@pytest.mark.parametrize('seed', range(12))
+def test_argmax_item_kernel_random_geometry(ops, seed):
+    """Random class counts, source counts, flips and plane sizes (rows of
+    whole items) through seg_argmax_items, both activations, both forms of
+    the truth: labels equal the arg-max of the device's exact scores."""
+    rng = np.random.default_rng(500 + seed)
+    c = int(rng.integers(2, 9))
+    n_src = int(rng.integers(1, 4))
+    n, h, w = int(rng.integers(1, 4)), int(rng.integers(1, 20)), \
+        8 * int(rng.integers(1, 40))
+    flips = [[], ['hflip'], ['vflip'], ['hflip', 'vflip']]
+    tags = [flips[int(k)] for k in rng.integers(0, 4, n_src)]
+    scale = float(rng.choice([0.25, 1.0, 4.0]))
+    srcs = [torch.from_numpy((rng.normal(0, scale, (n, c, h, w)))
+                             .astype(np.float32)).half() for _ in range(n_src)]
+    seen = [forward_tta(s_, t) for s_, t in zip(srcs, tags)]
+    dev = [s_.to(DEV) for s_ in seen]
+    gt_label = torch.from_numpy(rng.integers(0, c + 1, (n, h, w))
+                                .astype(np.uint8))
+    g1 = np.stack([(gt_label.numpy() == j) for j in range(c)], axis=1)
+    for act in ('softmax', None):
+        own = ops.seg_prob(dev, xforms=tags, activation=act).cpu().numpy()
+        want = np.argmax(own, axis=1)
+        out = ops.seg_argmax(dev, tags, act, gt_label=gt_label.to(DEV),
+                             want_counts=True, want_confusion=True)
+        label = out['label'].cpu().numpy()
+        assert np.array_equal(label, want), int((label != want).sum())
+        assert np.array_equal(out['counts'].cpu().numpy(),
+                              oracle.onehot_counts(label, g1))
+        out2 = ops.seg_argmax(dev, tags, act, gt_onehot=torch.from_numpy(
+            g1.astype(np.uint8) * int(rng.integers(1, 256))).to(DEV),
+            want_label=False, want_counts=True)
+        assert torch.equal(out2['counts'], out['counts'])
+
+
 def test_argmax_nan_and_ties(ops):
     """numpy order: first NaN wins, else first maximum."""
     x = torch.zeros((1, 4, 1, 8), dtype=torch.float32)

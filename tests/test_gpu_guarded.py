@@ -327,6 +327,32 @@ def test_guarded_tma_rows(ops, shape, n_src, flips):
     check(ops, seen, tags, gt.to(DEV), oracle.threshold_grid(100))
 
 
+@pytest.mark.parametrize('seed', range(24))
+def test_guarded_rows_random_geometry(ops, seed):
+    """Random widths (9 .. 700, mostly no multiple of 8), heights, plane
+    counts, source counts and flip sets through the band-staging kernel:
+    histograms and bin planes equal the exact binning."""
+    rng = np.random.default_rng(1000 + seed)
+    w = int(rng.integers(9, 700))
+    if seed % 6 == 0:
+        w = w // 8 * 8 + 8          # rows of whole items at odd plane starts
+    h = int(rng.integers(1, 24))
+    n, c = int(rng.integers(1, 4)), int(rng.integers(1, 6))
+    n_src = int(rng.integers(2, 5))
+    tags = [FLIPS[int(k)] for k in rng.integers(0, 4, n_src)]
+    srcs, gt = synth_seg(n, c, h, w, seed=seed, n_src=n_src)
+    seen = [forward_tta(s_, t) for s_, t in zip(srcs, tags)]
+    # planes that start at any 16-byte phase: views into a larger buffer
+    dev = []
+    for s_ in seen:
+        pad = int(rng.integers(0, 4)) * 8
+        buf = torch.empty(s_.numel() + pad, dtype=torch.float16, device=DEV)
+        v = buf[pad:].view(s_.shape)
+        v.copy_(s_)
+        dev.append(v)
+    check(ops, dev, tags, gt.to(DEV), oracle.threshold_grid(100))
+
+
 def test_guarded_tma_rows_special_values_and_tensor_ends(ops):
     """NaN / inf / huge values next to row ends, and tensors that end exactly
     where their allocation ends (a copy that runs over the end of the tensor
