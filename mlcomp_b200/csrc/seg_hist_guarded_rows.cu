@@ -45,7 +45,8 @@
 // whatever lies behind (or, flipped, before) the row: not counted
 // (finish_item nvalid).
 //
-// Pipeline: a full / empty mbarrier pair per slot, four slots.  Lanes 0 .. NS
+// Pipeline: a full / empty mbarrier pair per slot, four to eight slots (as
+// many as fit beside the counters).  Lanes 0 .. NS
 // of the last warp are the producer (wait for a slot to be empty, write its
 // header, issue one copy each: the sources and the truth bytes); the other
 // warps take 32 consecutive items of the unit at a time from a shared
@@ -55,7 +56,11 @@
 
 namespace mlc {
 
+// ring slots: as many as fit beside the counters, at least four (the host
+// sizes the bands for four), at most eight.  Depth matters: on 350 x 525
+// planes three slots ran at 0.63 of the HBM peak, four at 0.71, five at 0.72
 constexpr int kRowsSlots = 4;
+constexpr int kRowsMaxSlots = 8;
 constexpr int kRowsThreads = 512;
 constexpr uint32_t kRowsSmem = 112u * 1024u;  // dynamic, two CTAs per SM
 constexpr uint32_t kRowsRing = 78u * 1024u;   // of which the ring may take
@@ -115,6 +120,8 @@ struct RowRing {
   uint32_t bar_sa;  // full[s] at + 16 s, empty[s] at + 16 s + 8; behind them
                     // the next unassigned item of the CTA's unit
   uint32_t a_sa;    // slot s at + s * slot_bytes
+  int n_slot;
+  uint32_t slot_magic;  // floor(2^32 / n_slot) + 1
 };
 
 // All 32 lanes of the producer warp take part: lane = 8 * q + j serves copy j
@@ -179,7 +186,7 @@ __device__ __forceinline__ void rows_produce(const HistArgs &a,
       bulk_g2s(slot_sa + dst_off, reinterpret_cast<const void *>(from), bytes,
                full);
     }
-    if (++slot == kRowsSlots) {
+    if (++slot == ring.n_slot) {
       slot = 0;
       ++round;
     }
@@ -195,7 +202,7 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
   const int lane = threadIdx.x & 31;
   const int ipt = g.ipt, W = a.W;
   const int n_items = nrows * ipt;
-  const uint32_t next_sa = ring.bar_sa + kRowsSlots * 16u;
+  const uint32_t next_sa = ring.bar_sa + kRowsMaxSlots * 16u;
   const size_t plane_off = (size_t)plane * a.plane_px;
   int guard = 0;  // always >= 0, not provably so (see pf_unit)
   while (true) {
@@ -216,9 +223,10 @@ __device__ __forceinline__ void rows_consume(const HistArgs &a,
     const int r = (int)__umulhi((uint32_t)it, g.ipt_magic);
     const int xi = it - r * ipt;
     const int band = r >> g.log_r, rr = r & ((1 << g.log_r) - 1);
-    const int sl = band & (kRowsSlots - 1);
+    const uint32_t turn = __umulhi((uint32_t)band, ring.slot_magic);
+    const int sl = band - (int)turn * ring.n_slot;
     const uint32_t full = ring.bar_sa + sl * 16u;
-    mbar_wait(full, (uint32_t)(band / kRowsSlots) & 1u);
+    mbar_wait(full, turn & 1u);
     const uint32_t slot_sa = ring.a_sa + sl * g.slot_bytes;
     uint32_t w[4][4];
     const uint32_t row_sa = slot_sa + 32u * rr;
@@ -288,14 +296,16 @@ seg_hist_guarded_rows(const __grid_constant__ HistArgs a,
   const uint32_t cnt_sa = (end_sa - 16384u) & ~16383u;
   RowRing ring;
   ring.bar_sa = (gsm_sa + 15u) & ~15u;
-  ring.a_sa = (ring.bar_sa + kRowsSlots * 16u + 16u + 127u) & ~127u;
+  ring.a_sa = ring.bar_sa + kRowsMaxSlots * 16u + 16u;
+  ring.n_slot = min(kRowsMaxSlots, (int)((cnt_sa - ring.a_sa) / g.slot_bytes));
+  ring.slot_magic = (uint32_t)((1ull << 32) / (unsigned)max(ring.n_slot, 1) + 1);
   uint32_t *cnt = gsm + (cnt_sa - gsm_sa) / 4;
   float *thr = reinterpret_cast<float *>(cnt + nbins * 32);  // [B]
   for (int i = threadIdx.x; i < nbins * 32; i += NT) cnt[i] = 0;
   for (int i = threadIdx.x; i < B; i += NT) thr[i] = a.thr.v[i];
   if (threadIdx.x == 0) {
-    st_shared_u32(ring.bar_sa + kRowsSlots * 16u, 0u);
-    for (int s = 0; s < kRowsSlots; ++s) {
+    st_shared_u32(ring.bar_sa + kRowsMaxSlots * 16u, 0u);
+    for (int s = 0; s < ring.n_slot; ++s) {
       mbar_init(ring.bar_sa + s * 16u, 1u);
       mbar_init(ring.bar_sa + s * 16u + 8u, (uint32_t)(g.ipt << g.log_r));
     }
@@ -305,8 +315,7 @@ seg_hist_guarded_rows(const __grid_constant__ HistArgs a,
   const uint32_t plane = blockIdx.x, sub = blockIdx.y, upp = gridDim.y;
   const int row0 = (int)sub * g.rows_per_unit;
   const int nrows = max(0, min(a.H, row0 + g.rows_per_unit) - row0);
-  const bool fits = ring.a_sa + kRowsSlots * g.slot_bytes <= cnt_sa;
-  if (!fits) __trap();
+  if (ring.n_slot < 2) __trap();  // (the host sized the slots for four)
   if (threadIdx.x >= NT - 32) {
     rows_produce<NS>(a, g, ring, plane, row0, nrows);
   } else {
@@ -354,7 +363,7 @@ bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
     const uint32_t pitch = 16u * ((2u * W * R + 30u + 15u) / 16u + 2u);
     const uint32_t gt_off = 32u * R + (uint32_t)S * pitch;
     const uint32_t slot =
-        (gt_off + 16u * ((W * R + 15u + 15u) / 16u + 3u) + 127u) / 128u * 128u;
+        gt_off + 16u * ((W * R + 15u + 15u) / 16u + 3u);
     if (kRowsSlots * slot > kRowsRing) break;
     g.log_r = lr;
     g.pitch = pitch;
