@@ -354,7 +354,7 @@ bool seg_hist_guarded_rows_launch(HistArgs &a, cudaStream_t st, int *rc) {
     return false;
   g.nvalid_tail = (W & 7) ? (W & 7) : 8;
   g.ipt_magic = (uint32_t)((1ull << 32) / (unsigned)g.ipt + 1);
-  // rows per band: the largest power of two whose four slots fit the ring
+  // rows per band: the largest power of two whose four slots fit the ring (a fifth .. eighth slot is used when it fits)
   // (a source's area: 16 bytes of headroom, the vectors that enclose the
   // band's rows, 16 bytes spare for the second vector of the last window)
   g.log_r = -1;
