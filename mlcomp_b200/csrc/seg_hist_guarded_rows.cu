@@ -155,7 +155,6 @@ __device__ __forceinline__ void rows_produce(const HistArgs &a,
     const int nr = min(R, nrows - r), yb = row0 + r;
     const uint32_t slot_sa = ring.a_sa + slot * g.slot_bytes;
     const uint32_t full = ring.bar_sa + slot * 16u;
-    if (round > 0) mbar_wait(full + 8u, (round - 1u) & 1u);
     // the band's rows of this source are contiguous; the lowest one is
     const int ys_lo = vf ? H - yb - nr : yb;
     const uintptr_t p = base + (size_t)ys_lo * W * esz;
@@ -168,6 +167,9 @@ __device__ __forceinline__ void rows_produce(const HistArgs &a,
 #pragma unroll
     for (int d = 1; d <= 4; d <<= 1)
       total += __shfl_xor_sync(0xffffffffu, total, d, 8);
+    // (the addresses are ready before the slot is: only the header stores and
+    // the copies themselves follow the wait)
+    if (round > 0) mbar_wait(full + 8u, (round - 1u) & 1u);
     for (int rr = q; rr < nr; rr += 4) {
       // row rr of the band is the (nr - 1 - rr)-th of the copy when flipped
       const uint32_t at = (uint32_t)((vf ? nr - 1 - rr : rr) * W);
